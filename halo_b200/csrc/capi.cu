@@ -1,0 +1,343 @@
+// C ABI of libhalo_b200 (include/halo_b200.h): runtime, resident public parameters, MSM entry points,
+// arithmetic micro-benchmarks.  Each entry point cites the reference interface it stands in for in the header.
+#include "runtime.cuh"
+#include <cstring>
+
+namespace halo {
+
+Runtime& rt() { static Runtime r; return r; }
+
+int ws_get(int slot, size_t bytes, void** out) {
+    Runtime& R = rt();
+    if ((int)R.arena.size() < WS_COUNT) R.arena.resize(WS_COUNT);
+    DeviceBuf& b = R.arena[slot];
+    if (b.cap < bytes) {
+        if (b.p) { HALO_CUDA(cudaStreamSynchronize(R.stream)); HALO_CUDA(cudaFree(b.p)); b.p = nullptr; b.cap = 0; }
+        size_t cap = bytes + bytes / 8 + 256;
+        HALO_CUDA(cudaMalloc(&b.p, cap));
+        b.cap = cap;
+    }
+    *out = b.p;
+    return HALO_OK;
+}
+int pinned_get(size_t bytes, void** out) {
+    Runtime& R = rt();
+    if (R.pinned_cap < bytes) {
+        if (R.pinned) { HALO_CUDA(cudaStreamSynchronize(R.stream)); HALO_CUDA(cudaFreeHost(R.pinned)); R.pinned = nullptr; R.pinned_cap = 0; }
+        size_t cap = bytes < 4096 ? 4096 : bytes;
+        HALO_CUDA(cudaMallocHost(&R.pinned, cap));
+        R.pinned_cap = cap;
+    }
+    *out = R.pinned;
+    return HALO_OK;
+}
+
+template <int C> int msm_device(const void* d_bases, const void* d_scalars, size_t k, uint64_t out_xyz[12]);
+
+// ---- on-curve check for uploaded parameters (wrappers.rs:606 asserts per point) ----
+template <int C>
+__global__ void check_on_curve(const Affine<C>* pts, size_t n, int* bad) {
+    constexpr int B = CurveTraits<C>::BASE;
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Affine<C> p = pts[i];
+    if (affine_is_identity<C>(p)) return;
+    Fe<B> lhs = fe_sqr<B>(p.y);
+    Fe<B> rhs = fe_add<B>(fe_mul<B>(fe_sqr<B>(p.x), p.x), fe_from_u64<B>(5));
+    if (!fe_eq<B>(lhs, rhs)) atomicAdd(bad, 1);
+}
+
+template <int F>
+__global__ void field_op_kernel(int op, const Fe<F>* a, const Fe<F>* b, Fe<F>* o, size_t n) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fe<F> x = a[i], y = b ? b[i] : fe_zero<F>(), r;
+    switch (op) {
+        case 0: r = fe_mul<F>(x, y); break;
+        case 1: r = fe_add<F>(x, y); break;
+        case 2: r = fe_sub<F>(x, y); break;
+        case 3: r = fe_inv<F>(x); break;
+        case 4: r = fe_to_canonical<F>(x); break;
+        default: r = fe_from_canonical<F>(x); break;
+    }
+    o[i] = r;
+}
+
+// ---- arithmetic micro-benchmarks ----
+template <int F>
+__global__ void bench_modmul_kernel(int iters, Fe<F>* out) {
+    u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
+    Fe<F> a[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[j].l[i] = tid * 2654435761u + 40503u * (i + 8 * j) + 17u;
+        a[j].l[7] &= 0x3fffffffu;
+    }
+    Fe<F> m = a[3];
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) a[j] = fe_mul<F>(a[j], m);
+    }
+    Fe<F> s = fe_add<F>(fe_add<F>(a[0], a[1]), fe_add<F>(a[2], a[3]));
+    if (s.l[0] == 0x12345678u && s.l[5] == 77u) out[tid & 1023] = s;   // practically never: keeps the work alive
+    if (tid == 0) out[0] = s;
+}
+__global__ void bench_imad_kernel(int iters, unsigned long long* out) {
+    u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long acc[8];
+    u32 x = tid * 2654435761u + 12345u, y = tid ^ 0x9e3779b9u;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = tid + j;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = (unsigned long long)x * (u32)(y + j) + acc[j];
+        x += (u32)acc[0];
+    }
+    unsigned long long s = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s ^= acc[j];
+    if (s == 0x123456789abcdefULL) out[tid & 1023] = s;
+    if (tid == 0) out[0] = s;
+}
+
+}  // namespace halo
+
+using namespace halo;
+
+#define LOCK() std::lock_guard<std::recursive_mutex> lock__(rt().mu)
+#define NEED_INIT() HALO_CHECK(rt().inited, HALO_ENOINIT, "halo_init has not been called")
+
+extern "C" int halo_msm(int, const uint64_t*, size_t, const uint64_t*, size_t, uint64_t*);
+
+// point_dot (group.rs:53-56): CurveGroup::normalize_batch (one inversion, Montgomery's trick) on the host — the only
+// caller passes m <= 1024 accumulated U's (acc.rs:166) — then the affine MSM on the device.
+template <int C>
+static int msm_proj_impl(const uint64_t* bases_xyz, const uint64_t* scalars, size_t k, uint64_t out_xyz[12]) {
+    constexpr int B = CurveTraits<C>::BASE;
+    std::vector<Affine<C>> aff(k);
+    std::vector<Fe<B>> pre(k);
+    Fe<B> acc = fe_one<B>();
+    for (size_t i = 0; i < k; ++i) {
+        Jac<C> p; memcpy(&p, bases_xyz + 12 * i, 96);
+        pre[i] = acc;
+        if (!fe_is_zero<B>(p.Z)) acc = fe_mul<B>(acc, p.Z);
+    }
+    Fe<B> inv = fe_inv<B>(acc);
+    for (size_t i = k; i-- > 0;) {
+        Jac<C> p; memcpy(&p, bases_xyz + 12 * i, 96);
+        if (fe_is_zero<B>(p.Z)) { aff[i].x = fe_zero<B>(); aff[i].y = fe_zero<B>(); continue; }
+        Fe<B> zi = fe_mul<B>(inv, pre[i]);
+        inv = fe_mul<B>(inv, p.Z);
+        Fe<B> zi2 = fe_sqr<B>(zi);
+        aff[i].x = fe_mul<B>(p.X, zi2);
+        aff[i].y = fe_mul<B>(p.Y, fe_mul<B>(zi2, zi));
+    }
+    return halo_msm(C, (const uint64_t*)aff.data(), 0, scalars, k, out_xyz);
+}
+
+extern "C" {
+
+const char* halo_last_error(void) { return rt().err.c_str(); }
+
+int halo_init(int device) {
+    LOCK();
+    Runtime& R = rt();
+    if (R.inited) return HALO_OK;
+    if (device >= 0) HALO_CUDA(cudaSetDevice(device));
+    HALO_CUDA(cudaGetDevice(&R.device));
+    cudaDeviceProp prop;
+    HALO_CUDA(cudaGetDeviceProperties(&prop, R.device));
+    R.sm_count = prop.multiProcessorCount;
+    HALO_CUDA(cudaStreamCreateWithFlags(&R.own_stream, cudaStreamNonBlocking));
+    R.stream = R.own_stream;
+    R.arena.resize(WS_COUNT);
+    R.inited = true;
+    return HALO_OK;
+}
+
+int halo_shutdown(void) {
+    LOCK();
+    Runtime& R = rt();
+    if (!R.inited) return HALO_OK;
+    cudaStreamSynchronize(R.stream);
+    for (auto& b : R.arena) if (b.p) cudaFree(b.p);
+    R.arena.clear();
+    for (int c = 0; c < 2; ++c) { if (R.pp[c].d_gs) cudaFree(R.pp[c].d_gs); R.pp[c] = ResidentParams(); }
+    if (R.pinned) cudaFreeHost(R.pinned);
+    R.pinned = nullptr; R.pinned_cap = 0;
+    cudaStreamDestroy(R.own_stream);
+    R.own_stream = R.stream = nullptr;
+    R.inited = false;
+    return HALO_OK;
+}
+
+int halo_set_stream(void* s) {
+    LOCK(); NEED_INIT();
+    Runtime& R = rt();
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
+    R.stream = s ? (cudaStream_t)s : R.own_stream;
+    return HALO_OK;
+}
+int halo_device_synchronize(void) {
+    LOCK(); NEED_INIT();
+    HALO_CUDA(cudaStreamSynchronize(rt().stream));
+    return HALO_OK;
+}
+
+int halo_pp_load(int curve, const uint64_t* gs_xy, size_t n, const uint64_t s_xy[8], const uint64_t h_xy[8]) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
+    HALO_CHECK(gs_xy && s_xy && h_xy && n > 0, HALO_EINVAL, "pp_load: null or empty parameters");
+    Runtime& R = rt();
+    ResidentParams& P = R.pp[curve];
+    if (P.n) {
+        HALO_CHECK(n <= P.n, HALO_EPARAMS, "public parameters already resident with a smaller length (set_pp is monotone)");
+        return HALO_OK;
+    }
+    void* d = nullptr;
+    HALO_CUDA(cudaMalloc(&d, n * 64));
+    cudaError_t e = cudaMemcpyAsync(d, gs_xy, n * 64, cudaMemcpyHostToDevice, R.stream);
+    int* d_bad = nullptr;
+    if (e == cudaSuccess) e = cudaMalloc(&d_bad, 4);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d_bad, 0, 4, R.stream);
+    if (e == cudaSuccess) {
+        unsigned grid = (unsigned)((n + 255) / 256);
+        if (curve == 0) check_on_curve<0><<<grid, 256, 0, R.stream>>>((const Affine<0>*)d, n, d_bad);
+        else check_on_curve<1><<<grid, 256, 0, R.stream>>>((const Affine<1>*)d, n, d_bad);
+        e = cudaGetLastError();
+    }
+    int bad = 0;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&bad, d_bad, 4, cudaMemcpyDeviceToHost, R.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(R.stream);
+    if (d_bad) cudaFree(d_bad);
+    if (e != cudaSuccess) { cudaFree(d); R.err = std::string("pp_load: ") + cudaGetErrorString(e); return HALO_ECUDA; }
+    if (bad) { cudaFree(d); R.err = "pp_load: generator not on the curve"; return HALO_EINVAL; }
+    P.d_gs = d; P.n = n;
+    memcpy(P.s_xy, s_xy, 64); memcpy(P.h_xy, h_xy, 64);
+    return HALO_OK;
+}
+size_t halo_pp_len(int curve) { return (curve == 0 || curve == 1) ? rt().pp[curve].n : 0; }
+int halo_pp_reset(int curve) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
+    Runtime& R = rt();
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
+    if (R.pp[curve].d_gs) cudaFree(R.pp[curve].d_gs);
+    R.pp[curve] = ResidentParams();
+    return HALO_OK;
+}
+
+int halo_msm_set_window(int c) { rt().msm_window_override = c; return HALO_OK; }
+
+int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k, uint64_t out_xyz[12]) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
+    HALO_CHECK(out_xyz && (d_scalars || k == 0), HALO_EINVAL, "msm: null pointer");
+    Runtime& R = rt();
+    const char* bases = (const char*)d_bases_xy;
+    if (!bases) {
+        HALO_CHECK(R.pp[curve].n >= base_off + k, HALO_EPARAMS, "msm: resident generators missing or too few");
+        bases = (const char*)R.pp[curve].d_gs;
+    }
+    bases += base_off * 64;
+    return curve == 0 ? msm_device<0>(bases, d_scalars, k, out_xyz) : msm_device<1>(bases, d_scalars, k, out_xyz);
+}
+
+int halo_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_t* scalars, size_t k, uint64_t out_xyz[12]) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
+    HALO_CHECK(out_xyz && (scalars || k == 0), HALO_EINVAL, "msm: null pointer");
+    Runtime& R = rt();
+    void *d_s = nullptr, *d_b = nullptr;
+    if (k) {
+        if (int e = ws_get(WS_SCALARS, k * 32, &d_s)) return e;
+        HALO_CUDA(cudaMemcpyAsync(d_s, scalars, k * 32, cudaMemcpyHostToDevice, R.stream));
+        if (bases_xy) {
+            if (int e = ws_get(WS_BASES, k * 64, &d_b)) return e;
+            HALO_CUDA(cudaMemcpyAsync(d_b, bases_xy + 8 * base_off, k * 64, cudaMemcpyHostToDevice, R.stream));
+            base_off = 0;
+        }
+    }
+    return halo_msm_dev(curve, d_b, base_off, d_s, k, out_xyz);
+}
+
+int halo_msm_batch(int curve, size_t base_off, const uint64_t* scalars, size_t k, size_t b, uint64_t* out_xyz) {
+    LOCK(); NEED_INIT();
+    for (size_t i = 0; i < b; ++i) {
+        int e = halo_msm(curve, nullptr, base_off, scalars + i * k * 4, k, out_xyz + 12 * i);
+        if (e) return e;
+    }
+    return HALO_OK;
+}
+
+int halo_msm_proj(int curve, const uint64_t* bases_xyz, const uint64_t* scalars, size_t k, uint64_t out_xyz[12]) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
+    HALO_CHECK(out_xyz && ((bases_xyz && scalars) || k == 0), HALO_EINVAL, "msm_proj: null pointer");
+    return curve == 0 ? msm_proj_impl<0>(bases_xyz, scalars, k, out_xyz) : msm_proj_impl<1>(bases_xyz, scalars, k, out_xyz);
+}
+
+int halo_field_op(int field, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK((field == 0 || field == 1) && a && out && op >= 0 && op <= 5, HALO_EINVAL, "field_op: bad argument");
+    if (n == 0) return HALO_OK;
+    Runtime& R = rt();
+    void *da, *db = nullptr, *dout;
+    if (int e = ws_get(WS_TMP0, n * 32, &da)) return e;
+    if (int e = ws_get(WS_TMP2, n * 32, &dout)) return e;
+    HALO_CUDA(cudaMemcpyAsync(da, a, n * 32, cudaMemcpyHostToDevice, R.stream));
+    if (b) {
+        if (int e = ws_get(WS_TMP1, n * 32, &db)) return e;
+        HALO_CUDA(cudaMemcpyAsync(db, b, n * 32, cudaMemcpyHostToDevice, R.stream));
+    }
+    unsigned grid = (unsigned)((n + 127) / 128);
+    if (field == 0) field_op_kernel<0><<<grid, 128, 0, R.stream>>>(op, (const Fe<0>*)da, (const Fe<0>*)db, (Fe<0>*)dout, n);
+    else field_op_kernel<1><<<grid, 128, 0, R.stream>>>(op, (const Fe<1>*)da, (const Fe<1>*)db, (Fe<1>*)dout, n);
+    HALO_CUDA(cudaGetLastError());
+    HALO_CUDA(cudaMemcpyAsync(out, dout, n * 32, cudaMemcpyDeviceToHost, R.stream));
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
+    return HALO_OK;
+}
+
+int halo_bench_modmul(int field, int blocks, int threads, int iters, float* ms, uint64_t out[4]) {
+    LOCK(); NEED_INIT();
+    Runtime& R = rt();
+    void* d;
+    if (int e = ws_get(WS_TMP0, 1024 * 32, &d)) return e;
+    cudaEvent_t e0, e1;
+    HALO_CUDA(cudaEventCreate(&e0)); HALO_CUDA(cudaEventCreate(&e1));
+    for (int rep = 0; rep < 2; ++rep) {      // first pass warms up
+        HALO_CUDA(cudaEventRecord(e0, R.stream));
+        if (field == 0) bench_modmul_kernel<0><<<blocks, threads, 0, R.stream>>>(iters, (Fe<0>*)d);
+        else bench_modmul_kernel<1><<<blocks, threads, 0, R.stream>>>(iters, (Fe<1>*)d);
+        HALO_CUDA(cudaEventRecord(e1, R.stream));
+        HALO_CUDA(cudaStreamSynchronize(R.stream));
+    }
+    HALO_CUDA(cudaGetLastError());
+    HALO_CUDA(cudaEventElapsedTime(ms, e0, e1));
+    HALO_CUDA(cudaMemcpy(out, d, 32, cudaMemcpyDeviceToHost));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return HALO_OK;
+}
+int halo_bench_imad(int blocks, int threads, int iters, float* ms, uint64_t* out) {
+    LOCK(); NEED_INIT();
+    Runtime& R = rt();
+    void* d;
+    if (int e = ws_get(WS_TMP0, 1024 * 32, &d)) return e;
+    cudaEvent_t e0, e1;
+    HALO_CUDA(cudaEventCreate(&e0)); HALO_CUDA(cudaEventCreate(&e1));
+    for (int rep = 0; rep < 2; ++rep) {
+        HALO_CUDA(cudaEventRecord(e0, R.stream));
+        bench_imad_kernel<<<blocks, threads, 0, R.stream>>>(iters, (unsigned long long*)d);
+        HALO_CUDA(cudaEventRecord(e1, R.stream));
+        HALO_CUDA(cudaStreamSynchronize(R.stream));
+    }
+    HALO_CUDA(cudaGetLastError());
+    HALO_CUDA(cudaEventElapsedTime(ms, e0, e1));
+    HALO_CUDA(cudaMemcpy(out, d, 8, cudaMemcpyDeviceToHost));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return HALO_OK;
+}
+
+}  // extern "C"

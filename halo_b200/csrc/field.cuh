@@ -1,0 +1,339 @@
+// 255-bit Montgomery arithmetic for the two Pasta fields on the sm_100a 32-bit integer pipe.
+//
+// Replaces, on the device, what the reference gets from ark-ff 0.5.0
+// `Fp<MontBackend<_,4>,4>` (call sites: crates/group/src/group.rs:43-66,
+// crates/accumulation/src/pcdl.rs:412-435 ...).  Same in-memory form as the reference
+// (crates/group/src/wrappers.rs:603-616): Montgomery, R = 2^256, 4 x u64 LE limbs == 8 x u32 LE limbs.
+//
+// Both moduli have the shape  p = 1 + p1*2^32 + p2*2^64 + p3*2^96 + 2^254  with -p^{-1} = -1 (mod 2^32), so
+//   * the Montgomery quotient digit is just  m = -t0  (no multiplication),
+//   * m*p needs 3 wide multiplies (p1,p2,p3) instead of 8; the 2^254 term is a shift,
+//   * p1+p2+p3 < 2^32, so a whole reduction column fits a 64-bit accumulator without carry flags.
+// A modular multiplication is therefore 64 (product) + 24 (reduction) = 88 IMAD.WIDE on the FMA pipe
+// (instead of 128 for a generic modulus) plus carry/shift work that rides the ALU pipe.
+//
+// The carry-chain primitives are individual PTX statements on the device.  With -DHALO_EMULATE_PTX the same
+// algorithm compiles for the host with an emulated carry flag (used by tests/test_host_emulation to pin the
+// device algorithm on a machine without a GPU).  Plain host builds (the host-side Fiat-Shamir transcript) use
+// a 64-bit-limb implementation of the same functions.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define HD __host__ __device__ __forceinline__
+#define DEV __host__ __device__ __forceinline__
+#else
+#define HD inline
+#define DEV inline
+#endif
+
+namespace halo {
+
+typedef uint32_t u32;
+typedef uint64_t u64;
+
+// field id 0: halo Fp (ark_pallas::Fr), 1: halo Fq (ark_pallas::Fq)  -- crates/group/src/lib.rs:8-9
+template <int FID> struct FieldConst;
+template <> struct FieldConst<0> {
+    static constexpr u32 P1 = 0x8c46eb21u, P2 = 0x0994a8ddu, P3 = 0x224698fcu;
+};
+template <> struct FieldConst<1> {
+    static constexpr u32 P1 = 0x992d30edu, P2 = 0x094cf91bu, P3 = 0x224698fcu;
+};
+// limb k of the modulus
+template <int FID> HD constexpr u32 modulus_limb(int k) {
+    return k == 0 ? 1u : k == 1 ? FieldConst<FID>::P1 : k == 2 ? FieldConst<FID>::P2 : k == 3 ? FieldConst<FID>::P3
+         : k == 7 ? 0x40000000u : 0u;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// carry-chain primitives
+// ---------------------------------------------------------------------------------------------------------
+#if defined(__CUDA_ARCH__)
+#define HALO_PTX_PATH 1
+DEV u32 add_cc(u32 a, u32 b) { u32 r; asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+DEV u32 addc_cc(u32 a, u32 b) { u32 r; asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+DEV u32 addc(u32 a, u32 b) { u32 r; asm volatile("addc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+DEV u32 sub_cc(u32 a, u32 b) { u32 r; asm volatile("sub.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+DEV u32 subc_cc(u32 a, u32 b) { u32 r; asm volatile("subc.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+DEV u32 subc(u32 a, u32 b) { u32 r; asm volatile("subc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+DEV u32 mad_lo_cc(u32 a, u32 b, u32 c) { u32 r; asm volatile("mad.lo.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+DEV u32 madc_lo_cc(u32 a, u32 b, u32 c) { u32 r; asm volatile("madc.lo.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+DEV u32 madc_hi_cc(u32 a, u32 b, u32 c) { u32 r; asm volatile("madc.hi.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+DEV u32 madc_hi(u32 a, u32 b, u32 c) { u32 r; asm volatile("madc.hi.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+#elif defined(HALO_EMULATE_PTX)
+#define HALO_PTX_PATH 1
+static thread_local u32 g_cc = 0;   // emulated carry / borrow flag
+inline u32 add_cc(u32 a, u32 b) { u64 s = (u64)a + b; g_cc = (u32)(s >> 32); return (u32)s; }
+inline u32 addc_cc(u32 a, u32 b) { u64 s = (u64)a + b + g_cc; g_cc = (u32)(s >> 32); return (u32)s; }
+inline u32 addc(u32 a, u32 b) { u64 s = (u64)a + b + g_cc; return (u32)s; }
+inline u32 sub_cc(u32 a, u32 b) { u64 s = (u64)a - b; g_cc = (u32)(s >> 63); return (u32)s; }
+inline u32 subc_cc(u32 a, u32 b) { u64 s = (u64)a - b - g_cc; g_cc = (u32)(s >> 63); return (u32)s; }
+inline u32 subc(u32 a, u32 b) { u64 s = (u64)a - b - g_cc; return (u32)s; }
+inline u32 mad_lo_cc(u32 a, u32 b, u32 c) { u64 s = (u64)(u32)((u64)a * b) + c; g_cc = (u32)(s >> 32); return (u32)s; }
+inline u32 madc_lo_cc(u32 a, u32 b, u32 c) { u64 s = (u64)(u32)((u64)a * b) + c + g_cc; g_cc = (u32)(s >> 32); return (u32)s; }
+inline u32 madc_hi_cc(u32 a, u32 b, u32 c) { u64 s = (u64)(u32)(((u64)a * b) >> 32) + c + g_cc; g_cc = (u32)(s >> 32); return (u32)s; }
+inline u32 madc_hi(u32 a, u32 b, u32 c) { u64 s = (u64)(u32)(((u64)a * b) >> 32) + c + g_cc; return (u32)s; }
+#endif
+
+// ---------------------------------------------------------------------------------------------------------
+// element type
+// ---------------------------------------------------------------------------------------------------------
+template <int FID>
+struct alignas(16) Fe {
+    u32 l[8];
+};
+
+template <int FID> HD Fe<FID> fe_zero() { Fe<FID> r; for (int i = 0; i < 8; ++i) r.l[i] = 0; return r; }
+template <int FID> HD bool fe_is_zero(const Fe<FID>& a) {
+    u32 o = 0; for (int i = 0; i < 8; ++i) o |= a.l[i]; return o == 0;
+}
+template <int FID> HD bool fe_eq(const Fe<FID>& a, const Fe<FID>& b) {
+    u32 o = 0; for (int i = 0; i < 8; ++i) o |= a.l[i] ^ b.l[i]; return o == 0;
+}
+
+#if defined(HALO_PTX_PATH)
+// ---------------------------------------------------------------------------------------------------------
+// device algorithm (also compiled for the host under HALO_EMULATE_PTX)
+// ---------------------------------------------------------------------------------------------------------
+template <int FID> DEV Fe<FID> fe_add(const Fe<FID>& a, const Fe<FID>& b) {
+    u32 r[8], t[8];
+    r[0] = add_cc(a.l[0], b.l[0]);
+#pragma unroll
+    for (int i = 1; i < 8; ++i) r[i] = addc_cc(a.l[i], b.l[i]);      // a+b < 2^256: no carry out
+    t[0] = sub_cc(r[0], modulus_limb<FID>(0));
+#pragma unroll
+    for (int i = 1; i < 8; ++i) t[i] = subc_cc(r[i], modulus_limb<FID>(i));
+    u32 borrow = subc(0, 0);                                          // 0xffffffff when r < p
+    Fe<FID> o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.l[i] = borrow ? r[i] : t[i];
+    return o;
+}
+
+template <int FID> DEV Fe<FID> fe_sub(const Fe<FID>& a, const Fe<FID>& b) {
+    u32 r[8];
+    r[0] = sub_cc(a.l[0], b.l[0]);
+#pragma unroll
+    for (int i = 1; i < 8; ++i) r[i] = subc_cc(a.l[i], b.l[i]);
+    u32 mask = subc(0, 0);                                            // all ones when a < b
+    Fe<FID> o;
+    o.l[0] = add_cc(r[0], mask & modulus_limb<FID>(0));
+#pragma unroll
+    for (int i = 1; i < 8; ++i) o.l[i] = addc_cc(r[i], mask & modulus_limb<FID>(i));
+    return o;
+}
+
+template <int FID> DEV Fe<FID> fe_neg(const Fe<FID>& a) { return fe_sub<FID>(fe_zero<FID>(), a); }
+template <int FID> DEV Fe<FID> fe_dbl(const Fe<FID>& a) { return fe_add<FID>(a, a); }
+
+// acc[off..off+8) += (x0,x1,x2,x3) * b with the four 64-bit products on consecutive limb pairs;
+// the carry out is added into acc[off+8] when that limb exists.
+template <int OFF, int N>
+DEV void mad_row(u32 (&acc)[N], u32 x0, u32 x1, u32 x2, u32 x3, u32 b) {
+    acc[OFF + 0] = mad_lo_cc(x0, b, acc[OFF + 0]);
+    acc[OFF + 1] = madc_hi_cc(x0, b, acc[OFF + 1]);
+    acc[OFF + 2] = madc_lo_cc(x1, b, acc[OFF + 2]);
+    acc[OFF + 3] = madc_hi_cc(x1, b, acc[OFF + 3]);
+    acc[OFF + 4] = madc_lo_cc(x2, b, acc[OFF + 4]);
+    acc[OFF + 5] = madc_hi_cc(x2, b, acc[OFF + 5]);
+    acc[OFF + 6] = madc_lo_cc(x3, b, acc[OFF + 6]);
+    if (OFF + 8 < N) {
+        acc[OFF + 7] = madc_hi_cc(x3, b, acc[OFF + 7]);
+        acc[OFF + 8] = addc(acc[OFF + 8], 0);
+    } else {
+        acc[OFF + 7] = madc_hi(x3, b, acc[OFF + 7]);
+    }
+}
+
+// Montgomery reduction of a 16-limb value t < p*2^256; returns t / 2^256 mod p, fully reduced.
+// Column scan with a 64-bit accumulator: column j collects t[j] + m[j-1]*p1 + m[j-2]*p2 + m[j-3]*p3 (< 2^64
+// because p1+p2+p3 < 2^32); m[j] = -column (mod 2^32).  The 2^254 term of p contributes M >> 2 to the upper
+// half and (m[0] & 3) << 30 to column 7.
+template <int FID> DEV Fe<FID> mont_reduce(const u32 (&t)[16]) {
+    constexpr u32 P1 = FieldConst<FID>::P1, P2 = FieldConst<FID>::P2, P3 = FieldConst<FID>::P3;
+    u32 m[8];
+    u32 r[8];
+    u64 acc = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        acc += t[j];
+        if (j >= 1) acc += (u64)m[j - 1] * P1;
+        if (j >= 2) acc += (u64)m[j - 2] * P2;
+        if (j >= 3) acc += (u64)m[j - 3] * P3;
+        if (j == 7) acc += (u64)((m[0] & 3u) << 30);
+        m[j] = 0u - (u32)acc;
+        acc += m[j];            // p0 = 1: cancels the low word
+        acc >>= 32;
+    }
+#pragma unroll
+    for (int j = 8; j < 16; ++j) {
+        acc += t[j];
+        if (j - 1 <= 7) acc += (u64)m[j - 1] * P1;
+        if (j - 2 <= 7) acc += (u64)m[j - 2] * P2;
+        if (j - 3 <= 7) acc += (u64)m[j - 3] * P3;
+        r[j - 8] = (u32)acc;
+        acc >>= 32;
+    }
+    // + (M >> 2)
+    u32 s[8];
+#pragma unroll
+    for (int i = 0; i < 7; ++i) s[i] = (m[i] >> 2) | (m[i + 1] << 30);
+    s[7] = m[7] >> 2;
+    r[0] = add_cc(r[0], s[0]);
+#pragma unroll
+    for (int i = 1; i < 8; ++i) r[i] = addc_cc(r[i], s[i]);
+    // result < 2p < 2^256: one conditional subtraction
+    u32 d[8];
+    d[0] = sub_cc(r[0], modulus_limb<FID>(0));
+#pragma unroll
+    for (int i = 1; i < 8; ++i) d[i] = subc_cc(r[i], modulus_limb<FID>(i));
+    u32 borrow = subc(0, 0);
+    Fe<FID> o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.l[i] = borrow ? r[i] : d[i];
+    return o;
+}
+
+// 8x8 limb schoolbook product into even/odd-aligned accumulators so that every 64-bit partial product lands
+// on an aligned register pair (one IMAD.WIDE.U32.X each).  ev holds columns 0..15, od holds columns 1..15.
+template <int FID> DEV Fe<FID> fe_mul(const Fe<FID>& a, const Fe<FID>& b) {
+    u32 ev[16], od[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { ev[i] = 0; od[i] = 0; }
+    const u32 *x = a.l, *y = b.l;
+    // row 0
+    mad_row<0>(ev, x[0], x[2], x[4], x[6], y[0]);
+    mad_row<0>(od, x[1], x[3], x[5], x[7], y[0]);
+    // odd rows put a_even on od, a_odd on ev (shifted by 2); even rows the other way round
+    mad_row<0>(od, x[0], x[2], x[4], x[6], y[1]);
+    mad_row<2>(ev, x[1], x[3], x[5], x[7], y[1]);
+    mad_row<2>(ev, x[0], x[2], x[4], x[6], y[2]);
+    mad_row<2>(od, x[1], x[3], x[5], x[7], y[2]);
+    mad_row<2>(od, x[0], x[2], x[4], x[6], y[3]);
+    mad_row<4>(ev, x[1], x[3], x[5], x[7], y[3]);
+    mad_row<4>(ev, x[0], x[2], x[4], x[6], y[4]);
+    mad_row<4>(od, x[1], x[3], x[5], x[7], y[4]);
+    mad_row<4>(od, x[0], x[2], x[4], x[6], y[5]);
+    mad_row<6>(ev, x[1], x[3], x[5], x[7], y[5]);
+    mad_row<6>(ev, x[0], x[2], x[4], x[6], y[6]);
+    mad_row<6>(od, x[1], x[3], x[5], x[7], y[6]);
+    mad_row<6>(od, x[0], x[2], x[4], x[6], y[7]);
+    mad_row<8>(ev, x[1], x[3], x[5], x[7], y[7]);
+    // t = ev + (od << 32)
+    u32 t[16];
+    t[0] = ev[0];
+    t[1] = add_cc(ev[1], od[0]);
+#pragma unroll
+    for (int i = 2; i < 15; ++i) t[i] = addc_cc(ev[i], od[i - 1]);
+    t[15] = addc(ev[15], od[14]);
+    return mont_reduce<FID>(t);
+}
+
+template <int FID> DEV Fe<FID> fe_sqr(const Fe<FID>& a) { return fe_mul<FID>(a, a); }
+#endif  // HALO_PTX_PATH
+
+#if !defined(HALO_PTX_PATH)
+// ---------------------------------------------------------------------------------------------------------
+// plain host path (64-bit limbs): used by the host-side transcript / O(lg n) verifier work only
+// ---------------------------------------------------------------------------------------------------------
+namespace hostimpl {
+typedef unsigned __int128 u128;
+template <int FID> HD void modulus64(u64 p[4]) {
+    p[0] = ((u64)FieldConst<FID>::P1 << 32) | 1u;
+    p[1] = ((u64)FieldConst<FID>::P3 << 32) | FieldConst<FID>::P2;
+    p[2] = 0; p[3] = 0x4000000000000000ULL;
+}
+HD void load(u64 w[4], const u32* l) { for (int i = 0; i < 4; ++i) w[i] = (u64)l[2 * i] | ((u64)l[2 * i + 1] << 32); }
+HD void store(u32* l, const u64 w[4]) { for (int i = 0; i < 4; ++i) { l[2 * i] = (u32)w[i]; l[2 * i + 1] = (u32)(w[i] >> 32); } }
+HD bool geq(const u64 a[4], const u64 b[4]) { for (int i = 3; i >= 0; --i) if (a[i] != b[i]) return a[i] > b[i]; return true; }
+HD u64 add(u64 o[4], const u64 a[4], const u64 b[4]) { u128 c = 0; for (int i = 0; i < 4; ++i) { c += (u128)a[i] + b[i]; o[i] = (u64)c; c >>= 64; } return (u64)c; }
+HD u64 sub(u64 o[4], const u64 a[4], const u64 b[4]) { u64 br = 0; for (int i = 0; i < 4; ++i) { u128 d = (u128)a[i] - b[i] - br; o[i] = (u64)d; br = (u64)(d >> 64) & 1; } return br; }
+}  // namespace hostimpl
+
+template <int FID> HD Fe<FID> fe_add(const Fe<FID>& a, const Fe<FID>& b) {
+    using namespace hostimpl;
+    u64 x[4], y[4], p[4]; load(x, a.l); load(y, b.l); modulus64<FID>(p);
+    add(x, x, y); if (geq(x, p)) sub(x, x, p);
+    Fe<FID> o; store(o.l, x); return o;
+}
+template <int FID> HD Fe<FID> fe_sub(const Fe<FID>& a, const Fe<FID>& b) {
+    using namespace hostimpl;
+    u64 x[4], y[4], p[4]; load(x, a.l); load(y, b.l); modulus64<FID>(p);
+    if (sub(x, x, y)) add(x, x, p);
+    Fe<FID> o; store(o.l, x); return o;
+}
+template <int FID> HD Fe<FID> fe_neg(const Fe<FID>& a) { return fe_sub<FID>(fe_zero<FID>(), a); }
+template <int FID> HD Fe<FID> fe_dbl(const Fe<FID>& a) { return fe_add<FID>(a, a); }
+template <int FID> HD Fe<FID> fe_mul(const Fe<FID>& a, const Fe<FID>& b) {
+    using namespace hostimpl;
+    u64 x[4], y[4], p[4]; load(x, a.l); load(y, b.l); modulus64<FID>(p);
+    const u64 inv = (((u64)FieldConst<FID>::P1 - 1) << 32) | 0xffffffffULL;   // -p^{-1} mod 2^64
+    u64 t[6] = {0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < 4; ++i) {
+        u128 c = 0;
+        for (int j = 0; j < 4; ++j) { c += (u128)x[j] * y[i] + t[j]; t[j] = (u64)c; c >>= 64; }
+        c += t[4]; t[4] = (u64)c; t[5] = (u64)(c >> 64);
+        u64 m = t[0] * inv;
+        c = ((u128)m * p[0] + t[0]) >> 64;
+        for (int j = 1; j < 4; ++j) { c += (u128)m * p[j] + t[j]; t[j - 1] = (u64)c; c >>= 64; }
+        c += t[4]; t[3] = (u64)c; t[4] = t[5] + (u64)(c >> 64);
+    }
+    if (t[4] || geq(t, p)) sub(t, t, p);
+    Fe<FID> o; store(o.l, t); return o;
+}
+template <int FID> HD Fe<FID> fe_sqr(const Fe<FID>& a) { return fe_mul<FID>(a, a); }
+#endif  // !HALO_PTX_PATH
+
+// ---------------------------------------------------------------------------------------------------------
+// constants and derived operations (all paths)
+// ---------------------------------------------------------------------------------------------------------
+template <int FID> HD Fe<FID> fe_one() {       // R mod p
+    Fe<FID> r;
+    r.l[0] = 0xfffffffdu;
+    r.l[1] = FID == 0 ? 0x5b2b3e9cu : 0x34786d38u;
+    r.l[2] = FID == 0 ? 0xe3420567u : 0xe41914adu;
+    r.l[3] = 0x992c350bu;
+    r.l[4] = 0xffffffffu; r.l[5] = 0xffffffffu; r.l[6] = 0xffffffffu; r.l[7] = 0x3fffffffu;
+    return r;
+}
+template <int FID> HD Fe<FID> fe_r2() {        // R^2 mod p
+    Fe<FID> r;
+    if (FID == 0) {
+        r.l[0] = 0x0000000fu; r.l[1] = 0xfc9678ffu; r.l[2] = 0x891a16e3u; r.l[3] = 0x67bb433du;
+        r.l[4] = 0x04ccf590u; r.l[5] = 0x7fae2310u; r.l[6] = 0x7ccfdaa9u; r.l[7] = 0x096d41afu;
+    } else {
+        r.l[0] = 0x0000000fu; r.l[1] = 0x8c78ecb3u; r.l[2] = 0x8b0de0e7u; r.l[3] = 0xd7d30dbdu;
+        r.l[4] = 0xc3c95d18u; r.l[5] = 0x7797a99bu; r.l[6] = 0x7b9cb714u; r.l[7] = 0x096d41afu;
+    }
+    return r;
+}
+// canonical integer (8 x u32, < p) -> Montgomery
+template <int FID> HD Fe<FID> fe_from_canonical(const Fe<FID>& c) { return fe_mul<FID>(c, fe_r2<FID>()); }
+// Montgomery -> canonical integer
+template <int FID> HD Fe<FID> fe_to_canonical(const Fe<FID>& a) {
+    Fe<FID> one = fe_zero<FID>(); one.l[0] = 1;
+    return fe_mul<FID>(a, one);
+}
+template <int FID> HD Fe<FID> fe_from_u64(u64 x) {
+    Fe<FID> c = fe_zero<FID>(); c.l[0] = (u32)x; c.l[1] = (u32)(x >> 32);
+    return fe_from_canonical<FID>(c);
+}
+// a^e, e given as 8 x u32 little-endian
+template <int FID> HD Fe<FID> fe_pow(const Fe<FID>& a, const u32* e, int nbits = 256) {
+    Fe<FID> acc = fe_one<FID>();
+    for (int i = nbits - 1; i >= 0; --i) {
+        acc = fe_sqr<FID>(acc);
+        if ((e[i >> 5] >> (i & 31)) & 1) acc = fe_mul<FID>(acc, a);
+    }
+    return acc;
+}
+// Fermat inverse; 0 -> 0
+template <int FID> HD Fe<FID> fe_inv(const Fe<FID>& a) {
+    u32 e[8];
+    for (int i = 0; i < 8; ++i) e[i] = modulus_limb<FID>(i);
+    e[0] = 0xffffffffu; e[1] -= 1;            // p - 2  (p0 = 1 -> borrow from limb 1)
+    return fe_pow<FID>(a, e, 255);
+}
+
+}  // namespace halo

@@ -1,0 +1,73 @@
+// Process-wide runtime state of libhalo_b200: device binding, stream, resident generator sets (the device-side
+// analogue of the reference's per-curve OnceLock<PublicParams>, crates/group/src/wrappers.rs:28-29) and a
+// grow-only workspace arena so that steady-state calls do not allocate.
+#pragma once
+#include <cuda_runtime.h>
+#include <mutex>
+#include <string>
+#include <vector>
+#include <cstdio>
+#include "curve.cuh"
+#include "../../include/halo_b200.h"
+
+namespace halo {
+
+struct DeviceBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct ResidentParams {
+    void* d_gs = nullptr;      // n affine points, 64 B each
+    size_t n = 0;
+    uint64_t s_xy[8], h_xy[8]; // host copies (affine, Montgomery)
+};
+
+struct Runtime {
+    bool inited = false;
+    int device = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    int sm_count = 148;
+    ResidentParams pp[2];
+    std::vector<DeviceBuf> arena;   // indexed slots
+    void* pinned = nullptr;         // pinned host staging
+    size_t pinned_cap = 0;
+    int msm_window_override = 0;
+    std::recursive_mutex mu;
+    std::string err;
+};
+
+Runtime& rt();
+
+#define HALO_CUDA(call)                                                                        \
+    do {                                                                                       \
+        cudaError_t e__ = (call);                                                              \
+        if (e__ != cudaSuccess) {                                                              \
+            char buf__[512];                                                                   \
+            snprintf(buf__, sizeof buf__, "%s:%d: %s -> %s", __FILE__, __LINE__, #call,        \
+                     cudaGetErrorString(e__));                                                 \
+            halo::rt().err = buf__;                                                            \
+            return HALO_ECUDA;                                                                 \
+        }                                                                                      \
+    } while (0)
+
+#define HALO_CHECK(cond, code, msg)                 \
+    do {                                            \
+        if (!(cond)) {                              \
+            halo::rt().err = (msg);                 \
+            return (code);                          \
+        }                                           \
+    } while (0)
+
+// workspace slot: returns a device pointer with at least `bytes` capacity (contents undefined)
+int ws_get(int slot, size_t bytes, void** out);
+int pinned_get(size_t bytes, void** out);
+
+enum WsSlot {
+    WS_SCALARS = 0, WS_BASES, WS_COUNTS, WS_OFFSETS, WS_CURSOR, WS_IDX, WS_ORDER, WS_SIZEHIST, WS_BUCKETS,
+    WS_SEGSUM, WS_SEGWGT, WS_WINSUM, WS_TMP0, WS_TMP1, WS_TMP2, WS_TMP3, WS_IPA_G, WS_IPA_C, WS_IPA_Z, WS_IPA_T0,
+    WS_IPA_T1, WS_NTT0, WS_NTT1, WS_COUNT
+};
+
+}  // namespace halo

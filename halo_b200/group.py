@@ -1,0 +1,47 @@
+"""crates/group/src/group.rs:43-66 — point_dot_affine / point_dot on the GPU."""
+import ctypes
+
+import numpy as np
+
+from . import _lib
+from ._lib import lib, check, ptr, as_u64
+
+
+def point_dot_affine(curve, xs, Gs):
+    """≙ point_dot_affine (group.rs:48-50): MSM over min(len) pairs, no length check ("unchecked")."""
+    _lib.ensure_init()
+    xs, Gs = as_u64(xs, 4), as_u64(Gs, 8)
+    k = min(xs.shape[0], Gs.shape[0])
+    out = np.empty(12, dtype=np.uint64)
+    check(lib.halo_msm(curve, ptr(Gs), ctypes.c_size_t(0), ptr(xs), ctypes.c_size_t(k), ptr(out)))
+    return out
+
+
+def point_dot(curve, xs, Gs_proj):
+    """≙ point_dot (group.rs:53-56): projective bases."""
+    _lib.ensure_init()
+    xs, Gs = as_u64(xs, 4), as_u64(Gs_proj, 12)
+    k = min(xs.shape[0], Gs.shape[0])
+    out = np.empty(12, dtype=np.uint64)
+    check(lib.halo_msm_proj(curve, ptr(Gs), ptr(xs), ctypes.c_size_t(k), ptr(out)))
+    return out
+
+
+def msm_resident(curve, xs, base_off=0):
+    """MSM against the resident generators Gs[base_off : base_off+len(xs)]."""
+    _lib.ensure_init()
+    xs = as_u64(xs, 4)
+    out = np.empty(12, dtype=np.uint64)
+    check(lib.halo_msm(curve, None, ctypes.c_size_t(base_off), ptr(xs), ctypes.c_size_t(xs.shape[0]), ptr(out)))
+    return out
+
+
+def field_op(field, op, a, b=None):
+    """Elementwise field arithmetic on the GPU (test hook). op: mul add sub inv to_canonical from_canonical."""
+    _lib.ensure_init()
+    code = {"mul": 0, "add": 1, "sub": 2, "inv": 3, "to_canonical": 4, "from_canonical": 5}[op]
+    a = as_u64(a, 4)
+    b = as_u64(b, 4) if b is not None else None
+    out = np.empty_like(a)
+    check(lib.halo_field_op(field, code, ptr(a), ptr(b), ptr(out), ctypes.c_size_t(a.shape[0])))
+    return out

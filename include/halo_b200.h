@@ -1,0 +1,82 @@
+/* halo_b200 — C ABI of the B200-native MSM / IPA / NTT path for rasmus-kirk/halo.
+ *
+ * These are the symbols a `halo-b200-sys` Rust crate would bind (INTEGRATION.md shows the extern block and the
+ * call-site patches).  Conventions, all taken from the reference:
+ *   - field element  = 4 x u64 little-endian limbs, Montgomery form, R = 2^256, value < modulus
+ *                      (crates/group/src/wrappers.rs:603-616)
+ *   - affine point   = WrappedPoint {x:[u64;4], y:[u64;4]} (#[repr(C)], wrappers.rs:592-597); identity = (0,0)
+ *                      (wrappers.rs:91-93)
+ *   - projective pt  = Jacobian (X,Y,Z), 12 x u64, as ark_ec Projective (crates/plonk/src/frontend/ivc/mod.rs:40-45);
+ *                      identity has Z = 0.  Any representative of the group element may be returned.
+ *   - curve: 0 = Pallas, 1 = Vesta.   field: 0 = halo Fp (Pallas scalars), 1 = halo Fq (Vesta scalars)
+ *                      (crates/group/src/lib.rs:8-9).  A curve's scalars live in field == curve.
+ * Every function returns 0 on success or a negative HALO_E* code; nothing aborts.  Pointers are HOST pointers
+ * unless the name ends in _dev.  The library keeps no caller pointer after returning.  One process drives one GPU.
+ */
+#ifndef HALO_B200_H
+#define HALO_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HALO_OK 0
+#define HALO_EINVAL (-1)   /* bad argument (the reference would assert!/panic!) */
+#define HALO_ECUDA (-2)    /* CUDA runtime error; see halo_last_error() */
+#define HALO_ENOINIT (-3)  /* halo_init not called */
+#define HALO_EPARAMS (-4)  /* public parameters missing or too small (pp.rs:27-32, 63-82) */
+#define HALO_EREJECT (-5)  /* a verifier rejected (anyhow::ensure! sites: pcdl.rs:494,547-550,580; acc.rs:154,207-210) */
+
+/* ---- runtime ------------------------------------------------------------------------------------------ */
+/* Binds the library to CUDA device `device` of this process (-1 = current device) and creates its streams.
+ * Idempotent. */
+int halo_init(int device);
+int halo_shutdown(void);
+const char* halo_last_error(void);
+/* Use the caller's CUDA stream (cudaStream_t) for all subsequent work, so that the caller can bracket calls with
+ * its own events; NULL restores the library's stream. */
+int halo_set_stream(void* cuda_stream);
+int halo_device_synchronize(void);
+
+/* ---- public parameters  ≙ PublicParams::{new,set_pp,get_pp}  (crates/group/src/pp.rs:26-94) ------------- */
+/* Uploads n generators + S + H once per curve; idempotent and monotone like set_pp: a later call with a larger
+ * n than the resident set fails with HALO_EPARAMS, a smaller or equal one is a no-op.  Every point is checked to
+ * be on the curve (wrappers.rs:606); failure -> HALO_EINVAL. */
+int halo_pp_load(int curve, const uint64_t* gs_xy, size_t n, const uint64_t s_xy[8], const uint64_t h_xy[8]);
+/* number of resident generators (0 = none) */
+size_t halo_pp_len(int curve);
+/* drop the resident set (tests only; the reference's OnceLock cannot be reset) */
+int halo_pp_reset(int curve);
+
+/* ---- MSM  ≙ point_dot_affine / pedersen::commit / pcdl::commit  (group.rs:48-50, pedersen.rs:7-27, pcdl.rs:275) */
+/* out = sum_{i<k} scalars[i] * B[i];  B = bases_xy (k points) or, when bases_xy == NULL, resident Gs[base_off..]. */
+int halo_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_t* scalars, size_t k,
+             uint64_t out_xyz[12]);
+/* b independent MSMs over the same resident bases Gs[base_off .. base_off+k): scalars is b x k x 4 words.
+ * ≙ the 16 commits of a prover round (crates/plonk/src/plonk/protocol.rs:114,263). */
+int halo_msm_batch(int curve, size_t base_off, const uint64_t* scalars, size_t k, size_t b, uint64_t* out_xyz);
+/* projective bases  ≙ point_dot (group.rs:53-56): normalize_batch + MSM */
+int halo_msm_proj(int curve, const uint64_t* bases_xyz, const uint64_t* scalars, size_t k, uint64_t out_xyz[12]);
+/* same as halo_msm with inputs already in device memory (d_bases may be NULL for resident Gs) */
+int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k,
+                 uint64_t out_xyz[12]);
+/* window width override for experiments (0 = automatic) */
+int halo_msm_set_window(int c);
+
+/* ---- benchmarks of the arithmetic itself (denominator of the integer roofline) -------------------------- */
+/* Runs `iters` dependent Montgomery multiplications in each of blocks*threads threads (4 independent chains per
+ * thread); returns elapsed milliseconds measured with CUDA events in *ms and a checksum in out[4]. */
+int halo_bench_modmul(int field, int blocks, int threads, int iters, float* ms, uint64_t out[4]);
+/* raw IMAD.WIDE.U32 issue rate: `iters` x 8 independent wide multiply-adds per thread */
+int halo_bench_imad(int blocks, int threads, int iters, float* ms, uint64_t* out);
+
+/* ---- elementwise helpers used by tests -------------------------------------------------------------------- */
+/* op: 0 mul, 1 add, 2 sub, 3 inverse(a), 4 to_canonical(a), 5 from_canonical(a); n elements, on the GPU */
+int halo_field_op(int field, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HALO_B200_H */

@@ -1,0 +1,157 @@
+"""GPU parity of the field arithmetic and the MSM path against the CPU oracle, through the C ABI.
+Mirrors what the reference's tests check for this path (pedersen.rs:68 homomorphism, pp.rs:126 on-curve params)
+plus bit-exact known answers from the oracle and the golden commitment of ivc/mod.rs:197."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def hb():
+    import halo_b200
+    halo_b200.init()
+    return halo_b200
+
+
+def _aff(O, curve, xyz):
+    return O.point_to_affine(curve, np.asarray(xyz, dtype=np.uint64).reshape(-1, 12))
+
+
+@pytest.mark.parametrize("field", [0, 1])
+def test_field_ops_bit_exact(hb, oracle, field):
+    O = oracle
+    p = O.MODULUS[field]
+    n = 20000
+    a, b = O.random_scalars(field, n, 5), O.random_scalars(field, n, 6)
+    edge = O.ints_to_mont(field, [0, 1, p - 1, p - 2, 2, (1 << 254) - 1, 1 << 32, (1 << 32) - 1, p >> 1])
+    a[: len(edge)] = edge
+    b[3: 3 + len(edge)] = edge
+    assert (hb.group.field_op(field, "mul", a, b) == O.field_mul(field, a, b)).all()
+    assert (hb.group.field_op(field, "add", a, b) == O.field_add(field, a, b)).all()
+    assert (hb.group.field_op(field, "sub", a, b) == O.field_sub(field, a, b)).all()
+    assert (hb.group.field_op(field, "inv", a[:200]) == O.field_inv(field, a[:200])).all()
+    c = hb.group.field_op(field, "to_canonical", a)
+    assert (c == O.field_to_canonical(field, a)).all()
+    assert (hb.group.field_op(field, "from_canonical", c) == a).all()
+
+
+@pytest.mark.parametrize("curve", [0, 1])
+@pytest.mark.parametrize("k", [0, 1, 2, 3, 7, 33, 100, 1 << 8, 1000, 1 << 12, (1 << 14) + 5, 1 << 16])
+def test_msm_random_points(hb, oracle, curve, k):
+    O = oracle
+    sf = O.SCALAR_FIELD[curve]
+    pts = O.points_arith(curve, max(k, 1))[:k]
+    sc = O.random_scalars(sf, max(k, 1), 1000 + k)[:k]
+    got = hb.group.point_dot_affine(curve, sc, pts)
+    exp = O.msm(curve, pts, sc) if k else O.affine_to_jac(curve, np.zeros(8, dtype=np.uint64))[0]
+    assert (_aff(O, curve, got) == _aff(O, curve, exp)).all()
+
+
+@pytest.mark.parametrize("curve", [0, 1])
+def test_msm_edge_scalars_and_identity_bases(hb, oracle, curve):
+    O = oracle
+    sf = O.SCALAR_FIELD[curve]
+    k = 5000
+    pts = O.points_arith(curve, k).copy()
+    pts[17] = 0            # identity base
+    pts[18] = pts[19]      # duplicate base
+    pts[21] = pts[20]; pts[21, 4:8] = O.field_sub(O.BASE_FIELD[curve], np.zeros(4, dtype=np.uint64), pts[20, 4:8])[0]  # -P
+    sc = O.edge_scalars(sf, k, 99)
+    sc[20] = sc[21]        # s*P + s*(-P)
+    got = hb.group.point_dot_affine(curve, sc, pts)
+    assert (_aff(O, curve, got) == _aff(O, curve, O.msm(curve, pts, sc))).all()
+    # all-zero scalars -> identity
+    z = hb.group.point_dot_affine(curve, np.zeros((64, 4), dtype=np.uint64), pts[:64])
+    assert not _aff(O, curve, z).any()
+    # unchecked semantics: min(len) pairs
+    got = hb.group.point_dot_affine(curve, sc[:100], pts[:60])
+    assert (_aff(O, curve, got) == _aff(O, curve, O.msm(curve, pts[:60], sc[:60]))).all()
+
+
+@pytest.mark.parametrize("c", [4, 7, 11, 13, 16])
+def test_msm_every_window_width(hb, oracle, c):
+    import ctypes
+    O = oracle
+    k = 3000
+    pts, sc = O.points_arith(0, k), O.random_scalars(0, k, c)
+    hb._lib.lib.halo_msm_set_window(ctypes.c_int(c))
+    try:
+        got = hb.group.point_dot_affine(0, sc, pts)
+    finally:
+        hb._lib.lib.halo_msm_set_window(ctypes.c_int(0))
+    assert (_aff(O, 0, got) == _aff(O, 0, O.msm(0, pts, sc))).all()
+
+
+@pytest.mark.parametrize("curve,name", [(0, "pallas"), (1, "vesta")])
+def test_resident_generators_commit_and_golden_C(hb, oracle, golden_dir, curve, name):
+    """pcdl::commit path on the reference's real (duplicate-heavy) generators; reproduces the golden
+    acc_0.q.C = commit(h_0) of crates/plonk/src/frontend/ivc/mod.rs:197,246."""
+    O = oracle
+    G = json.load(open(os.path.join(golden_dir, "ivc_genesis.json")))[name]
+    n = G["n"]
+    gs, S, H = O.pp_generate(curve, n)
+    hb.pp.reset(curve)
+    hb.pp.set_pp(curve, gs, S, H)
+    assert hb.pp.pp_len(curve) == n
+    with pytest.raises(hb.ParamsError):
+        hb.pp.set_pp(curve, np.concatenate([gs, gs]), S, H)      # monotone like set_pp (pp.rs:63-82)
+    hb.pp.set_pp(curve, gs[:1024], S, H)                         # smaller: no-op
+    sf = O.SCALAR_FIELD[curve]
+    sc = O.random_scalars(sf, n, 31337)
+    got = hb.pedersen.commit(curve, None, (0, n), sc)
+    assert (_aff(O, curve, got) == _aff(O, curve, O.msm(curve, gs, sc))).all()
+    # hiding commit: w*S + MSM
+    w = O.random_scalars(sf, 1, 7)[0]
+    O.pp_set(curve, gs, S, H)
+    got = hb.pedersen.commit(curve, w, (0, 4096), sc[:4096])
+    assert (_aff(O, curve, got) == _aff(O, curve, O.pcdl_commit(curve, sc[:4096], 4095, w))).all()
+    # golden: h_0 from the zero instance's transcript, C = commit(h_0)
+    q = O.instance_open(curve, np.zeros((0, 4), dtype=np.uint64), n - 1, np.zeros(4, dtype=np.uint64))
+    ok, xis, _ = O.pcdl_succinct_check(curve, q)
+    assert ok
+    h = O.hpoly_coeffs(sf, xis)
+    got = hb.pedersen.commit(curve, None, (0, n), h)
+    assert (_aff(O, curve, got) == _aff(O, curve, np.array(G["C"], dtype=np.uint64).reshape(12))).all()
+    with pytest.raises(hb.PreconditionError):
+        hb.pedersen.commit(curve, None, (0, 16), sc[:17])
+    hb.pp.reset(curve)
+
+
+def test_pp_rejects_off_curve_point(hb, oracle):
+    gs, S, H = oracle.pp_generate(0, 64)
+    bad = gs.copy(); bad[5, 0] ^= np.uint64(1)
+    hb.pp.reset(0)
+    with pytest.raises(hb.PreconditionError):
+        hb.pp.set_pp(0, bad, S, H)
+    assert hb.pp.pp_len(0) == 0
+
+
+def test_pedersen_homomorphism(hb, oracle):
+    """pedersen.rs:68 test_homomorphism_property."""
+    O = oracle
+    gs, S, H = O.pp_generate(0, 64)
+    hb.pp.reset(0); hb.pp.set_pp(0, gs, S, H)
+    m1, m2 = O.random_scalars(0, 2, 1), O.random_scalars(0, 2, 2)
+    w1, w2 = O.random_scalars(0, 1, 3)[0], O.random_scalars(0, 1, 4)[0]
+    inner = hb.pedersen.commit(0, O.field_add(0, w1, w2)[0], (0, 2), O.field_add(0, m1, m2))
+    outer = O.point_add(0, hb.pedersen.commit(0, w1, (0, 2), m1), hb.pedersen.commit(0, w2, (0, 2), m2))
+    assert (_aff(O, 0, inner) == _aff(O, 0, outer)).all()
+    hb.pp.reset(0)
+
+
+@pytest.mark.parametrize("k", [1 << 18, 1 << 20])
+def test_msm_large_bit_exact(hb, oracle, k):
+    O = oracle
+    pts = O.points_arith(0, k)
+    sc = O.random_scalars(0, k, k)
+    got = hb.group.point_dot_affine(0, sc, pts)
+    assert (_aff(O, 0, got) == _aff(O, 0, O.msm(0, pts, sc))).all()
+    # linearity at full size: MSM(a) + MSM(b) == MSM(a+b)
+    sc2 = O.random_scalars(0, k, k + 1)
+    got2 = hb.group.point_dot_affine(0, sc2, pts)
+    got3 = hb.group.point_dot_affine(0, O.field_add(0, sc, sc2), pts)
+    assert (_aff(O, 0, got3) == _aff(O, 0, O.point_add(0, got, got2))).all()

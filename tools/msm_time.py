@@ -1,0 +1,30 @@
+"""Quick MSM timing sweep on the GPU (inputs resident in HBM)."""
+import ctypes, sys, os, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+import numpy as np, torch
+import halo_b200
+from halo_b200._lib import lib, check
+import oracle_lib as O
+halo_b200.init()
+O.set_threads(os.cpu_count())
+lgs = [int(x) for x in sys.argv[1:]] or [12, 16, 18, 20]
+kmax = 1 << max(lgs)
+t = time.time(); pts = O.points_arith(0, kmax); print("points", time.time() - t, flush=True)
+sc = O.random_scalars(0, kmax, 1)
+d_pts = torch.from_numpy(pts.view(np.int64)).cuda()
+d_sc = torch.from_numpy(sc.view(np.int64)).cuda()
+s = torch.cuda.current_stream()
+check(lib.halo_set_stream(ctypes.c_void_p(s.cuda_stream)))
+out = np.empty(12, dtype=np.uint64)
+for lg in lgs:
+    k = 1 << lg
+    for c in ([0] if len(sys.argv) > 1 and False else [0]):
+        ts = []
+        for it in range(6):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(s)
+            check(lib.halo_msm_dev(0, ctypes.c_void_p(d_pts.data_ptr()), ctypes.c_size_t(0), ctypes.c_void_p(d_sc.data_ptr()), ctypes.c_size_t(k), out.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64))))
+            e1.record(s); e1.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        print(f"k=2^{lg} ms: " + " ".join(f"{x:.3f}" for x in ts) + f"  -> {k / (min(ts) * 1e-3):.3e} pts/s", flush=True)
