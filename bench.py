@@ -1,0 +1,389 @@
+#!/usr/bin/env python3
+"""bench.py — Pallas variable-base MSM throughput (BASELINE.json metric, config 2: random points/scalars).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--log-n 20] [--impl reference]
+
+One "step" = one MSM over 2^log_n (default 2^20) synthetic points per GPU through libhalo_b200's C ABI.
+  value  : points/s with bases and scalars already resident in HBM (halo_msm_dev), CUDA events, max over ranks
+  e2e    : the same MSM through halo_msm with HOST (pinned) bases and scalars: H2D copies, kernels, D2H of the
+           window sums and the host-side combine are all inside the timed region
+  N > 1  : weak scaling — every rank owns a 2^log_n point range of one N*2^log_n MSM; the N partial sums
+           (one Jacobian point each) are all-gathered with NCCL and added, inside the timed region
+  --impl reference : the CPU restatement of the reference's path (oracle/, arkworks itself cannot be built
+           here: no Rust toolchain) timed on the host cores, same workload / metric / unit.
+The own arm never touches oracle/ except in the clearly separated cpu_baseline leg (rank 0, N = 1).
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "pallas_msm_points_per_s"
+UNIT = "points/s"
+PALLAS = 0
+# Pallas base field (halo Fq) and scalar field (halo Fp) moduli — crates/group/src/wrappers.rs:516-517,577-578
+P_BASE = 0x40000000000000000000000000000000224698fc094cf91b992d30ed00000001
+Q_SCALAR = 0x40000000000000000000000000000000224698fc0994a8dd8c46eb2100000001
+# XYZZ mixed addition = 8M + 2S (halo_b200/csrc/curve.cuh xyzz_madd); one per (point, window)
+MODMUL_PER_MADD = 10
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--log-n", type=int, default=20)
+    ap.add_argument("--impl", default="halo_b200", choices=["halo_b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled every 200 ms during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = max(mx, float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for nm, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        # "under load": samples in the upper half (idle samples before/after the region sit at the idle clock)
+        load = sm[len(sm) // 2:] if sm else []
+        return {"sm_mhz": load[len(load) // 2] if load else None, "sm_max_mhz": mx or None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# host-side helpers (python ints; verification only, outside every timed region)
+# ---------------------------------------------------------------------------------------------------------
+def limbs_to_int(a):
+    return sum(int(x) << (64 * i) for i, x in enumerate(a))
+
+
+def int_to_limbs(x):
+    import numpy as np
+    return np.array([(x >> (64 * i)) & 0xFFFFFFFFFFFFFFFF for i in range(4)], dtype=np.uint64)
+
+
+def jac_equal(a_xyz, b_xyz):
+    """Group equality of two Jacobian points given as 12 Montgomery limbs each (Montgomery factors cancel)."""
+    X1, Y1, Z1 = (limbs_to_int(a_xyz[4 * i:4 * i + 4]) for i in range(3))
+    X2, Y2, Z2 = (limbs_to_int(b_xyz[4 * i:4 * i + 4]) for i in range(3))
+    if Z1 == 0 or Z2 == 0:
+        return Z1 == Z2
+    p = P_BASE
+    return (X1 * Z2 * Z2 - X2 * Z1 * Z1) % p == 0 and (Y1 * Z2 ** 3 - Y2 * Z1 ** 3) % p == 0
+
+
+def gen_multipliers(seed, first, n):
+    """numpy mirror of halo_gen_point_multiplier (halo_b200/csrc/capi.cu splitmix64)."""
+    import numpy as np
+    with np.errstate(over="ignore"):
+        x = np.uint64(seed) + (np.uint64(first) + np.arange(n, dtype=np.uint64)) * np.uint64(0x2545F4914F6CDD1D)
+        x = x + np.uint64(0x9E3779B97F4A7C15)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        x = x ^ (x >> np.uint64(31))
+    return x | np.uint64(1)
+
+
+def expected_scalar(scalars_mont, seed, first):
+    """sum_i s_i * m_i mod q for P_i = m_i * G (halo_gen_points); scalars arrive in Montgomery form.  Returns the
+    canonical integer t with  MSM == t * G."""
+    s = scalars_mont.astype(object)
+    vals = s[:, 0] + (s[:, 1] << 64) + (s[:, 2] << 128) + (s[:, 3] << 192)
+    m = gen_multipliers(seed, first, scalars_mont.shape[0]).astype(object)
+    acc = int((vals * m).sum())
+    return (acc % Q_SCALAR) * pow(1 << 256, -1, Q_SCALAR) % Q_SCALAR
+
+
+def cpu_msm_leg(log_n, reps):
+    """Times the CPU restatement (oracle/msm.hpp, all host threads) on a 2^log_n Pallas MSM.  The ONLY place
+    bench.py executes anything under oracle/."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    cores = os.cpu_count() or 1
+    O.set_threads(cores)
+    k = 1 << log_n
+    pts = O.points_arith(PALLAS, k)
+    sc = O.random_scalars(O.SCALAR_FIELD[PALLAS], k, 20)
+    times = []
+    for _ in range(reps):
+        t = time.perf_counter()
+        O.msm(PALLAS, pts, sc)
+        times.append(time.perf_counter() - t)
+    return k, cores, times
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    # bounded sample: the full 2^20 MSM is ~10-20 s of single-core work, a few seconds on all cores
+    log_n = min(args.log_n, 20)
+    k, cores, times = cpu_msm_leg(log_n, args.warmup + args.steps)
+    timed = times[args.warmup:]
+    total = sum(timed)
+    v = k * len(timed) / total
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / len(timed), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u32x8-montgomery", "data": "synthetic",
+        "config": {"workload": f"pallas_msm_2^{log_n}_random_points", "log_n": log_n,
+                   "note": "CPU restatement of the reference path (oracle/), not arkworks: no Rust toolchain on this box"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{len(timed)} x MSM of 2^{log_n} points, all host threads"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def run_halo(args, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import halo_b200
+    from halo_b200._lib import lib, check
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — halo_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    halo_b200.init(local_rank)
+    stream = torch.cuda.current_stream()
+    check(lib.halo_set_stream(ctypes.c_void_p(stream.cuda_stream)))
+    lib.halo_launch_count.restype = ctypes.c_ulonglong
+    u64p = ctypes.POINTER(ctypes.c_uint64)
+
+    k = 1 << args.log_n
+    seed, first = 0x48414C4F, rank * k
+    # ---- synthetic inputs: distinct points P_i = m_i*G generated on the device, uniform scalars (any 254-bit
+    # value is a valid Montgomery representative of a uniformly distributed field element)
+    d_pts = torch.empty((k, 8), dtype=torch.int64, device="cuda")
+    check(lib.halo_gen_points_dev(PALLAS, ctypes.c_uint64(seed), ctypes.c_size_t(first), ctypes.c_size_t(k),
+                                  ctypes.c_void_p(d_pts.data_ptr())))
+    g = torch.Generator(device="cuda"); g.manual_seed(1234 + rank)
+    d_sc = torch.randint(-(1 << 63), (1 << 63) - 1, (k, 4), dtype=torch.int64, device="cuda", generator=g)
+    d_sc[:, 3] &= (1 << 62) - 1
+    h_pts = d_pts.cpu().pin_memory()
+    h_sc = d_sc.cpu().pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # 256 MiB > 126 MB L2
+    out = np.zeros(12, dtype=np.uint64)
+    d_part = torch.zeros(12, dtype=torch.int64, device="cuda")
+    gathered = torch.zeros((world, 12), dtype=torch.int64, device="cuda") if world > 1 else None
+
+    # Montgomery one of the scalar field, for summing the gathered partials with halo_msm_proj
+    one_m = int_to_limbs((1 << 256) % Q_SCALAR)
+    ones = np.tile(one_m, (world, 1)).copy()
+    total = np.zeros(12, dtype=np.uint64)
+
+    def step_dev():
+        check(lib.halo_msm_dev(PALLAS, ctypes.c_void_p(d_pts.data_ptr()), ctypes.c_size_t(0),
+                               ctypes.c_void_p(d_sc.data_ptr()), ctypes.c_size_t(k), out.ctypes.data_as(u64p)))
+        combine()
+
+    def step_e2e():
+        check(lib.halo_msm(PALLAS, ctypes.cast(h_pts.data_ptr(), u64p), ctypes.c_size_t(0),
+                           ctypes.cast(h_sc.data_ptr(), u64p), ctypes.c_size_t(k), out.ctypes.data_as(u64p)))
+        combine()
+
+    def combine():
+        # the real exchange step of a point-range-sharded MSM: one Jacobian point per rank over NCCL, then N adds
+        if world == 1:
+            total[:] = out
+            return
+        d_part.copy_(torch.from_numpy(out.view(np.int64)))
+        dist.all_gather_into_tensor(gathered, d_part)
+        parts = gathered.cpu().numpy().view(np.uint64).copy()
+        check(lib.halo_msm_proj(PALLAS, parts.ctypes.data_as(u64p), ones.ctypes.data_as(u64p),
+                                ctypes.c_size_t(world), total.ctypes.data_as(u64p)))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, collect_profile=False):
+        """K steps, each bracketed by CUDA events on the launching stream with an L2 flush in between (outside the
+        events); returns total ms (max over ranks) and per-stage sums."""
+        stage_ms = {}
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        ms_buf = (ctypes.c_float * 24)()
+        nm_buf = (ctypes.c_char_p * 24)()
+        barrier()
+        for i in range(steps):
+            flush.zero_()
+            ev[i][0].record(stream)
+            fn()
+            ev[i][1].record(stream)
+            if collect_profile:
+                n = lib.halo_profile_read(ms_buf, nm_buf, 24)
+                for j in range(max(n, 0)):
+                    nm = nm_buf[j].decode()
+                    stage_ms[nm] = stage_ms.get(nm, 0.0) + ms_buf[j]
+        barrier()
+        tot = sum(a.elapsed_time(b) for a, b in ev)
+        if dist is not None:
+            t = torch.tensor([tot], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            tot = float(t.item())
+        return tot, stage_ms
+
+    # ---- measured integer-pipe peak: dependent Montgomery multiplications, 4 chains/thread (capi.cu) ----
+    ms = ctypes.c_float()
+    chk = (ctypes.c_uint64 * 4)()
+    peak_modmul = 0.0
+    for threads, bps in ((256, 4), (512, 2)):
+        check(lib.halo_bench_modmul(1, 148 * bps, threads, 400, ctypes.byref(ms), chk))
+        peak_modmul = max(peak_modmul, 148 * bps * threads * 400 * 4 / (ms.value * 1e-3))
+
+    # ---- device-resident arm ----
+    for _ in range(max(args.warmup, 3)):
+        step_dev()
+    check(lib.halo_profile_enable(1))
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    l0 = lib.halo_launch_count()
+    tot_ms, stage_ms = timed(step_dev, args.steps, collect_profile=True)
+    launches = lib.halo_launch_count() - l0
+    check(lib.halo_profile_enable(0))
+    result_dev = total.copy()
+
+    # ---- end-to-end arm (host buffers) ----
+    for _ in range(2):
+        step_e2e()
+    e2e_ms, _ = timed(step_e2e, args.steps)
+    clocks = sampler.stop() if sampler else None
+    result_e2e = total.copy()
+
+    # ---- verification against the known discrete logs (outside the timed regions) ----
+    t_loc = expected_scalar(d_sc.cpu().numpy().view(np.uint64), seed, first)
+    if dist is not None:
+        parts = [None] * world
+        dist.all_gather_object(parts, t_loc)
+        t_all = sum(parts) % Q_SCALAR
+    else:
+        t_all = t_loc
+    verified = None
+    if rank == 0:
+        exp = np.zeros(12, dtype=np.uint64)
+        gen = np.zeros((1, 8), dtype=np.uint64)
+        check(lib.halo_gen_points(PALLAS, ctypes.c_uint64(0), ctypes.c_size_t(0), ctypes.c_size_t(1),
+                                  gen.ctypes.data_as(u64p)))
+        m0 = int(gen_multipliers(0, 0, 1)[0])
+        # gen[0] = m0 * G  =>  t*G = (t / m0) * gen[0]
+        t_adj = t_all * pow(m0, -1, Q_SCALAR) % Q_SCALAR
+        sc1 = int_to_limbs(t_adj * (1 << 256) % Q_SCALAR).reshape(1, 4)
+        check(lib.halo_msm(PALLAS, gen.ctypes.data_as(u64p), ctypes.c_size_t(0), sc1.ctypes.data_as(u64p),
+                           ctypes.c_size_t(1), exp.ctypes.data_as(u64p)))
+        verified = bool(jac_equal(result_dev, exp) and jac_equal(result_e2e, exp))
+        if not verified:
+            raise SystemExit("bench.py: MSM result does not match the known discrete-log check")
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    n_pts = k * world
+    value = n_pts * args.steps / (tot_ms * 1e-3)
+    e2e_value = n_pts * args.steps / (e2e_ms * 1e-3)
+    acc_ms = stage_ms.get("accumulate", 0.0) / args.steps
+    c = min(16, max(4, args.log_n - 4)); nw = 255 // c + 1          # msm.cu pick_window / make_plan
+    roof = None
+    if acc_ms > 0:
+        # dominant kernel: bucket accumulation.  Algorithmic work per launch: one mixed addition (10 modmul) per
+        # (point, window); algorithmic bytes per launch: 4 B index + 64 B base per (point, window) + bucket writes
+        modmul = MODMUL_PER_MADD * k * nw
+        abytes = k * nw * (4 + 64) + (nw << (c - 1)) * 128
+        ach = modmul / (acc_ms * 1e-3)
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        roof = {"kernel": "msm_accumulate", "bound": "int32-pipe", "achieved": ach / 1e9, "peak": peak_modmul / 1e9,
+                "unit": "Gmodmul/s", "frac": ach / peak_modmul, "traffic": None,
+                "peak_source": "measured live: halo_bench_modmul (dependent 255-bit Montgomery multiplications)",
+                "ms_per_launch": acc_ms, "share_of_step": acc_ms / (tot_ms / args.steps),
+                "hbm": {"bound": "hbm", "achieved": abytes / (acc_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": abytes / (acc_ms * 1e-3) / 1e9 / hbm_peak,
+                        "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+                "stages_ms": {kk: v / args.steps for kk, v in stage_ms.items()}}
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        kk, cores, times = cpu_msm_leg(min(args.log_n, 20), 2)
+        cpu = {"value": kk / min(times), "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"best of 2 x MSM of 2^{min(args.log_n, 20)} points, CPU restatement (oracle/msm.hpp), all host threads"}
+
+    print(json.dumps({
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u32x8-montgomery", "data": "synthetic",
+        "config": {"workload": f"pallas_msm_2^{args.log_n}_random_points", "log_n": args.log_n, "points_per_gpu": k,
+                   "sharding": "point-range, NCCL all-gather of partial sums" if world > 1 else "single GPU",
+                   "l2": "flushed between timed iterations (256 MiB memset outside the event pair)"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(k * 96), "d2h_bytes_per_step": int(nw * 128),
+                "ms_per_step": e2e_ms / args.steps},
+        "gpu_launches": int(launches), "verified": verified, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+    }))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world == 1 and args.gpus > 1:
+        # launched without torchrun: re-launch one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    run_halo(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -32,7 +32,48 @@ int pinned_get(size_t bytes, void** out) {
     return HALO_OK;
 }
 
+int prof_begin() {
+    Runtime& R = rt();
+    R.prof_n = 0;
+    if (!R.prof_on) return HALO_OK;
+    if (!R.prof_ev[0]) for (int i = 0; i <= Runtime::PROF_MAX; ++i) HALO_CUDA(cudaEventCreate(&R.prof_ev[i]));
+    HALO_CUDA(cudaEventRecord(R.prof_ev[0], R.stream));
+    return HALO_OK;
+}
+int prof_mark(const char* name) {
+    Runtime& R = rt();
+    if (!R.prof_on || R.prof_n >= Runtime::PROF_MAX) return HALO_OK;
+    R.prof_name[R.prof_n] = name;
+    HALO_CUDA(cudaEventRecord(R.prof_ev[++R.prof_n], R.stream));
+    return HALO_OK;
+}
+
 template <int C> int msm_device(const void* d_bases, const void* d_scalars, size_t k, uint64_t out_xyz[12]);
+
+// ---- synthetic inputs: P_i = k_i * G with k_i = splitmix64(seed, i) | 1  (distinct with overwhelming probability) ----
+__host__ __device__ inline u64 splitmix64(u64 x) {
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+template <int C>
+__global__ void __launch_bounds__(128) gen_points_kernel(u64 seed, size_t first, size_t n, Affine<C>* out) {
+    constexpr int B = CurveTraits<C>::BASE;
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    u64 k = splitmix64(seed + (first + i) * 0x2545F4914F6CDD1DULL) | 1ULL;
+    // both Pasta curves use the generator (-1, 2)
+    Affine<C> G;
+    G.x = fe_neg<B>(fe_one<B>());
+    G.y = fe_dbl<B>(fe_one<B>());
+    XYZZ<C> acc = xyzz_identity<C>();
+    for (int b = 63; b >= 0; --b) {
+        acc = xyzz_dbl<C>(acc);
+        if ((k >> b) & 1) xyzz_madd<C>(acc, G, false);
+    }
+    out[i] = xyzz_to_affine<C>(acc);
+}
 
 // ---- on-curve check for uploaded parameters (wrappers.rs:606 asserts per point) ----
 template <int C>
@@ -225,6 +266,44 @@ int halo_pp_reset(int curve) {
     HALO_CUDA(cudaStreamSynchronize(R.stream));
     if (R.pp[curve].d_gs) cudaFree(R.pp[curve].d_gs);
     R.pp[curve] = ResidentParams();
+    return HALO_OK;
+}
+
+int halo_profile_enable(int on) { LOCK(); rt().prof_on = on != 0; rt().prof_n = 0; return HALO_OK; }
+int halo_profile_read(float* ms, const char** names, int max_stages) {
+    LOCK(); NEED_INIT();
+    Runtime& R = rt();
+    int n = R.prof_n < max_stages ? R.prof_n : max_stages;
+    if (n > 0) HALO_CUDA(cudaEventSynchronize(R.prof_ev[R.prof_n]));
+    for (int i = 0; i < n; ++i) {
+        HALO_CUDA(cudaEventElapsedTime(&ms[i], R.prof_ev[i], R.prof_ev[i + 1]));
+        if (names) names[i] = R.prof_name[i];
+    }
+    return n;
+}
+unsigned long long halo_launch_count(void) { return rt().launches; }
+
+uint64_t halo_gen_point_multiplier(uint64_t seed, uint64_t i) { return splitmix64(seed + i * 0x2545F4914F6CDD1DULL) | 1ULL; }
+int halo_gen_points_dev(int curve, uint64_t seed, size_t first, size_t n, void* d_out_xy) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK((curve == 0 || curve == 1) && (d_out_xy || n == 0), HALO_EINVAL, "gen_points: bad argument");
+    if (n == 0) return HALO_OK;
+    Runtime& R = rt();
+    unsigned grid = (unsigned)((n + 127) / 128);
+    if (curve == 0) gen_points_kernel<0><<<grid, 128, 0, R.stream>>>(seed, first, n, (Affine<0>*)d_out_xy);
+    else gen_points_kernel<1><<<grid, 128, 0, R.stream>>>(seed, first, n, (Affine<1>*)d_out_xy);
+    HALO_CUDA(cudaGetLastError());
+    return HALO_OK;
+}
+int halo_gen_points(int curve, uint64_t seed, size_t first, size_t n, uint64_t* out_xy) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK(out_xy || n == 0, HALO_EINVAL, "gen_points: null output");
+    if (n == 0) return HALO_OK;
+    void* d;
+    if (int e = ws_get(WS_BASES, n * 64, &d)) return e;
+    if (int e = halo_gen_points_dev(curve, seed, first, n, d)) return e;
+    HALO_CUDA(cudaMemcpyAsync(out_xy, d, n * 64, cudaMemcpyDeviceToHost, rt().stream));
+    HALO_CUDA(cudaStreamSynchronize(rt().stream));
     return HALO_OK;
 }
 

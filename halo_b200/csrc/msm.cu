@@ -309,23 +309,32 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     if (int e = ws_get(WS_SEGSUM, P.nseg_total * sizeof(XYZZ<C>), (void**)&segsum)) return e;
     if (int e = ws_get(WS_SEGWGT, P.nseg_total * sizeof(XYZZ<C>), (void**)&segwgt)) return e;
     if (int e = ws_get(WS_WINSUM, (size_t)P.nwin * sizeof(XYZZ<C>), (void**)&winsum)) return e;
+    if (int e = prof_begin()) return e;
     HALO_CUDA(cudaMemsetAsync(counts, 0, zero_words * 4, st));
 
     int grid_pts = (int)std::min<size_t>((k + 255) / 256, (size_t)R.sm_count * 8);
     int grid_b = (int)std::min<size_t>((P.nb + 255) / 256, (size_t)R.sm_count * 8);
     msm_count<SF><<<grid_pts, 256, 0, st>>>(d_scalars, k, P.c, P.nwin, counts);
+    prof_mark("count");
     msm_scan<<<1, 1024, 0, st>>>(counts, offsets, P.nb);
+    prof_mark("scan");
     msm_scatter<SF><<<grid_pts, 256, 0, st>>>(d_scalars, k, P.c, P.nwin, offsets, cursor, idx);
+    prof_mark("scatter");
     msm_size_hist<<<grid_b, 256, 0, st>>>(counts, P.nb, sizehist);
     msm_scan<<<1, 1024, 0, st>>>(sizehist, sizehist + 1024, 1024);
     msm_size_scatter<<<grid_b, 256, 0, st>>>(counts, P.nb, sizehist + 1024, sizehist + 2048, order);
+    prof_mark("order");
     msm_accumulate<C><<<(unsigned)((P.nb + 127) / 128), 128, 0, st>>>(d_bases, idx, offsets, counts, order, P.nb, buckets);
+    prof_mark("accumulate");
+    R.launches += 8;
     if (P.S > 1) {
         msm_reduce_a<C><<<(unsigned)((P.nseg_total + 127) / 128), 128, 0, st>>>(buckets, P.nseg_total, P.S, segsum, segwgt);
         msm_reduce_b<C><<<P.nwin, 256, 0, st>>>(segsum, segwgt, P.nitems, P.log2S, winsum);
+        R.launches += 1;
     } else {
         msm_reduce_b<C><<<P.nwin, 256, 0, st>>>(buckets, nullptr, P.nitems, 0, winsum);
     }
+    prof_mark("reduce");
     HALO_CUDA(cudaGetLastError());
     *d_winsum_out = winsum;
     return HALO_OK;

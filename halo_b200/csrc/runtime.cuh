@@ -34,6 +34,13 @@ struct Runtime {
     void* pinned = nullptr;         // pinned host staging
     size_t pinned_cap = 0;
     int msm_window_override = 0;
+    // per-stage CUDA-event timing of the last MSM (halo_profile_*), and a count of kernels launched
+    bool prof_on = false;
+    static const int PROF_MAX = 24;
+    cudaEvent_t prof_ev[PROF_MAX + 1] = {};
+    const char* prof_name[PROF_MAX] = {};
+    int prof_n = 0;
+    unsigned long long launches = 0;
     std::recursive_mutex mu;
     std::string err;
 };
@@ -59,6 +66,10 @@ Runtime& rt();
             return (code);                          \
         }                                           \
     } while (0)
+
+// stage timing: prof_begin() at the start of a pipeline, prof_mark("name") after each stage's launches
+int prof_begin();
+int prof_mark(const char* name);
 
 // workspace slot: returns a device pointer with at least `bytes` capacity (contents undefined)
 int ws_get(int slot, size_t bytes, void** out);

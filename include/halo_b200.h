@@ -72,6 +72,22 @@ int halo_bench_modmul(int field, int blocks, int threads, int iters, float* ms, 
 /* raw IMAD.WIDE.U32 issue rate: `iters` x 8 independent wide multiply-adds per thread */
 int halo_bench_imad(int blocks, int threads, int iters, float* ms, uint64_t* out);
 
+/* ---- instrumentation ------------------------------------------------------------------------------------- */
+/* When enabled, every MSM records CUDA events between its pipeline stages on the stream it launches on;
+ * halo_profile_read returns the number of stages of the LAST call and fills their durations (ms) and names. */
+int halo_profile_enable(int on);
+int halo_profile_read(float* ms, const char** names, int max_stages);
+/* number of kernels this library has launched since it was loaded */
+unsigned long long halo_launch_count(void);
+
+/* ---- synthetic inputs for benchmarks and property tests ---------------------------------------------------- */
+/* out[i] = m_i * G (affine, Montgomery) for i in [first, first+n), m_i = halo_gen_point_multiplier(seed, i), a
+ * 64-bit odd integer; G = (-1, 2) is the generator of both Pasta curves.  Because the discrete logs are known,
+ * sum_i s_i * P_i == (sum_i s_i * m_i) * G gives a size-independent check of an MSM result. */
+uint64_t halo_gen_point_multiplier(uint64_t seed, uint64_t i);
+int halo_gen_points_dev(int curve, uint64_t seed, size_t first, size_t n, void* d_out_xy);
+int halo_gen_points(int curve, uint64_t seed, size_t first, size_t n, uint64_t* out_xy);
+
 /* ---- elementwise helpers used by tests -------------------------------------------------------------------- */
 /* op: 0 mul, 1 add, 2 sub, 3 inverse(a), 4 to_canonical(a), 5 from_canonical(a); n elements, on the GPU */
 int halo_field_op(int field, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n);
