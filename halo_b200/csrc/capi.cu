@@ -48,7 +48,7 @@ int prof_mark(const char* name) {
     return HALO_OK;
 }
 
-template <int C> int msm_device(const void* d_bases, const void* d_scalars, size_t k, uint64_t out_xyz[12]);
+template <int C> int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, uint64_t* out_xyz);
 
 // ---- synthetic inputs: P_i = k_i * G with k_i = splitmix64(seed, i) | 1  (distinct with overwhelming probability) ----
 __host__ __device__ inline u64 splitmix64(u64 x) {
@@ -150,6 +150,7 @@ using namespace halo;
 #define NEED_INIT() HALO_CHECK(rt().inited, HALO_ENOINIT, "halo_init has not been called")
 
 extern "C" int halo_msm(int, const uint64_t*, size_t, const uint64_t*, size_t, uint64_t*);
+extern "C" int halo_msm_batch_dev(int, const void*, size_t, const void*, size_t, size_t, uint64_t*);
 
 // point_dot (group.rs:53-56): CurveGroup::normalize_batch (one inversion, Montgomery's trick) on the host — the only
 // caller passes m <= 1024 accumulated U's (acc.rs:166) — then the affine MSM on the device.
@@ -307,6 +308,7 @@ int halo_gen_points(int curve, uint64_t seed, size_t first, size_t n, uint64_t* 
     return HALO_OK;
 }
 
+int halo_set_tuning(int key, int value) { if (key < 0 || key >= 8) return HALO_EINVAL; rt().tune[key] = value; return HALO_OK; }
 int halo_msm_set_window(int c) { rt().msm_window_override = c; return HALO_OK; }
 
 int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k, uint64_t out_xyz[12]) {
@@ -320,7 +322,22 @@ int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void*
         bases = (const char*)R.pp[curve].d_gs;
     }
     bases += base_off * 64;
-    return curve == 0 ? msm_device<0>(bases, d_scalars, k, out_xyz) : msm_device<1>(bases, d_scalars, k, out_xyz);
+    return curve == 0 ? msm_device<0>(bases, d_scalars, k, 1, out_xyz) : msm_device<1>(bases, d_scalars, k, 1, out_xyz);
+}
+
+int halo_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k, size_t b,
+                       uint64_t* out_xyz) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
+    HALO_CHECK(out_xyz && (d_scalars || k == 0 || b == 0), HALO_EINVAL, "msm_batch: null pointer");
+    Runtime& R = rt();
+    const char* bases = (const char*)d_bases_xy;
+    if (!bases) {
+        HALO_CHECK(R.pp[curve].n >= base_off + k, HALO_EPARAMS, "msm_batch: resident generators missing or too few");
+        bases = (const char*)R.pp[curve].d_gs;
+    }
+    bases += base_off * 64;
+    return curve == 0 ? msm_device<0>(bases, d_scalars, k, b, out_xyz) : msm_device<1>(bases, d_scalars, k, b, out_xyz);
 }
 
 int halo_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_t* scalars, size_t k, uint64_t out_xyz[12]) {
@@ -343,11 +360,14 @@ int halo_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_
 
 int halo_msm_batch(int curve, size_t base_off, const uint64_t* scalars, size_t k, size_t b, uint64_t* out_xyz) {
     LOCK(); NEED_INIT();
-    for (size_t i = 0; i < b; ++i) {
-        int e = halo_msm(curve, nullptr, base_off, scalars + i * k * 4, k, out_xyz + 12 * i);
-        if (e) return e;
+    HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
+    HALO_CHECK(out_xyz && (scalars || k == 0 || b == 0), HALO_EINVAL, "msm_batch: null pointer");
+    void* d_s = nullptr;
+    if (k && b) {
+        if (int e = ws_get(WS_SCALARS, b * k * 32, &d_s)) return e;
+        HALO_CUDA(cudaMemcpyAsync(d_s, scalars, b * k * 32, cudaMemcpyHostToDevice, rt().stream));
     }
-    return HALO_OK;
+    return halo_msm_batch_dev(curve, nullptr, base_off, d_s, k, b, out_xyz);
 }
 
 int halo_msm_proj(int curve, const uint64_t* bases_xyz, const uint64_t* scalars, size_t k, uint64_t out_xyz[12]) {

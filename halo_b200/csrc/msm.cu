@@ -2,20 +2,28 @@
 //
 // Replaces ark-ec's `VariableBaseMSM::msm_unchecked` as reached from
 //   crates/group/src/group.rs:48-56 (point_dot_affine / point_dot),
-//   crates/accumulation/src/pedersen.rs:21 (commit), crates/accumulation/src/pcdl.rs:413,417 (IPA L/R).
+//   crates/accumulation/src/pedersen.rs:21 (commit), crates/accumulation/src/pcdl.rs:413,417 (IPA L/R),
+// and, batched over one resident base set, the 16 commits of a prover round
+//   (crates/plonk/src/plonk/protocol.rs:114,263).
 // The result is a group element, so it is bit-identical (as canonical affine coordinates) to the reference's
-// for any correct schedule.  Pipeline for k points, window width c, nwin = floor(255/c)+1 windows,
-// B = 2^(c-1) buckets per window (signed digits in [-2^(c-1), 2^(c-1)]):
-//   1. msm_count      scalars -> canonical -> signed digits; histogram of (window,bucket) sizes     [HBM: 32 B/pt]
-//   2. msm_scan       exclusive prefix sum of the nwin*B bucket sizes
-//   3. msm_scatter    digits again; write point index|sign into its bucket's slice                  [4*nwin B/pt]
-//   4. msm_size_*     counting sort of buckets by size so that a warp works on equally long buckets
-//   5. msm_accumulate one thread per bucket: XYZZ accumulator += (+/-)base  (8M+2S each)            [the hot loop]
-//   6. msm_reduce_a/b per window sum_b (b+1)*bucket_b: per-thread running sums over 32-bucket segments, then a
-//                     block-wide suffix scan (no scalar multiplications, only additions and a few doublings)
-//   7. host           Horner over the nwin window sums (255 doublings; a single GPU thread would take longer
-//                     than the PCIe round trip)
+// for any correct schedule.  Pipeline for nbatch scalar vectors of k points over the same bases, window width c,
+// nwin = floor(255/c)+1 windows per MSM, B = 2^(c-1) buckets per window (signed digits in [-2^(c-1), 2^(c-1)]);
+// "window" below means one of the nbatch*nwin (MSM, window) pairs:
+//   1. msm_count       scalars -> canonical -> signed digits; histogram of (window,bucket) sizes    [HBM: 32 B/pt]
+//   2. scan_*          exclusive prefix sum of the bucket sizes (three small multi-block kernels)
+//   3. msm_scatter     digits again; write point index|sign into its bucket's slice                 [4*nwin B/pt]
+//   4. msm_task_*      cut every bucket into tasks of at most L points and counting-sort the tasks by size, so
+//                      that a warp works on equally long tasks and no thread ever owns more than L points
+//                      (degenerate scalar distributions put a whole window into a handful of buckets)
+//   5. msm_accumulate  one thread per task: XYZZ accumulator += (+/-)base  (8M+2S each)             [the hot loop]
+//   6. msm_fixup       buckets that were cut into several tasks: one warp sums the partial results
+//   7. msm_reduce_level  per window sum_b (b+1)*bucket_b by recursive grouping (groups of 8 buckets carry a
+//                      plain sum and a weighted sum up one level; only additions and a few doublings)
+//   8. host            Horner over the nwin window sums of each MSM (255 doublings; a single GPU thread would
+//                      take longer than the 2 KB D2H copy)
 #include "runtime.cuh"
+#include <algorithm>
+#include <thread>
 
 namespace halo {
 
@@ -61,105 +69,167 @@ __device__ __forceinline__ int window_digit(const u32 (&s)[8], int w, int c, int
     return d;
 }
 
+
 // ---------------------------------------------------------------------------------------------------------
-// 1. histogram of bucket sizes
+// 1. histogram of bucket sizes.  scalars: nbatch vectors of k elements; counts: nbatch*nwin*B
 // ---------------------------------------------------------------------------------------------------------
 template <int SF>
-__global__ void __launch_bounds__(256) msm_count(const Fe<SF>* __restrict__ scalars, size_t k, int c, int nwin,
-                                                 u32* __restrict__ counts) {
+__global__ void __launch_bounds__(256) msm_count(const Fe<SF>* __restrict__ scalars, size_t k, size_t total, int c,
+                                                 int nwin, u32* __restrict__ counts) {
     const u32 B = 1u << (c - 1);
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < k; i += (size_t)gridDim.x * blockDim.x) {
-        Fe<SF> s = fe_to_canonical<SF>(load_fe(scalars + i));
+    for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const size_t j = t / k;                                   // which MSM of the batch
+        Fe<SF> s = fe_to_canonical<SF>(load_fe(scalars + t));
+        u32* cw = counts + j * (size_t)nwin * B;
         int carry = 0;
         for (int w = 0; w < nwin; ++w) {
             int d = window_digit(s.l, w, c, carry);
-            if (d != 0) atomicAdd(&counts[(size_t)w * B + (u32)(abs(d) - 1)], 1u);
+            if (d != 0) atomicAdd(&cw[(size_t)w * B + (u32)(abs(d) - 1)], 1u);
         }
     }
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// 2. exclusive scan (single block; n up to a few million 32-bit counters)
+// 2. exclusive scan of n 32-bit counters: per-block sums, scan of the block sums, apply.  1024 items / block.
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) msm_scan(const u32* __restrict__ in, u32* __restrict__ out, size_t n) {
-    __shared__ u32 part[1024];
-    const int t = threadIdx.x;
-    const size_t chunk = (n + 1023) / 1024;
-    const size_t lo = min(n, (size_t)t * chunk), hi = min(n, lo + chunk);
-    u32 s = 0;
-    for (size_t i = lo; i < hi; ++i) s += in[i];
-    part[t] = s;
+__device__ __forceinline__ u32 block_exclusive_scan_256(u32 v, u32* sh /*[8]*/, u32& block_total) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    u32 x = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { u32 y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= d) x += y; }
+    if (lane == 31) sh[wid] = x;
     __syncthreads();
-    // Hillis-Steele inclusive scan over the 1024 partials
-    for (int d = 1; d < 1024; d <<= 1) {
-        u32 v = t >= d ? part[t - d] : 0u;
-        __syncthreads();
-        part[t] += v;
-        __syncthreads();
-    }
-    u32 run = t ? part[t - 1] : 0u;
-    for (size_t i = lo; i < hi; ++i) { u32 v = in[i]; out[i] = run; run += v; }
+    u32 woff = 0, tot = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { u32 s = sh[i]; if (i < wid) woff += s; tot += s; }
+    block_total = tot;
+    __syncthreads();
+    return woff + x - v;
+}
+__global__ void __launch_bounds__(256) scan_block_sums(const u32* __restrict__ in, size_t n, u32* __restrict__ bsum) {
+    __shared__ u32 sh[8];
+    size_t base = (size_t)blockIdx.x * 1024 + threadIdx.x * 4;
+    u32 v = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) if (base + i < n) v += in[base + i];
+    u32 tot;
+    block_exclusive_scan_256(v, sh, tot);
+    if (threadIdx.x == 0) bsum[blockIdx.x] = tot;
+}
+// single block: exclusive scan of up to 256*per items in place, also writes the grand total to *total_out
+__global__ void __launch_bounds__(256) scan_partials(u32* __restrict__ bsum, size_t nblk, u32* __restrict__ total_out) {
+    __shared__ u32 sh[8];
+    const size_t per = (nblk + 255) / 256;
+    const size_t lo = min(nblk, threadIdx.x * per), hi = min(nblk, lo + per);
+    u32 v = 0;
+    for (size_t i = lo; i < hi; ++i) v += bsum[i];
+    u32 tot;
+    u32 run = block_exclusive_scan_256(v, sh, tot);
+    for (size_t i = lo; i < hi; ++i) { u32 x = bsum[i]; bsum[i] = run; run += x; }
+    if (threadIdx.x == 0 && total_out) *total_out = tot;
+}
+// out = exclusive scan; out2 (optional) gets a second copy (used as the scatter cursor)
+__global__ void __launch_bounds__(256) scan_apply(const u32* __restrict__ in, size_t n, const u32* __restrict__ bsum,
+                                                  u32* __restrict__ out, u32* __restrict__ out2) {
+    __shared__ u32 sh[8];
+    size_t base = (size_t)blockIdx.x * 1024 + threadIdx.x * 4;
+    u32 x[4], v = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { x[i] = base + i < n ? in[base + i] : 0u; v += x[i]; }
+    u32 tot;
+    u32 run = block_exclusive_scan_256(v, sh, tot) + bsum[blockIdx.x];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) if (base + i < n) { out[base + i] = run; if (out2) out2[base + i] = run; run += x[i]; }
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// 3. scatter point indices into bucket slices
+// 3. scatter point indices into bucket slices.  cursor starts as a copy of the offsets.
 // ---------------------------------------------------------------------------------------------------------
 template <int SF>
-__global__ void __launch_bounds__(256) msm_scatter(const Fe<SF>* __restrict__ scalars, size_t k, int c, int nwin,
-                                                   const u32* __restrict__ offsets, u32* __restrict__ cursor,
-                                                   u32* __restrict__ idx) {
+__global__ void __launch_bounds__(256) msm_scatter(const Fe<SF>* __restrict__ scalars, size_t k, size_t total, int c,
+                                                   int nwin, u32* __restrict__ cursor, u32* __restrict__ idx) {
     const u32 B = 1u << (c - 1);
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < k; i += (size_t)gridDim.x * blockDim.x) {
-        Fe<SF> s = fe_to_canonical<SF>(load_fe(scalars + i));
+    for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const size_t j = t / k;
+        const u32 i = (u32)(t - j * k);
+        Fe<SF> s = fe_to_canonical<SF>(load_fe(scalars + t));
+        u32* cw = cursor + j * (size_t)nwin * B;
         int carry = 0;
         for (int w = 0; w < nwin; ++w) {
             int d = window_digit(s.l, w, c, carry);
             if (d != 0) {
-                size_t b = (size_t)w * B + (u32)(abs(d) - 1);
-                u32 pos = atomicAdd(&cursor[b], 1u);
-                idx[offsets[b] + pos] = (u32)i | (d < 0 ? 0x80000000u : 0u);
+                u32 pos = atomicAdd(&cw[(size_t)w * B + (u32)(abs(d) - 1)], 1u);
+                idx[pos] = i | (d < 0 ? 0x80000000u : 0u);
             }
         }
     }
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// 4. order buckets by size (descending): counting sort on min(size, 1023)
+// 4. tasks: bucket b with cnt points becomes max(1, ceil(cnt/L)) tasks of at most L points; tasks are
+//    counting-sorted by size (descending: bin = L - size).  A bucket cut into several tasks ("multi") reserves a
+//    run of slots in the partial-result array.
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) msm_size_hist(const u32* __restrict__ counts, size_t nb, u32* __restrict__ hist) {
-    __shared__ u32 sh[1024];
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) sh[i] = 0;
+struct TaskMeta { u32 ntasks, npartial, nmulti, pad; };
+constexpr int MSM_MAX_L = 64;
+
+__global__ void __launch_bounds__(256) msm_task_hist(const u32* __restrict__ counts, size_t nb, u32 L,
+                                                     u32* __restrict__ hist, TaskMeta* __restrict__ meta,
+                                                     u32* __restrict__ pslot, u32* __restrict__ multi) {
+    __shared__ u32 sh[MSM_MAX_L + 1];
+    for (int i = threadIdx.x; i <= MSM_MAX_L; i += blockDim.x) sh[i] = 0;
     __syncthreads();
-    for (size_t b = blockIdx.x * (size_t)blockDim.x + threadIdx.x; b < nb; b += (size_t)gridDim.x * blockDim.x)
-        atomicAdd(&sh[1023u - min(counts[b], 1023u)], 1u);
-    __syncthreads();
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) if (sh[i]) atomicAdd(&hist[i], sh[i]);
-}
-__global__ void __launch_bounds__(256) msm_size_scatter(const u32* __restrict__ counts, size_t nb,
-                                                        const u32* __restrict__ hist_off, u32* __restrict__ hist_cur,
-                                                        u32* __restrict__ order) {
     for (size_t b = blockIdx.x * (size_t)blockDim.x + threadIdx.x; b < nb; b += (size_t)gridDim.x * blockDim.x) {
-        u32 bin = 1023u - min(counts[b], 1023u);
-        u32 pos = atomicAdd(&hist_cur[bin], 1u);
-        order[hist_off[bin] + pos] = (u32)b;
+        const u32 cnt = counts[b];
+        const u32 full = cnt / L, rem = cnt - full * L;
+        if (full) atomicAdd(&sh[0], full);
+        if (rem || cnt == 0) atomicAdd(&sh[L - rem], 1u);
+        const u32 nt = full + (rem ? 1u : 0u);
+        if (nt > 1) {
+            pslot[b] = atomicAdd(&meta->npartial, nt);
+            multi[atomicAdd(&meta->nmulti, 1u)] = (u32)b;
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i <= (int)L; i += blockDim.x) if (sh[i]) atomicAdd(&hist[i], sh[i]);
+}
+// bincur: exclusive scan of hist (in place), used as cursors
+__global__ void __launch_bounds__(256) msm_task_emit(const u32* __restrict__ counts, size_t nb, u32 L,
+                                                     u32* __restrict__ bincur, uint2* __restrict__ tasks) {
+    for (size_t b = blockIdx.x * (size_t)blockDim.x + threadIdx.x; b < nb; b += (size_t)gridDim.x * blockDim.x) {
+        const u32 cnt = counts[b];
+        const u32 full = cnt / L, rem = cnt - full * L;
+        if (full) {
+            u32 pos = atomicAdd(&bincur[0], full);
+            for (u32 s = 0; s < full; ++s) tasks[pos + s] = make_uint2((u32)b, s);
+        }
+        if (rem || cnt == 0) {
+            u32 pos = atomicAdd(&bincur[L - rem], 1u);
+            tasks[pos] = make_uint2((u32)b, full);
+        }
     }
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// 5. bucket accumulation: one thread per bucket, buckets visited in size order
+// 5. bucket accumulation: one thread per task, tasks visited in size order
 // ---------------------------------------------------------------------------------------------------------
 template <int C>
 __global__ void __launch_bounds__(128, 4) msm_accumulate(const Affine<C>* __restrict__ bases,
                                                          const u32* __restrict__ idx,
                                                          const u32* __restrict__ offsets,
                                                          const u32* __restrict__ counts,
-                                                         const u32* __restrict__ order, size_t nb,
-                                                         XYZZ<C>* __restrict__ buckets) {
+                                                         const uint2* __restrict__ tasks,
+                                                         const TaskMeta* __restrict__ meta, u32 L,
+                                                         const u32* __restrict__ pslot,
+                                                         XYZZ<C>* __restrict__ buckets, XYZZ<C>* __restrict__ partial) {
     size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (t >= nb) return;
-    const u32 b = order[t];
-    const u32 cnt = counts[b];
-    const u32* my = idx + offsets[b];
+    if (t >= meta->ntasks) return;
+    const uint2 tk = tasks[t];
+    const u32 b = tk.x, seg = tk.y;
+    const u32 cnt_b = counts[b];
+    const u32 cnt = min(L, cnt_b - seg * L);
+    const u32* my = idx + offsets[b] + seg * L;
+    XYZZ<C>* dest = cnt_b > L ? partial + pslot[b] + seg : buckets + b;
     XYZZ<C> acc = xyzz_identity<C>();
     if (cnt) {
         u32 e = __ldg(my);
@@ -172,90 +242,75 @@ __global__ void __launch_bounds__(128, 4) msm_accumulate(const Affine<C>* __rest
             e = e_next; p = p_next;
         }
     }
-    store_xyzz(buckets + b, acc);
+    store_xyzz(dest, acc);
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// 6a. per-segment running sums: segment of S consecutive buckets -> (sum, sum_j j*bucket_{lo+j})
+// 6. multi-task buckets: one warp adds the partial results of one bucket
 // ---------------------------------------------------------------------------------------------------------
+template <int C> __device__ __forceinline__ XYZZ<C> xyzz_shfl_down(const XYZZ<C>& v, int d) {
+    XYZZ<C> r;
+    const u32* s = reinterpret_cast<const u32*>(&v);
+    u32* o = reinterpret_cast<u32*>(&r);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) o[i] = __shfl_down_sync(0xffffffffu, s[i], d);
+    return r;
+}
 template <int C>
-__global__ void __launch_bounds__(128, 2) msm_reduce_a(const XYZZ<C>* __restrict__ buckets, size_t nseg_total, int S,
-                                                       XYZZ<C>* __restrict__ segsum, XYZZ<C>* __restrict__ segwgt) {
-    size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (t >= nseg_total) return;
-    const XYZZ<C>* base = buckets + t * (size_t)S;
-    XYZZ<C> run = xyzz_identity<C>(), acc = xyzz_identity<C>();
-    for (int j = S - 1; j >= 1; --j) {
-        XYZZ<C> bkt = load_xyzz(base + j);
-        xyzz_add<C>(run, bkt);
-        xyzz_add<C>(acc, run);
+__global__ void __launch_bounds__(128, 2) msm_fixup(const u32* __restrict__ multi, const TaskMeta* __restrict__ meta,
+                                                    const u32* __restrict__ counts, const u32* __restrict__ pslot,
+                                                    u32 L, const XYZZ<C>* __restrict__ partial,
+                                                    XYZZ<C>* __restrict__ buckets) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 nwarps = gridDim.x * (blockDim.x >> 5);
+    const u32 nmulti = meta->nmulti;
+    for (u32 m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); m < nmulti; m += nwarps) {
+        const u32 b = multi[m];
+        const u32 nt = (counts[b] + L - 1) / L;
+        const XYZZ<C>* src = partial + pslot[b];
+        XYZZ<C> acc = xyzz_identity<C>();
+        for (u32 s = lane; s < nt; s += 32) { XYZZ<C> v = load_xyzz(src + s); xyzz_add<C>(acc, v); }
+        int d0 = 16;
+        while (d0 >= 1 && (u32)d0 >= nt) d0 >>= 1;          // lanes >= nt hold the identity
+        for (int d = d0; d >= 1; d >>= 1) { XYZZ<C> o = xyzz_shfl_down<C>(acc, d); xyzz_add<C>(acc, o); }
+        if (lane == 0) store_xyzz(buckets + b, acc);
     }
-    XYZZ<C> b0 = load_xyzz(base);
-    xyzz_add<C>(run, b0);
-    store_xyzz(segsum + t, run);
-    store_xyzz(segwgt + t, acc);
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// 6b. one block per window: items j < nitems with (sum_j, wgt_j), item j covering buckets [j*S, (j+1)*S).
-//     window result = sum_j [ wgt_j + (j*S) * sum_j ] + sum_j sum_j          (bucket b carries weight b+1)
+// 7. window sums  W = sum_b (b+1) * bucket_b  by recursive grouping.  At a level with items i = 0..n_in-1 per
+//    window, item i stands for  w_i + (i*M) * s_i  (level 0: s_i = w_i = bucket_i, M = 1).  A group of S items
+//    g*S + j becomes one item of the next level:  s' = sum_j s,  w' = sum_j w + M * sum_j j*s,  M' = S*M.
+//    One thread per group; when one item is left, W = w_0.
 // ---------------------------------------------------------------------------------------------------------
 template <int C> __device__ __forceinline__ void xyzz_dbl_n(XYZZ<C>& p, int n) {
     for (int i = 0; i < n; ++i) p = xyzz_dbl<C>(p);
 }
-
-template <int C>
-__global__ void __launch_bounds__(256, 1) msm_reduce_b(const XYZZ<C>* __restrict__ sums, const XYZZ<C>* __restrict__ wgts,
-                                                       int nitems, int log2S, XYZZ<C>* __restrict__ winsum) {
-    __shared__ XYZZ<C> sh[256];
-    const int t = threadIdx.x, T = blockDim.x;
-    const int w = blockIdx.x;
-    sums += (size_t)w * nitems;
-    if (wgts) wgts += (size_t)w * nitems;
-    const int I = (nitems + T - 1) / T;                 // items per thread (power of two or 1)
-    int log2I = 0; while ((1 << log2I) < I) ++log2I;
-    const int lo = t * I;
+template <int C, int MINB>
+__global__ void __launch_bounds__(128, MINB) msm_reduce_level(const XYZZ<C>* __restrict__ s_in, const XYZZ<C>* __restrict__ w_in,
+                                                           u32 n_in, u32 S, int log2M, size_t ngroups_total,
+                                                           XYZZ<C>* __restrict__ s_out, XYZZ<C>* __restrict__ w_out) {
+    size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (t >= ngroups_total) return;
+    const u32 n_out = n_in / S;
+    const size_t win = t / n_out, g = t - win * n_out;
+    const size_t base = win * n_in + g * S;
     XYZZ<C> run = xyzz_identity<C>(), acc = xyzz_identity<C>(), wsum = xyzz_identity<C>();
-    for (int j = I - 1; j >= 0; --j) {
-        int it = lo + j;
-        if (it < nitems) {
-            XYZZ<C> s = load_xyzz(sums + it);
-            xyzz_add<C>(run, s);
-            if (wgts) { XYZZ<C> wg = load_xyzz(wgts + it); xyzz_add<C>(wsum, wg); }
-        }
-        if (j >= 1) xyzz_add<C>(acc, run);
+    for (u32 j = S - 1; j >= 1; --j) {
+        XYZZ<C> v = load_xyzz(s_in + base + j);
+        xyzz_add<C>(run, v);
+        xyzz_add<C>(acc, run);
+        if (w_in) { XYZZ<C> wv = load_xyzz(w_in + base + j); xyzz_add<C>(wsum, wv); }
     }
-    // thread-local weighted sum relative to the thread's first bucket: wsum + S * acc
-    xyzz_dbl_n<C>(acc, log2S);
+    {
+        XYZZ<C> v = load_xyzz(s_in + base);
+        xyzz_add<C>(run, v);
+        if (w_in) { XYZZ<C> wv = load_xyzz(w_in + base); xyzz_add<C>(wsum, wv); } else wsum = run;
+    }
+    xyzz_dbl_n<C>(acc, log2M);
     xyzz_add<C>(wsum, acc);
-    // suffix scan of the thread sums
-    sh[t] = run;
-    __syncthreads();
-    for (int d = 1; d < T; d <<= 1) {
-        XYZZ<C> mine = sh[t];
-        if (t + d < T) { XYZZ<C> o = sh[t + d]; xyzz_add<C>(mine, o); }
-        __syncthreads();
-        sh[t] = mine;
-        __syncthreads();
-    }
-    // sum_t t * s_t = sum_{t>=1} suffix_t ;  thread t starts at bucket t*I*S
-    XYZZ<C> z = wsum;
-    if (t >= 1) {
-        XYZZ<C> y = sh[t];
-        xyzz_dbl_n<C>(y, log2S + log2I);
-        xyzz_add<C>(z, y);
-    } else {
-        XYZZ<C> tot = sh[0];          // + sum of all buckets (weight b+1 instead of b)
-        xyzz_add<C>(z, tot);
-    }
-    __syncthreads();
-    sh[t] = z;
-    __syncthreads();
-    for (int d = T >> 1; d >= 1; d >>= 1) {
-        if (t < d) { XYZZ<C> a = sh[t], b = sh[t + d]; xyzz_add<C>(a, b); sh[t] = a; }
-        __syncthreads();
-    }
-    if (t == 0) store_xyzz(winsum + w, sh[0]);
+    if (n_out > 1) store_xyzz(s_out + t, run);
+    store_xyzz(w_out + t, wsum);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -272,67 +327,114 @@ static int pick_window(size_t k) {
 }
 
 struct MsmPlan {
-    int c, nwin, S, log2S, nitems;
-    size_t B, nb, nseg_total;
+    int c, nwin;          // window width, windows per MSM
+    size_t nbatch, nwt;   // MSMs in the batch, total windows = nbatch*nwin
+    size_t B, nb;         // buckets per window, total buckets
+    u32 L;                // max points per task
+    size_t max_tasks, max_partial;
 };
-static MsmPlan make_plan(size_t k) {
+static MsmPlan make_plan(size_t k, size_t nbatch) {
     MsmPlan p;
     p.c = pick_window(k);
     p.nwin = 255 / p.c + 1;
+    p.nbatch = nbatch;
+    p.nwt = nbatch * p.nwin;
     p.B = (size_t)1 << (p.c - 1);
-    p.nb = p.B * p.nwin;
-    p.S = p.B > 1024 ? (int)(p.B / 1024) : 1;
-    p.log2S = 0; while ((1 << p.log2S) < p.S) ++p.log2S;
-    p.nitems = (int)(p.B / p.S);
-    p.nseg_total = (size_t)p.nitems * p.nwin;
+    p.nb = p.B * p.nwt;
+    // long tasks amortise the bucket write; short tasks give small problems enough threads
+    size_t work = k * p.nwt;
+    p.L = work >= ((size_t)1 << 23) ? 64 : work >= ((size_t)1 << 20) ? 32 : 16;
+    p.max_tasks = p.nb + work / p.L + 1;
+    p.max_partial = 2 * (work / p.L) + 2;
     return p;
 }
 
-// Enqueues the whole device pipeline on the runtime stream and leaves nwin window sums (XYZZ) in *d_winsum.
+static int scan_u32(const u32* in, size_t n, u32* out, u32* out2, u32* bsum /*>= n/1024+1*/, u32* total_out, cudaStream_t st) {
+    unsigned nblk = (unsigned)((n + 1023) / 1024);
+    scan_block_sums<<<nblk, 256, 0, st>>>(in, n, bsum);
+    scan_partials<<<1, 256, 0, st>>>(bsum, nblk, total_out);
+    scan_apply<<<nblk, 256, 0, st>>>(in, n, bsum, out, out2);
+    rt().launches += 3;
+    return HALO_OK;
+}
+
+// Enqueues the whole device pipeline on the runtime stream and leaves nwt window sums (XYZZ) in *d_winsum_out.
 template <int C>
 static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR>* d_scalars, size_t k,
                        const MsmPlan& P, XYZZ<C>** d_winsum_out) {
     constexpr int SF = CurveTraits<C>::SCALAR;
     Runtime& R = rt();
     cudaStream_t st = R.stream;
-    u32 *counts, *offsets, *cursor, *idx, *order, *sizehist;
-    XYZZ<C> *buckets, *segsum, *segwgt, *winsum;
-    // counts | cursor | sizehist(3*1024) share one zero-filled allocation
-    size_t zero_words = 2 * P.nb + 3 * 1024;
+    const size_t total = k * P.nbatch;
+    u32 *counts, *offsets, *cursor, *bsum, *idx, *pslot, *multi, *hist;
+    uint2* tasks;
+    TaskMeta* meta;
+    XYZZ<C> *buckets, *partial, *lvl[4], *winsum;
+    // counts | hist (MSM_MAX_L+1, padded to 128) | meta share one zero-filled allocation
+    const size_t zero_words = P.nb + 128 + 4;
     if (int e = ws_get(WS_COUNTS, zero_words * 4, (void**)&counts)) return e;
-    cursor = counts + P.nb;
-    sizehist = cursor + P.nb;                       // [0,1024) hist, [1024,2048) offsets, [2048,3072) cursors
-    if (int e = ws_get(WS_OFFSETS, P.nb * 4, (void**)&offsets)) return e;
-    if (int e = ws_get(WS_IDX, (size_t)P.nwin * k * 4, (void**)&idx)) return e;
-    if (int e = ws_get(WS_ORDER, P.nb * 4, (void**)&order)) return e;
+    hist = counts + P.nb;
+    meta = (TaskMeta*)(hist + 128);
+    const size_t nblk = (P.nb + 1023) / 1024;
+    if (int e = ws_get(WS_OFFSETS, (2 * P.nb + nblk + 1) * 4, (void**)&offsets)) return e;
+    cursor = offsets + P.nb;
+    bsum = cursor + P.nb;
+    if (int e = ws_get(WS_IDX, P.nwt * k * 4, (void**)&idx)) return e;
+    if (int e = ws_get(WS_ORDER, P.max_tasks * sizeof(uint2), (void**)&tasks)) return e;
+    if (int e = ws_get(WS_SIZEHIST, 2 * P.nb * 4, (void**)&pslot)) return e;
+    multi = pslot + P.nb;
     if (int e = ws_get(WS_BUCKETS, P.nb * sizeof(XYZZ<C>), (void**)&buckets)) return e;
-    if (int e = ws_get(WS_SEGSUM, P.nseg_total * sizeof(XYZZ<C>), (void**)&segsum)) return e;
-    if (int e = ws_get(WS_SEGWGT, P.nseg_total * sizeof(XYZZ<C>), (void**)&segwgt)) return e;
-    if (int e = ws_get(WS_WINSUM, (size_t)P.nwin * sizeof(XYZZ<C>), (void**)&winsum)) return e;
+    if (int e = ws_get(WS_TMP3, P.max_partial * sizeof(XYZZ<C>), (void**)&partial)) return e;
+    const size_t l1 = P.nb / 2 + P.nwt, l2 = P.nb / 4 + P.nwt;
+    if (int e = ws_get(WS_SEGSUM, 2 * l1 * sizeof(XYZZ<C>), (void**)&lvl[0])) return e;
+    lvl[1] = lvl[0] + l1;
+    if (int e = ws_get(WS_SEGWGT, 2 * l2 * sizeof(XYZZ<C>), (void**)&lvl[2])) return e;
+    lvl[3] = lvl[2] + l2;
+    if (int e = ws_get(WS_WINSUM, P.nwt * sizeof(XYZZ<C>), (void**)&winsum)) return e;
+
     if (int e = prof_begin()) return e;
     HALO_CUDA(cudaMemsetAsync(counts, 0, zero_words * 4, st));
-
-    int grid_pts = (int)std::min<size_t>((k + 255) / 256, (size_t)R.sm_count * 8);
-    int grid_b = (int)std::min<size_t>((P.nb + 255) / 256, (size_t)R.sm_count * 8);
-    msm_count<SF><<<grid_pts, 256, 0, st>>>(d_scalars, k, P.c, P.nwin, counts);
+    const int grid_pts = (int)std::min<size_t>((total + 255) / 256, (size_t)R.sm_count * 8);
+    const int grid_b = (int)std::min<size_t>((P.nb + 255) / 256, (size_t)R.sm_count * 8);
+    msm_count<SF><<<grid_pts, 256, 0, st>>>(d_scalars, k, total, P.c, P.nwin, counts);
     prof_mark("count");
-    msm_scan<<<1, 1024, 0, st>>>(counts, offsets, P.nb);
+    scan_u32(counts, P.nb, offsets, cursor, bsum, nullptr, st);
     prof_mark("scan");
-    msm_scatter<SF><<<grid_pts, 256, 0, st>>>(d_scalars, k, P.c, P.nwin, offsets, cursor, idx);
+    msm_scatter<SF><<<grid_pts, 256, 0, st>>>(d_scalars, k, total, P.c, P.nwin, cursor, idx);
     prof_mark("scatter");
-    msm_size_hist<<<grid_b, 256, 0, st>>>(counts, P.nb, sizehist);
-    msm_scan<<<1, 1024, 0, st>>>(sizehist, sizehist + 1024, 1024);
-    msm_size_scatter<<<grid_b, 256, 0, st>>>(counts, P.nb, sizehist + 1024, sizehist + 2048, order);
-    prof_mark("order");
-    msm_accumulate<C><<<(unsigned)((P.nb + 127) / 128), 128, 0, st>>>(d_bases, idx, offsets, counts, order, P.nb, buckets);
+    msm_task_hist<<<grid_b, 256, 0, st>>>(counts, P.nb, P.L, hist, meta, pslot, multi);
+    scan_partials<<<1, 256, 0, st>>>(hist, P.L + 1, &meta->ntasks);
+    msm_task_emit<<<grid_b, 256, 0, st>>>(counts, P.nb, P.L, hist, tasks);
+    prof_mark("tasks");
+    msm_accumulate<C><<<(unsigned)((P.max_tasks + 127) / 128), 128, 0, st>>>(d_bases, idx, offsets, counts, tasks, meta,
+                                                                           P.L, pslot, buckets, partial);
     prof_mark("accumulate");
-    R.launches += 8;
-    if (P.S > 1) {
-        msm_reduce_a<C><<<(unsigned)((P.nseg_total + 127) / 128), 128, 0, st>>>(buckets, P.nseg_total, P.S, segsum, segwgt);
-        msm_reduce_b<C><<<P.nwin, 256, 0, st>>>(segsum, segwgt, P.nitems, P.log2S, winsum);
-        R.launches += 1;
-    } else {
-        msm_reduce_b<C><<<P.nwin, 256, 0, st>>>(buckets, nullptr, P.nitems, 0, winsum);
+    msm_fixup<C><<<R.sm_count * 2, 128, 0, st>>>(multi, meta, counts, pslot, P.L, partial, buckets);
+    prof_mark("fixup");
+    R.launches += 7;
+    // bucket reduction levels
+    {
+        const XYZZ<C>*s_in = buckets, *w_in = nullptr;
+        u32 n_in = (u32)P.B;
+        int log2M = 0, lv = 0;
+        while (n_in > 1) {
+            const u32 S0 = R.tune[1] > 0 ? (u32)R.tune[1] : 8u;        // group size (power of two)
+            const u32 S = n_in >= S0 ? S0 : n_in;
+            const u32 n_out = n_in / S;
+            const size_t groups = (size_t)n_out * P.nwt;
+            XYZZ<C>* s_out = lvl[(lv & 1) * 2];
+            XYZZ<C>* w_out = n_out > 1 ? lvl[(lv & 1) * 2 + 1] : winsum;
+            if (R.tune[0] == 1)
+                msm_reduce_level<C, 4><<<(unsigned)((groups + 127) / 128), 128, 0, st>>>(s_in, w_in, n_in, S, log2M, groups, s_out, w_out);
+            else if (R.tune[0] == 2)
+                msm_reduce_level<C, 3><<<(unsigned)((groups + 127) / 128), 128, 0, st>>>(s_in, w_in, n_in, S, log2M, groups, s_out, w_out);
+            else
+                msm_reduce_level<C, 2><<<(unsigned)((groups + 127) / 128), 128, 0, st>>>(s_in, w_in, n_in, S, log2M, groups, s_out, w_out);
+            R.launches += 1;
+            s_in = s_out; w_in = w_out; n_in = n_out;
+            for (u32 x = S; x > 1; x >>= 1) ++log2M;
+            ++lv;
+        }
     }
     prof_mark("reduce");
     HALO_CUDA(cudaGetLastError());
@@ -352,26 +454,37 @@ static void msm_combine_host(const XYZZ<C>* win, const MsmPlan& P, uint64_t out_
     memcpy(out_xyz, &j, 96);
 }
 
+// nbatch MSMs of k points over the same bases; scalars: nbatch x k elements, out: nbatch x 12 words
 template <int C>
-int msm_device(const void* d_bases, const void* d_scalars, size_t k, uint64_t out_xyz[12]) {
+int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, uint64_t* out_xyz) {
     Runtime& R = rt();
-    if (k == 0) {
+    if (k == 0 || nbatch == 0) {
         Jac<C> j = xyzz_to_jac<C>(xyzz_identity<C>());
-        memcpy(out_xyz, &j, 96);
+        for (size_t i = 0; i < nbatch; ++i) memcpy(out_xyz + 12 * i, &j, 96);
         return HALO_OK;
     }
     HALO_CHECK(k < ((size_t)1 << 31), HALO_EINVAL, "msm: k must be < 2^31");
-    MsmPlan P = make_plan(k);
+    MsmPlan P = make_plan(k, nbatch);
+    HALO_CHECK(P.nwt * k < ((size_t)1 << 32), HALO_EINVAL, "msm: batch too large (nbatch*nwin*k must be < 2^32)");
     XYZZ<C>* d_win = nullptr;
     if (int e = msm_enqueue<C>((const Affine<C>*)d_bases, (const Fe<CurveTraits<C>::SCALAR>*)d_scalars, k, P, &d_win)) return e;
     void* h = nullptr;
-    if (int e = pinned_get((size_t)P.nwin * sizeof(XYZZ<C>), &h)) return e;
-    HALO_CUDA(cudaMemcpyAsync(h, d_win, (size_t)P.nwin * sizeof(XYZZ<C>), cudaMemcpyDeviceToHost, R.stream));
+    if (int e = pinned_get(P.nwt * sizeof(XYZZ<C>), &h)) return e;
+    HALO_CUDA(cudaMemcpyAsync(h, d_win, P.nwt * sizeof(XYZZ<C>), cudaMemcpyDeviceToHost, R.stream));
     HALO_CUDA(cudaStreamSynchronize(R.stream));
-    msm_combine_host<C>((const XYZZ<C>*)h, P, out_xyz);
+    const XYZZ<C>* win = (const XYZZ<C>*)h;
+    if (nbatch < 4) {
+        for (size_t i = 0; i < nbatch; ++i) msm_combine_host<C>(win + i * P.nwin, P, out_xyz + 12 * i);
+    } else {
+        unsigned nt = std::min<size_t>(nbatch, std::max(1u, std::thread::hardware_concurrency()));
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < nt; ++t)
+            th.emplace_back([&, t]() { for (size_t i = t; i < nbatch; i += nt) msm_combine_host<C>(win + i * P.nwin, P, out_xyz + 12 * i); });
+        for (auto& x : th) x.join();
+    }
     return HALO_OK;
 }
-template int msm_device<0>(const void*, const void*, size_t, uint64_t*);
-template int msm_device<1>(const void*, const void*, size_t, uint64_t*);
+template int msm_device<0>(const void*, const void*, size_t, size_t, uint64_t*);
+template int msm_device<1>(const void*, const void*, size_t, size_t, uint64_t*);
 
 }  // namespace halo

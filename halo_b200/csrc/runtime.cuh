@@ -34,6 +34,7 @@ struct Runtime {
     void* pinned = nullptr;         // pinned host staging
     size_t pinned_cap = 0;
     int msm_window_override = 0;
+    int tune[8] = {};               // experiment knobs (halo_set_tuning)
     // per-stage CUDA-event timing of the last MSM (halo_profile_*), and a count of kernels launched
     bool prof_on = false;
     static const int PROF_MAX = 24;

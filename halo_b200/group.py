@@ -45,3 +45,16 @@ def field_op(field, op, a, b=None):
     out = np.empty_like(a)
     check(lib.halo_field_op(field, code, ptr(a), ptr(b), ptr(out), ctypes.c_size_t(a.shape[0])))
     return out
+
+
+def msm_batch_resident(curve, xs, base_off=0):
+    """b MSMs over the same resident generators Gs[base_off : base_off+k] in one device pipeline — the shape of the
+    16 commits of a prover round (crates/plonk/src/plonk/protocol.rs:114,263).  xs: (b, k, 4)."""
+    _lib.ensure_init()
+    xs = np.ascontiguousarray(xs, dtype=np.uint64)
+    assert xs.ndim == 3 and xs.shape[2] == 4
+    b, k = xs.shape[0], xs.shape[1]
+    out = np.empty((b, 12), dtype=np.uint64)
+    check(lib.halo_msm_batch(curve, ctypes.c_size_t(base_off), ptr(xs.reshape(-1, 4)), ctypes.c_size_t(k),
+                             ctypes.c_size_t(b), ptr(out)))
+    return out

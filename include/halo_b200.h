@@ -62,6 +62,11 @@ int halo_msm_proj(int curve, const uint64_t* bases_xyz, const uint64_t* scalars,
 /* same as halo_msm with inputs already in device memory (d_bases may be NULL for resident Gs) */
 int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k,
                  uint64_t out_xyz[12]);
+/* batched variant over device memory: b scalar vectors of k elements against the same k bases */
+int halo_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k, size_t b,
+                       uint64_t* out_xyz);
+/* experiment knobs (0 = default): key 0 = bucket-reduction occupancy variant, key 1 = reduction group size */
+int halo_set_tuning(int key, int value);
 /* window width override for experiments (0 = automatic) */
 int halo_msm_set_window(int c);
 

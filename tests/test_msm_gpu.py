@@ -155,3 +155,46 @@ def test_msm_large_bit_exact(hb, oracle, k):
     got2 = hb.group.point_dot_affine(0, sc2, pts)
     got3 = hb.group.point_dot_affine(0, O.field_add(0, sc, sc2), pts)
     assert (_aff(O, 0, got3) == _aff(O, 0, O.point_add(0, got, got2))).all()
+
+
+@pytest.mark.parametrize("curve", [0, 1])
+def test_msm_batch_over_resident_generators(hb, oracle, curve):
+    """The 16-commit shape of a prover round (protocol.rs:114,263): one pipeline, same bases, b scalar vectors."""
+    O = oracle
+    sf = O.SCALAR_FIELD[curve]
+    n, b = 4096, 7
+    gs, S, H = O.pp_generate(curve, n)
+    hb.pp.reset(curve); hb.pp.set_pp(curve, gs, S, H)
+    xs = np.stack([O.random_scalars(sf, n, 500 + i) for i in range(b)])
+    xs[2] = 0                                   # an all-zero column commits to the identity
+    xs[3, 100:] = 0                             # short polynomial (trailing zero coefficients)
+    got = hb.group.msm_batch_resident(curve, xs)
+    for i in range(b):
+        assert (_aff(O, curve, got[i]) == _aff(O, curve, O.msm(curve, gs, xs[i]))).all(), i
+    # a sub-range of the generators
+    got = hb.group.msm_batch_resident(curve, xs[:, :1000], base_off=512)
+    for i in range(b):
+        assert (_aff(O, curve, got[i]) == _aff(O, curve, O.msm(curve, gs[512:1512], xs[i, :1000]))).all(), i
+    hb.pp.reset(curve)
+
+
+@pytest.mark.parametrize("kind", ["all_equal", "tiny", "two_values", "top_heavy"])
+def test_msm_degenerate_scalar_distributions(hb, oracle, kind):
+    """Scalar vectors that put a whole window into a handful of buckets (selector-like columns, constants):
+    buckets are cut into bounded tasks, so these must stay exact and must not serialise on one thread."""
+    O = oracle
+    k = 40000
+    pts = O.points_arith(0, k)
+    base = O.random_scalars(0, k, 77)
+    if kind == "all_equal":
+        sc = np.tile(base[0], (k, 1))
+    elif kind == "tiny":
+        sc = O.ints_to_mont(0, [(i * 7) % 3 for i in range(k)])
+    elif kind == "two_values":
+        sc = np.where((np.arange(k) % 2 == 0)[:, None], base[1], base[2])
+    else:
+        p = O.MODULUS[0]
+        sc = O.ints_to_mont(0, [p - 1 - (i % 5) for i in range(k)])
+    sc = np.ascontiguousarray(sc, dtype=np.uint64)
+    got = hb.group.point_dot_affine(0, sc, pts)
+    assert (_aff(O, 0, got) == _aff(O, 0, O.msm(0, pts, sc))).all()
