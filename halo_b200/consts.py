@@ -48,3 +48,16 @@ def affine_to_projective(curve, xy):
             out[i, 0:8] = xy[i]
             out[i, 8:12] = o
     return out
+
+
+def root_of_unity(field, log_n):
+    """omega_N = (5^((p-1)/2^32))^(2^(32-log N)) as a canonical integer (ark-ff GENERATOR = 5, TWO_ADICITY = 32;
+    pinned by crates/plonk/src/frontend/ivc/mod.rs:56,113)."""
+    p = MODULUS[field]
+    w = pow(GENERATOR, (p - 1) >> TWO_ADICITY, p)
+    return pow(w, 1 << (TWO_ADICITY - log_n), p)
+
+
+def root_power(field, log_n, i):
+    """omega_N^i in Montgomery limbs (host-side scalar, not a hot path)."""
+    return to_mont(field, pow(root_of_unity(field, log_n), i, MODULUS[field]))

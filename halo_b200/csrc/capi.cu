@@ -49,6 +49,8 @@ int prof_mark(const char* name) {
 }
 
 template <int C> int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, uint64_t* out_xyz);
+template <int F> int ntt_device(Fe<F>* data, Fe<F>* out, int log_n, size_t batch, bool inverse, const Fe<F>* coset);
+template <int F> int ntt_fold_device(const Fe<F>* coeffs, size_t len, int log_n, Fe<F>* out);
 
 // ---- synthetic inputs: P_i = k_i * G with k_i = splitmix64(seed, i) | 1  (distinct with overwhelming probability) ----
 __host__ __device__ inline u64 splitmix64(u64 x) {
@@ -208,6 +210,7 @@ int halo_shutdown(void) {
     for (int c = 0; c < 2; ++c) { if (R.pp[c].d_gs) cudaFree(R.pp[c].d_gs); R.pp[c] = ResidentParams(); }
     if (R.pinned) cudaFreeHost(R.pinned);
     R.pinned = nullptr; R.pinned_cap = 0;
+    for (int f = 0; f < 2; ++f) { if (R.ntt_tw[f]) cudaFree(R.ntt_tw[f]); R.ntt_tw[f] = nullptr; R.ntt_logmax[f] = 0; }
     cudaStreamDestroy(R.own_stream);
     R.own_stream = R.stream = nullptr;
     R.inited = false;
@@ -439,4 +442,74 @@ int halo_bench_imad(int blocks, int threads, int iters, float* ms, uint64_t* out
     return HALO_OK;
 }
 
+}  // extern "C"
+
+// ---- NTT ----
+template <int F>
+static int ntt_dev_impl(void* d_data, unsigned log_n, size_t b, int inverse, const uint64_t* coset) {
+    Runtime& R = rt();
+    const size_t bytes = ((size_t)b << log_n) * 32;
+    void* scratch;
+    if (int e = ws_get(WS_NTT1, bytes, &scratch)) return e;
+    Fe<F> g;
+    if (coset) memcpy(&g, coset, 32);
+    if (int e = ntt_device<F>((Fe<F>*)d_data, (Fe<F>*)scratch, (int)log_n, b, inverse != 0, coset ? &g : nullptr)) return e;
+    HALO_CUDA(cudaMemcpyAsync(d_data, scratch, bytes, cudaMemcpyDeviceToDevice, R.stream));
+    return HALO_OK;
+}
+template <int F>
+static int ntt_host_impl(uint64_t* data, unsigned log_n, size_t b, int inverse, const uint64_t* coset) {
+    Runtime& R = rt();
+    const size_t bytes = ((size_t)b << log_n) * 32;
+    void *d_in, *d_out;
+    if (int e = ws_get(WS_NTT0, bytes, &d_in)) return e;
+    if (int e = ws_get(WS_NTT1, bytes, &d_out)) return e;
+    HALO_CUDA(cudaMemcpyAsync(d_in, data, bytes, cudaMemcpyHostToDevice, R.stream));
+    Fe<F> g;
+    if (coset) memcpy(&g, coset, 32);
+    if (int e = ntt_device<F>((Fe<F>*)d_in, (Fe<F>*)d_out, (int)log_n, b, inverse != 0, coset ? &g : nullptr)) return e;
+    HALO_CUDA(cudaMemcpyAsync(data, d_out, bytes, cudaMemcpyDeviceToHost, R.stream));
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
+    return HALO_OK;
+}
+template <int F>
+static int poly_evaluate_impl(const uint64_t* coeffs, size_t len, unsigned log_n, uint64_t* out_evals) {
+    Runtime& R = rt();
+    const size_t N = (size_t)1 << log_n;
+    void *d_c, *d_in, *d_out;
+    if (int e = ws_get(WS_NTT0, N * 32, &d_in)) return e;
+    if (int e = ws_get(WS_NTT1, N * 32, &d_out)) return e;
+    if (len) {
+        if (int e = ws_get(WS_TMP0, len * 32, &d_c)) return e;
+        HALO_CUDA(cudaMemcpyAsync(d_c, coeffs, len * 32, cudaMemcpyHostToDevice, R.stream));
+        if (int e = ntt_fold_device<F>((const Fe<F>*)d_c, len, (int)log_n, (Fe<F>*)d_in)) return e;
+    } else {
+        HALO_CUDA(cudaMemsetAsync(d_in, 0, N * 32, R.stream));
+    }
+    if (int e = ntt_device<F>((Fe<F>*)d_in, (Fe<F>*)d_out, (int)log_n, 1, false, nullptr)) return e;
+    HALO_CUDA(cudaMemcpyAsync(out_evals, d_out, N * 32, cudaMemcpyDeviceToHost, R.stream));
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
+    return HALO_OK;
+}
+
+extern "C" {
+int halo_ntt_dev(int field, void* d_data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK((field == 0 || field == 1) && (d_data || b == 0) && log_n <= 30, HALO_EINVAL, "ntt: bad argument");
+    if (b == 0) return HALO_OK;
+    return field == 0 ? ntt_dev_impl<0>(d_data, log_n, b, inverse, coset_offset_or_null)
+                      : ntt_dev_impl<1>(d_data, log_n, b, inverse, coset_offset_or_null);
+}
+int halo_ntt(int field, uint64_t* data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK((field == 0 || field == 1) && (data || b == 0) && log_n <= 30, HALO_EINVAL, "ntt: bad argument");
+    if (b == 0) return HALO_OK;
+    return field == 0 ? ntt_host_impl<0>(data, log_n, b, inverse, coset_offset_or_null)
+                      : ntt_host_impl<1>(data, log_n, b, inverse, coset_offset_or_null);
+}
+int halo_poly_evaluate(int field, const uint64_t* coeffs, size_t len, unsigned log_n, uint64_t* out_evals) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK((field == 0 || field == 1) && (coeffs || len == 0) && out_evals && log_n <= 30, HALO_EINVAL, "poly_evaluate: bad argument");
+    return field == 0 ? poly_evaluate_impl<0>(coeffs, len, log_n, out_evals) : poly_evaluate_impl<1>(coeffs, len, log_n, out_evals);
+}
 }  // extern "C"

@@ -171,7 +171,7 @@ __global__ void __launch_bounds__(256) msm_scatter(const Fe<SF>* __restrict__ sc
 //    run of slots in the partial-result array.
 // ---------------------------------------------------------------------------------------------------------
 struct TaskMeta { u32 ntasks, npartial, nmulti, pad; };
-constexpr int MSM_MAX_L = 64;
+constexpr int MSM_MAX_L = 128;
 
 __global__ void __launch_bounds__(256) msm_task_hist(const u32* __restrict__ counts, size_t nb, u32 L,
                                                      u32* __restrict__ hist, TaskMeta* __restrict__ meta,
@@ -343,7 +343,7 @@ static MsmPlan make_plan(size_t k, size_t nbatch) {
     p.nb = p.B * p.nwt;
     // long tasks amortise the bucket write; short tasks give small problems enough threads
     size_t work = k * p.nwt;
-    p.L = work >= ((size_t)1 << 23) ? 64 : work >= ((size_t)1 << 20) ? 32 : 16;
+    p.L = work >= ((size_t)1 << 23) ? 128 : work >= ((size_t)1 << 20) ? 32 : 16;
     p.max_tasks = p.nb + work / p.L + 1;
     p.max_partial = 2 * (work / p.L) + 2;
     return p;
@@ -370,11 +370,11 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     uint2* tasks;
     TaskMeta* meta;
     XYZZ<C> *buckets, *partial, *lvl[4], *winsum;
-    // counts | hist (MSM_MAX_L+1, padded to 128) | meta share one zero-filled allocation
-    const size_t zero_words = P.nb + 128 + 4;
+    // counts | hist (MSM_MAX_L+1, padded to 256) | meta share one zero-filled allocation
+    const size_t zero_words = P.nb + 256 + 4;
     if (int e = ws_get(WS_COUNTS, zero_words * 4, (void**)&counts)) return e;
     hist = counts + P.nb;
-    meta = (TaskMeta*)(hist + 128);
+    meta = (TaskMeta*)(hist + 256);
     const size_t nblk = (P.nb + 1023) / 1024;
     if (int e = ws_get(WS_OFFSETS, (2 * P.nb + nblk + 1) * 4, (void**)&offsets)) return e;
     cursor = offsets + P.nb;
@@ -418,7 +418,7 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
         u32 n_in = (u32)P.B;
         int log2M = 0, lv = 0;
         while (n_in > 1) {
-            const u32 S0 = R.tune[1] > 0 ? (u32)R.tune[1] : 8u;        // group size (power of two)
+            const u32 S0 = R.tune[1] > 0 ? (u32)R.tune[1] : 4u;        // group size (power of two)
             const u32 S = n_in >= S0 ? S0 : n_in;
             const u32 n_out = n_in / S;
             const size_t groups = (size_t)n_out * P.nwt;

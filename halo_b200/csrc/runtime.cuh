@@ -42,6 +42,8 @@ struct Runtime {
     const char* prof_name[PROF_MAX] = {};
     int prof_n = 0;
     unsigned long long launches = 0;
+    void* ntt_tw[2] = {nullptr, nullptr};   // twiddle table per field: omega_max^k, k < 2^(logmax-1)
+    int ntt_logmax[2] = {0, 0};
     std::recursive_mutex mu;
     std::string err;
 };

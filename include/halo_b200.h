@@ -70,6 +70,18 @@ int halo_set_tuning(int key, int value);
 /* window width override for experiments (0 = automatic) */
 int halo_msm_set_window(int c);
 
+/* ---- NTT / iNTT  ≙ Evals::from_poly* / Evals::interpolate*  (crates/group/src/poly.rs:56-64,133-139) and the direct
+ * evaluate_over_domain_by_ref / interpolate calls at crates/plonk/src/plonk/protocol.rs:82-106,140-141,158-159,195.
+ * data: b vectors of 2^log_n elements of `field`, transformed in place, natural order in and out; the inverse
+ * includes the factor N^-1.  coset_offset (4 words, Montgomery) evaluates on g*<omega> / interpolates from it
+ * (API addition: the reference has no coset call site); NULL = the plain subgroup domain.
+ * omega_N = (5^((p-1)/2^32))^(2^(32-log_n)) as in ark-ff (pinned by ivc/mod.rs:56,113). */
+int halo_ntt(int field, uint64_t* data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null);
+int halo_ntt_dev(int field, void* d_data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null);
+/* evals[i] = p(omega^i) for a coefficient vector of ANY length: zero-padded when len < N, reduced modulo X^N - 1
+ * when len > N, as ark-poly's evaluate_over_domain_by_ref does (protocol.rs:140-141 relies on the latter). */
+int halo_poly_evaluate(int field, const uint64_t* coeffs, size_t len, unsigned log_n, uint64_t* out_evals);
+
 /* ---- benchmarks of the arithmetic itself (denominator of the integer roofline) -------------------------- */
 /* Runs `iters` dependent Montgomery multiplications in each of blocks*threads threads (4 independent chains per
  * thread); returns elapsed milliseconds measured with CUDA events in *ms and a checksum in out[4]. */
