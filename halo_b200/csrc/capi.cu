@@ -48,9 +48,20 @@ int prof_mark(const char* name) {
     return HALO_OK;
 }
 
-template <int C> int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, uint64_t* out_xyz);
+template <int C> int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, uint64_t* out_xyz,
+                                ptrdiff_t base_stride);
 template <int F> int ntt_device(Fe<F>* data, Fe<F>* out, int log_n, size_t batch, bool inverse, const Fe<F>* coset);
 template <int F> int ntt_fold_device(const Fe<F>* coeffs, size_t len, int log_n, Fe<F>* out);
+template <int C> int pcdl_commit(const uint64_t*, size_t, size_t, const uint64_t*, uint64_t*);
+template <int C> int pcdl_open(const uint64_t*, size_t, const uint64_t*, size_t, const uint64_t*, const uint64_t*, const uint64_t*,
+                               const uint64_t*, const uint64_t*, uint64_t*, uint64_t*, bool);
+template <int C> int pcdl_succinct_check(const uint64_t*, uint64_t*, uint64_t*);
+template <int C> int pcdl_check(const uint64_t*);
+template <int C> int acc_prover(const uint64_t*, size_t, uint64_t*);
+template <int C> int acc_verifier(const uint64_t*, size_t, const uint64_t*);
+template <int S> int hpoly_coeffs(const uint64_t*, const uint64_t*, size_t, unsigned, uint64_t*);
+template <int C> int hpoly_commit_words(const uint64_t*, unsigned, uint64_t*);
+template <int S> void hpoly_eval_words(const uint64_t*, unsigned, const uint64_t*, uint64_t*);
 
 // ---- synthetic inputs: P_i = k_i * G with k_i = splitmix64(seed, i) | 1  (distinct with overwhelming probability) ----
 __host__ __device__ inline u64 splitmix64(u64 x) {
@@ -182,7 +193,7 @@ static int msm_proj_impl(const uint64_t* bases_xyz, const uint64_t* scalars, siz
 
 extern "C" {
 
-const char* halo_last_error(void) { return rt().err.c_str(); }
+const char* halo_last_error(void) { return last_err().c_str(); }
 
 int halo_init(int device) {
     LOCK();
@@ -256,8 +267,8 @@ int halo_pp_load(int curve, const uint64_t* gs_xy, size_t n, const uint64_t s_xy
     if (e == cudaSuccess) e = cudaMemcpyAsync(&bad, d_bad, 4, cudaMemcpyDeviceToHost, R.stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(R.stream);
     if (d_bad) cudaFree(d_bad);
-    if (e != cudaSuccess) { cudaFree(d); R.err = std::string("pp_load: ") + cudaGetErrorString(e); return HALO_ECUDA; }
-    if (bad) { cudaFree(d); R.err = "pp_load: generator not on the curve"; return HALO_EINVAL; }
+    if (e != cudaSuccess) { cudaFree(d); last_err() = std::string("pp_load: ") + cudaGetErrorString(e); return HALO_ECUDA; }
+    if (bad) { cudaFree(d); last_err() = "pp_load: generator not on the curve"; return HALO_EINVAL; }
     P.d_gs = d; P.n = n;
     memcpy(P.s_xy, s_xy, 64); memcpy(P.h_xy, h_xy, 64);
     return HALO_OK;
@@ -325,7 +336,7 @@ int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void*
         bases = (const char*)R.pp[curve].d_gs;
     }
     bases += base_off * 64;
-    return curve == 0 ? msm_device<0>(bases, d_scalars, k, 1, out_xyz) : msm_device<1>(bases, d_scalars, k, 1, out_xyz);
+    return curve == 0 ? msm_device<0>(bases, d_scalars, k, 1, out_xyz, 0) : msm_device<1>(bases, d_scalars, k, 1, out_xyz, 0);
 }
 
 int halo_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k, size_t b,
@@ -340,7 +351,7 @@ int halo_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const
         bases = (const char*)R.pp[curve].d_gs;
     }
     bases += base_off * 64;
-    return curve == 0 ? msm_device<0>(bases, d_scalars, k, b, out_xyz) : msm_device<1>(bases, d_scalars, k, b, out_xyz);
+    return curve == 0 ? msm_device<0>(bases, d_scalars, k, b, out_xyz, 0) : msm_device<1>(bases, d_scalars, k, b, out_xyz, 0);
 }
 
 int halo_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_t* scalars, size_t k, uint64_t out_xyz[12]) {
@@ -511,5 +522,64 @@ int halo_poly_evaluate(int field, const uint64_t* coeffs, size_t len, unsigned l
     LOCK(); NEED_INIT();
     HALO_CHECK((field == 0 || field == 1) && (coeffs || len == 0) && out_evals && log_n <= 30, HALO_EINVAL, "poly_evaluate: bad argument");
     return field == 0 ? poly_evaluate_impl<0>(coeffs, len, log_n, out_evals) : poly_evaluate_impl<1>(coeffs, len, log_n, out_evals);
+}
+}  // extern "C"
+
+// ---- PC_DL / AS_DL ----
+#define NEED_CURVE() HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)")
+extern "C" {
+size_t halo_instance_words(unsigned lg_n) { return 24 * (size_t)lg_n + 54; }
+size_t halo_proof_words(unsigned lg_n) { return 24 * (size_t)lg_n + 33; }
+
+int halo_pcdl_commit(int curve, const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w_or_null, uint64_t out_xyz[12]) {
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    HALO_CHECK(out_xyz && (coeffs || len == 0), HALO_EINVAL, "pcdl_commit: null pointer");
+    return curve == 0 ? pcdl_commit<0>(coeffs, len, d, w_or_null, out_xyz) : pcdl_commit<1>(coeffs, len, d, w_or_null, out_xyz);
+}
+int halo_pcdl_open(int curve, const uint64_t* coeffs, size_t len, const uint64_t C_xyz[12], size_t d, const uint64_t z[4],
+                   const uint64_t* v_or_null, const uint64_t* w_or_null, const uint64_t* hide_q, const uint64_t* hide_wbar,
+                   uint64_t* out_proof, uint64_t* out_v_or_null) {
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    HALO_CHECK(C_xyz && z && out_proof && (coeffs || len == 0), HALO_EINVAL, "pcdl_open: null pointer");
+    return curve == 0 ? pcdl_open<0>(coeffs, len, C_xyz, d, z, v_or_null, w_or_null, hide_q, hide_wbar, out_proof, out_v_or_null, false)
+                      : pcdl_open<1>(coeffs, len, C_xyz, d, z, v_or_null, w_or_null, hide_q, hide_wbar, out_proof, out_v_or_null, false);
+}
+int halo_pcdl_succinct_check(int curve, const uint64_t* instance, uint64_t* out_xis_or_null, uint64_t* out_U_or_null) {
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    HALO_CHECK(instance, HALO_EINVAL, "succinct_check: null pointer");
+    return curve == 0 ? pcdl_succinct_check<0>(instance, out_xis_or_null, out_U_or_null)
+                      : pcdl_succinct_check<1>(instance, out_xis_or_null, out_U_or_null);
+}
+int halo_pcdl_check(int curve, const uint64_t* instance) {
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    HALO_CHECK(instance, HALO_EINVAL, "check: null pointer");
+    return curve == 0 ? pcdl_check<0>(instance) : pcdl_check<1>(instance);
+}
+int halo_acc_prover(int curve, const uint64_t* instances, size_t m, uint64_t* out_acc) {
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    HALO_CHECK(out_acc, HALO_EINVAL, "acc_prover: null pointer");
+    return curve == 0 ? acc_prover<0>(instances, m, out_acc) : acc_prover<1>(instances, m, out_acc);
+}
+int halo_acc_verifier(int curve, const uint64_t* instances, size_t m, const uint64_t* acc) {
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    HALO_CHECK(acc, HALO_EINVAL, "acc_verifier: null pointer");
+    return curve == 0 ? acc_verifier<0>(instances, m, acc) : acc_verifier<1>(instances, m, acc);
+}
+int halo_acc_decider(int curve, const uint64_t* acc) { return halo_pcdl_check(curve, acc); }
+int halo_hpoly_commit(int curve, const uint64_t* xis, size_t lg_n, uint64_t out_xyz[12]) {
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    HALO_CHECK(xis && out_xyz && lg_n <= 30, HALO_EINVAL, "hpoly_commit: bad argument");
+    HALO_CHECK(rt().pp[curve].n >= ((size_t)1 << lg_n), HALO_EPARAMS, "hpoly_commit: resident generators missing or too few");
+    return curve == 0 ? hpoly_commit_words<0>(xis, (unsigned)lg_n, out_xyz) : hpoly_commit_words<1>(xis, (unsigned)lg_n, out_xyz);
+}
+int halo_acc_hpoly(int field, const uint64_t* xis, const uint64_t* alphas, size_t m, size_t lg_n, uint64_t* out_coeffs) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK((field == 0 || field == 1) && xis && alphas && out_coeffs && lg_n <= 30, HALO_EINVAL, "acc_hpoly: bad argument");
+    return field == 0 ? hpoly_coeffs<0>(xis, alphas, m, (unsigned)lg_n, out_coeffs) : hpoly_coeffs<1>(xis, alphas, m, (unsigned)lg_n, out_coeffs);
+}
+int halo_hpoly_eval(int field, const uint64_t* xis, size_t lg_n, const uint64_t z[4], uint64_t out[4]) {
+    HALO_CHECK((field == 0 || field == 1) && xis && z && out, HALO_EINVAL, "hpoly_eval: bad argument");
+    if (field == 0) hpoly_eval_words<0>(xis, (unsigned)lg_n, z, out); else hpoly_eval_words<1>(xis, (unsigned)lg_n, z, out);
+    return HALO_OK;
 }
 }  // extern "C"

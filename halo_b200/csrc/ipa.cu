@@ -1,0 +1,708 @@
+// PC_DL (inner-product-argument polynomial commitment) and AS_DL (its accumulation scheme) on sm_100a.
+//
+// Stands in for
+//   crates/accumulation/src/pcdl.rs:266-287   commit
+//   crates/accumulation/src/pcdl.rs:326-473   open_without_eval / open        (the lg n fold rounds run on the GPU)
+//   crates/accumulation/src/pcdl.rs:483-554   succinct_check                  (O(lg n) host work)
+//   crates/accumulation/src/pcdl.rs:563-583   check                           (h(X) expanded + committed on the GPU)
+//   crates/accumulation/src/pcdl.rs:191-233   HPoly::{get_poly, eval}
+//   crates/accumulation/src/acc.rs:71-110,128-217   common_subroutine / prover / verifier / decider
+//   crates/group/src/group.rs:43-66           scalar_dot / construct_powers (device kernels below)
+// Division of labour: everything whose size is n (generators, coefficient and power vectors, h(X)) lives in HBM and
+// is touched only by kernels; the Fiat-Shamir transcript and the O(lg n) point arithmetic of the verifier stay on
+// the host, which receives two points per round and sends one challenge back.
+#include "runtime.cuh"
+#include "transcript.cuh"
+#include <algorithm>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+extern "C" int halo_msm_proj(int, const uint64_t*, const uint64_t*, size_t, uint64_t*);
+
+namespace halo {
+
+template <int F> __device__ __forceinline__ Fe<F> g_ld(const Fe<F>* p) {
+    Fe<F> r;
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    uint4 a = q[0], b = q[1];
+    r.l[0] = a.x; r.l[1] = a.y; r.l[2] = a.z; r.l[3] = a.w;
+    r.l[4] = b.x; r.l[5] = b.y; r.l[6] = b.z; r.l[7] = b.w;
+    return r;
+}
+template <int F> __device__ __forceinline__ void g_st(Fe<F>* p, const Fe<F>& v) {
+    uint4* q = reinterpret_cast<uint4*>(p);
+    q[0] = make_uint4(v.l[0], v.l[1], v.l[2], v.l[3]);
+    q[1] = make_uint4(v.l[4], v.l[5], v.l[6], v.l[7]);
+}
+
+struct Bits256 { u32 w[8]; };
+
+// ---------------------------------------------------------------------------------------------------------
+// construct_powers (group.rs:58-66): out[j] = c0 * z^j, 16 consecutive powers per thread
+// ---------------------------------------------------------------------------------------------------------
+template <int F>
+__global__ void __launch_bounds__(128) ipa_powers_kernel(Fe<F>* __restrict__ out, size_t n, Fe<F> z, Fe<F> c0) {
+    size_t lo = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) * 16;
+    if (lo >= n) return;
+    u32 e[8] = {(u32)lo, (u32)(lo >> 32), 0, 0, 0, 0, 0, 0};
+    Fe<F> w = fe_mul<F>(fe_pow<F>(z, e, 40), c0);
+    size_t hi = lo + 16 < n ? lo + 16 : n;
+    for (size_t k = lo; k < hi; ++k) { g_st(out + k, w); w = fe_mul<F>(w, z); }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// scalar_dot (group.rs:43-45), both dot products of a round in one pass:
+//   part[2*blk] = sum_j a_hi[j]*b_lo[j]  (<r(c), l(z)>),  part[2*blk+1] = sum_j a_lo[j]*b_hi[j]  (<l(c), r(z)>)
+// With b == nullptr computes plain sums (used for reductions).  The host adds the per-block partials.
+// ---------------------------------------------------------------------------------------------------------
+template <int F>
+__global__ void __launch_bounds__(256) ipa_dots_kernel(const Fe<F>* __restrict__ a, const Fe<F>* __restrict__ b, size_t m,
+                                                       Fe<F>* __restrict__ part) {
+    __shared__ Fe<F> sh[2][256];
+    Fe<F> s0 = fe_zero<F>(), s1 = fe_zero<F>();
+    for (size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x; j < m; j += (size_t)gridDim.x * blockDim.x) {
+        s0 = fe_add<F>(s0, fe_mul<F>(g_ld(a + m + j), g_ld(b + j)));
+        s1 = fe_add<F>(s1, fe_mul<F>(g_ld(a + j), g_ld(b + m + j)));
+    }
+    sh[0][threadIdx.x] = s0; sh[1][threadIdx.x] = s1;
+    __syncthreads();
+    for (int d = 128; d >= 1; d >>= 1) {
+        if ((int)threadIdx.x < d) {
+            sh[0][threadIdx.x] = fe_add<F>(sh[0][threadIdx.x], sh[0][threadIdx.x + d]);
+            sh[1][threadIdx.x] = fe_add<F>(sh[1][threadIdx.x], sh[1][threadIdx.x + d]);
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { g_st(part + 2 * blockIdx.x, sh[0][0]); g_st(part + 2 * blockIdx.x + 1, sh[1][0]); }
+}
+// single dot product <a, b> over n elements -> per-block partials
+template <int F>
+__global__ void __launch_bounds__(256) ipa_dot1_kernel(const Fe<F>* __restrict__ a, const Fe<F>* __restrict__ b, size_t n,
+                                                       Fe<F>* __restrict__ part) {
+    __shared__ Fe<F> sh[256];
+    Fe<F> s = fe_zero<F>();
+    for (size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x; j < n; j += (size_t)gridDim.x * blockDim.x)
+        s = fe_add<F>(s, fe_mul<F>(g_ld(a + j), g_ld(b + j)));
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int d = 128; d >= 1; d >>= 1) {
+        if ((int)threadIdx.x < d) sh[threadIdx.x] = fe_add<F>(sh[threadIdx.x], sh[threadIdx.x + d]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) g_st(part + blockIdx.x, sh[0]);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// one fold round (pcdl.rs:427-435), all three vectors in one kernel:
+//   gs[j] = (gs[j] + xi * gs[m+j]).into_affine()      (uniform double-and-add: every lane has the same xi)
+//   cs[j] += xi^-1 * cs[m+j]        zs[j] += xi * zs[m+j]
+// ---------------------------------------------------------------------------------------------------------
+template <int C>
+__global__ void __launch_bounds__(128, 4) ipa_fold_kernel(Affine<C>* __restrict__ gs, Fe<CurveTraits<C>::SCALAR>* __restrict__ cs,
+                                                          Fe<CurveTraits<C>::SCALAR>* __restrict__ zs, size_t m,
+                                                          Bits256 xi_bits, Fe<CurveTraits<C>::SCALAR> xi,
+                                                          Fe<CurveTraits<C>::SCALAR> xi_inv) {
+    constexpr int S = CurveTraits<C>::SCALAR;
+    size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (j >= m) return;
+    g_st(cs + j, fe_add<S>(g_ld(cs + j), fe_mul<S>(g_ld(cs + m + j), xi_inv)));
+    g_st(zs + j, fe_add<S>(g_ld(zs + j), fe_mul<S>(g_ld(zs + m + j), xi)));
+    Affine<C> P;
+    P.x = g_ld(&gs[m + j].x); P.y = g_ld(&gs[m + j].y);
+    XYZZ<C> acc = xyzz_identity<C>();
+    for (int b = 254; b >= 0; --b) {
+        acc = xyzz_dbl<C>(acc);
+        if ((xi_bits.w[b >> 5] >> (b & 31)) & 1u) xyzz_madd<C>(acc, P, false);
+    }
+    Affine<C> Q;
+    Q.x = g_ld(&gs[j].x); Q.y = g_ld(&gs[j].y);
+    xyzz_madd<C>(acc, Q, false);
+    Affine<C> r = xyzz_to_affine<C>(acc);
+    g_st(&gs[j].x, r.x); g_st(&gs[j].y, r.y);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// hiding helpers (pcdl.rs:344-366):  p_bar = q * (X - z)  ->  pbar[i] = q[i-1] - z*q[i]  (q has d = n-1 coefficients)
+// and  cs = p + a * p_bar
+// ---------------------------------------------------------------------------------------------------------
+template <int F>
+__global__ void __launch_bounds__(256) ipa_pbar_kernel(const Fe<F>* __restrict__ q, size_t n, Fe<F> z, Fe<F>* __restrict__ pbar) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fe<F> v = i >= 1 ? g_ld(q + i - 1) : fe_zero<F>();
+    if (i + 1 < n) v = fe_sub<F>(v, fe_mul<F>(g_ld(q + i), z));
+    g_st(pbar + i, v);
+}
+template <int F>
+__global__ void __launch_bounds__(256) ipa_axpy_kernel(Fe<F>* __restrict__ y, const Fe<F>* __restrict__ x, size_t n, Fe<F> a) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    g_st(y + i, fe_add<F>(g_ld(y + i), fe_mul<F>(g_ld(x + i), a)));
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// h(X) = prod_{i<lg n} (1 + xi_{lg n - i} X^{2^i})  (pcdl.rs:198-219): coefficient j is the product of the
+// challenges selected by the bits of j.  out[j] (+)= sum_inst alpha_inst * h_inst[j]  (acc.rs:86-92 with m
+// instances; m = 1, alpha = 1 for a single h).  A thread owns 16 consecutive coefficients: the product over the
+// high bits is shared, the 16 low-bit combinations cost one multiplication each.
+// xis: m x (lg_n+1) elements (xis[0] is xi_0, unused by h), alphas: m elements.
+// ---------------------------------------------------------------------------------------------------------
+template <int F>
+__global__ void __launch_bounds__(128) ipa_hpoly_kernel(const Fe<F>* __restrict__ xis, const Fe<F>* __restrict__ alphas,
+                                                        size_t m, int lg_n, Fe<F>* __restrict__ out) {
+    const size_t n = (size_t)1 << lg_n;
+    const size_t base = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) * 16;
+    if (base >= n) return;
+    const int lowbits = lg_n < 4 ? lg_n : 4;
+    const int cnt = 1 << lowbits;
+    Fe<F> acc[16];
+#pragma unroll
+    for (int t = 0; t < 16; ++t) acc[t] = fe_zero<F>();
+    for (size_t inst = 0; inst < m; ++inst) {
+        const Fe<F>* x = xis + inst * (size_t)(lg_n + 1);
+        Fe<F> hi = g_ld(alphas + inst);
+        for (int b = lowbits; b < lg_n; ++b)
+            if ((base >> b) & 1) hi = fe_mul<F>(hi, g_ld(x + (lg_n - b)));
+        // low 4 bits: v[t] for t = 0..15 built by doubling, v[t | 2^b] = v[t] * xi_{lg n - b}
+        Fe<F> v[16];
+        v[0] = hi;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            if (b < lowbits) {
+                Fe<F> xb = g_ld(x + (lg_n - b));
+#pragma unroll
+                for (int t = 0; t < (1 << b); ++t) v[t | (1 << b)] = fe_mul<F>(v[t], xb);
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < 16; ++t) if (t < cnt) acc[t] = fe_add<F>(acc[t], v[t]);
+    }
+#pragma unroll
+    for (int t = 0; t < 16; ++t) if (t < cnt) g_st(out + base + t, acc[t]);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// host-side group helpers (O(lg n) work only)
+// ---------------------------------------------------------------------------------------------------------
+template <int C> int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, uint64_t* out_xyz,
+                                ptrdiff_t base_stride);
+
+template <int C>
+struct Host {
+    static constexpr int S = CurveTraits<C>::SCALAR, B = CurveTraits<C>::BASE;
+    typedef Fe<S> SF;
+    typedef XYZZ<C> Pt;
+
+    static Pt from_words(const uint64_t* w) { Jac<C> j; memcpy(&j, w, 96); return jac_to_xyzz<C>(j); }
+    static void to_words(const Pt& p, uint64_t* w) { Jac<C> j = xyzz_to_jac<C>(p); memcpy(w, &j, 96); }
+    static Pt from_affine_words(const uint64_t* w) { Affine<C> a; memcpy(&a, w, 64); return xyzz_from_affine<C>(a); }
+    static SF scalar(const uint64_t* w) { SF s; memcpy(&s, w, 32); return s; }
+    static void put_scalar(const SF& s, uint64_t* w) { memcpy(w, &s, 32); }
+    static Bits256 bits(const SF& k) { SF c = fe_to_canonical<S>(k); Bits256 b; memcpy(b.w, c.l, 32); return b; }
+    static Pt mul(const Pt& p, const SF& k) { Bits256 b = bits(k); return xyzz_mul_bits<C>(p, b.w, 255); }
+    static Pt add(Pt a, const Pt& b) { xyzz_add<C>(a, b); return a; }
+    static Pt neg(Pt a) { a.Y = fe_neg<B>(a.Y); return a; }
+    static bool scalar_is_valid(const SF& s) {           // canonical limbs below the modulus
+        for (int i = 7; i >= 0; --i) { u32 p = modulus_limb<S>(i); if (s.l[i] != p) return s.l[i] < p; }
+        return false;
+    }
+};
+
+// fixed-base table for the many multiplications by H' inside one opening: T[i][d-1] = d * 16^i * P
+template <int C>
+struct FixedBase {
+    typedef Host<C> H;
+    std::vector<typename H::Pt> tab;
+    explicit FixedBase(const typename H::Pt& P) : tab(64 * 15) {
+        typename H::Pt base = P;
+        for (int i = 0; i < 64; ++i) {
+            tab[i * 15] = base;
+            for (int d = 2; d <= 15; ++d) tab[i * 15 + d - 1] = H::add(tab[i * 15 + d - 2], base);
+            base = H::add(tab[i * 15 + 14], base);       // 16 * base
+        }
+    }
+    typename H::Pt mul(const typename H::SF& k) const {
+        Bits256 b = H::bits(k);
+        typename H::Pt acc = xyzz_identity<C>();
+        for (int i = 0; i < 64; ++i) {
+            u32 d = (b.w[i >> 3] >> ((i & 7) * 4)) & 15u;
+            if (d) xyzz_add<C>(acc, tab[i * 15 + d - 1]);
+        }
+        return acc;
+    }
+};
+
+static inline unsigned ilog2(size_t n) { unsigned l = 0; while (((size_t)1 << (l + 1)) <= n) ++l; return l; }
+static inline size_t proof_words(unsigned lg_n) { return 24 * (size_t)lg_n + 33; }
+static inline size_t instance_words(unsigned lg_n) { return 24 * (size_t)lg_n + 54; }
+
+// trailing zero coefficients do not count (ark-poly's DensePolynomial strips them)
+static size_t strip_len(const uint64_t* coeffs, size_t len) {
+    while (len > 0 && !(coeffs[4 * len - 1] | coeffs[4 * len - 2] | coeffs[4 * len - 3] | coeffs[4 * len - 4])) --len;
+    return len;
+}
+
+// sum of `count` per-block partials (device) -> host element
+template <int F>
+static int sum_partials(const Fe<F>* d_part, size_t count, Fe<F>* out, int nout) {
+    Runtime& R = rt();
+    void* h;
+    if (int e = pinned_get(count * nout * 32, &h)) return e;
+    Fe<F>* hp = (Fe<F>*)h;
+    HALO_CUDA(cudaMemcpyAsync(hp, d_part, count * nout * 32, cudaMemcpyDeviceToHost, R.stream));
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
+    for (int o = 0; o < nout; ++o) {
+        Fe<F> s = fe_zero<F>();
+        for (size_t i = 0; i < count; ++i) s = fe_add<F>(s, hp[i * nout + o]);
+        out[o] = s;
+    }
+    return HALO_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// pcdl::commit (pcdl.rs:275-287) = pedersen::commit(w, Gs[0..n], coeffs) (pedersen.rs:7-27)
+// ---------------------------------------------------------------------------------------------------------
+template <int C>
+static int commit_dev(const void* d_coeffs, size_t len, const typename Host<C>::SF* w, typename Host<C>::Pt* out) {
+    typedef Host<C> H;
+    Runtime& R = rt();
+    uint64_t xyz[12];
+    if (int e = msm_device<C>(R.pp[C].d_gs, d_coeffs, len, 1, xyz, 0)) return e;
+    *out = H::from_words(xyz);
+    if (w) *out = H::add(H::mul(H::from_affine_words(R.pp[C].s_xy), *w), *out);
+    return HALO_OK;
+}
+
+template <int C>
+int pcdl_commit(const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w, uint64_t* out_xyz) {
+    typedef Host<C> H;
+    constexpr int S = H::S;
+    Runtime& R = rt();
+    const size_t n = d + 1;
+    len = strip_len(coeffs, len);
+    HALO_CHECK((n & (n - 1)) == 0, HALO_EINVAL, "commit: n is not a power of two");
+    HALO_CHECK(len <= n, HALO_EINVAL, "commit: p_deg <= d violated");
+    HALO_CHECK(R.pp[C].n > 0, HALO_EPARAMS, "commit: public parameters not loaded");
+    HALO_CHECK(d <= R.pp[C].n - 1, HALO_EINVAL, "commit: d <= D violated");
+    void* d_c = nullptr;
+    if (len) {
+        if (int e = ws_get(WS_SCALARS, len * 32, &d_c)) return e;
+        HALO_CUDA(cudaMemcpyAsync(d_c, coeffs, len * 32, cudaMemcpyHostToDevice, R.stream));
+    }
+    typename H::SF ws;
+    if (w) ws = H::scalar(w);
+    typename H::Pt out;
+    if (int e = commit_dev<C>(d_c, len, w ? &ws : nullptr, &out)) return e;
+    H::to_words(out, out_xyz);
+    (void)S;
+    return HALO_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// pcdl::open / open_without_eval (pcdl.rs:326-473)
+//   proof layout (u64 words): Ls[12 lg n] Rs[12 lg n] U[12] c[4] hiding[1] C_bar[12] w_prime[4]
+// ---------------------------------------------------------------------------------------------------------
+template <int C>
+int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t d, const uint64_t* z_w,
+              const uint64_t* v_w, const uint64_t* w_w, const uint64_t* hide_q, const uint64_t* hide_wbar,
+              uint64_t* out_proof, uint64_t* out_v, bool coeffs_resident = false) {
+    // coeffs_resident: the n zero-padded coefficients are already in the WS_IPA_C workspace (acc::prover's h(X))
+    typedef Host<C> H;
+    typedef typename H::SF SF;
+    typedef typename H::Pt Pt;
+    constexpr int S = H::S;
+    Runtime& R = rt();
+    cudaStream_t st = R.stream;
+    const size_t n = d + 1;
+    HALO_CHECK(n > 1 && (n & (n - 1)) == 0, HALO_EINVAL, "open: n is not a power of two (or n <= 1)");
+    if (!coeffs_resident) len = strip_len(coeffs, len);
+    HALO_CHECK(len <= n, HALO_EINVAL, "open: p.degree() <= d violated");
+    HALO_CHECK(R.pp[C].n > 0, HALO_EPARAMS, "open: public parameters not loaded");
+    HALO_CHECK(d <= R.pp[C].n - 1, HALO_EINVAL, "open: d <= pp.D violated");
+    HALO_CHECK(!w_w || (hide_q && hide_wbar), HALO_EINVAL, "open: hiding needs the prover's randomness (q, w_bar)");
+    const unsigned lg_n = ilog2(n);
+    const SF z = H::scalar(z_w);
+
+    Affine<C>* gs; SF *cs, *zs, *part, *tmp;
+    if (int e = ws_get(WS_IPA_G, n * 64, (void**)&gs)) return e;
+    if (int e = ws_get(WS_IPA_C, n * 32, (void**)&cs)) return e;
+    if (int e = ws_get(WS_IPA_Z, n * 32, (void**)&zs)) return e;
+    if (int e = ws_get(WS_IPA_T0, 2 * 256 * 32 + 64, (void**)&part)) return e;
+    // cs = coefficients of p, zero-padded to n (pcdl.rs:392-393)
+    if (!coeffs_resident) {
+        if (len) HALO_CUDA(cudaMemcpyAsync(cs, coeffs, len * 32, cudaMemcpyHostToDevice, st));
+        if (len < n) HALO_CUDA(cudaMemsetAsync(cs + len, 0, (n - len) * 32, st));
+    }
+    // zs = (1, z, ..., z^(n-1)) (pcdl.rs:395)
+    ipa_powers_kernel<S><<<(unsigned)((n / 16 + 128) / 128), 128, 0, st>>>(zs, n, z, fe_one<S>());
+    R.launches += 1;
+    HALO_CUDA(cudaGetLastError());
+
+    // v = p(z) = <cs, zs> when the caller did not supply it (pcdl::open, pcdl.rs:471)
+    SF v;
+    if (v_w) v = H::scalar(v_w);
+    else {
+        const int g = (int)std::min<size_t>(256, (n + 255) / 256);
+        ipa_dot1_kernel<S><<<g, 256, 0, st>>>(cs, zs, n, part);
+        R.launches += 1;
+        if (int e = sum_partials<S>(part, g, &v, 1)) return e;
+    }
+    if (out_v) H::put_scalar(v, out_v);
+
+    Transcript<C> tr(LABEL_PCDL);
+    Pt Cp = H::from_words(C_xyz);
+    const unsigned L = lg_n;
+    uint64_t* o_hiding = out_proof + 24 * L + 16;
+    memset(o_hiding, 0, 17 * 8);
+    if (w_w) {
+        // p_bar = q (X - z), C_bar = commit(p_bar; w_bar), a = rho(C, C_bar, z, v), p' = p + a p_bar,
+        // w' = w + a w_bar, C' = C + a C_bar - w' S   (pcdl.rs:344-371)
+        const SF w = H::scalar(w_w), wbar = H::scalar(hide_wbar);
+        SF* q;
+        if (int e = ws_get(WS_IPA_T1, 2 * n * 32, (void**)&q)) return e;
+        tmp = q + n;
+        HALO_CUDA(cudaMemcpyAsync(q, hide_q, d * 32, cudaMemcpyHostToDevice, st));
+        ipa_pbar_kernel<S><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(q, n, z, tmp);
+        R.launches += 1;
+        Pt Cbar;
+        if (int e = commit_dev<C>(tmp, n, &wbar, &Cbar)) return e;
+        tr.absorb_point(Cp); tr.absorb_point(Cbar);
+        tr.absorb_scalar(z); tr.absorb_scalar(v);
+        const SF a = tr.challenge();
+        ipa_axpy_kernel<S><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(cs, tmp, n, a);
+        R.launches += 1;
+        const SF wprime = fe_add<S>(fe_mul<S>(wbar, a), w);
+        Cp = H::add(H::add(Cp, H::mul(Cbar, a)), H::neg(H::mul(H::from_affine_words(R.pp[C].s_xy), wprime)));
+        o_hiding[0] = 1;
+        H::to_words(Cbar, o_hiding + 1);
+        H::put_scalar(wprime, o_hiding + 13);
+    }
+    tr.absorb_point(Cp);
+    tr.absorb_scalar(z); tr.absorb_scalar(v);
+    SF xi = tr.challenge();
+    FixedBase<C> Hp(H::mul(H::from_affine_words(R.pp[C].h_xy), xi));
+
+    // gs = pp.Gs[0..n] (pcdl.rs:394)
+    HALO_CUDA(cudaMemcpyAsync(gs, R.pp[C].d_gs, n * 64, cudaMemcpyDeviceToDevice, st));
+
+    size_t m = n / 2;
+    for (unsigned r = 0; r < lg_n; ++r, m /= 2) {
+        const int g = (int)std::min<size_t>(256, (m + 255) / 256);
+        ipa_dots_kernel<S><<<g, 256, 0, st>>>(cs, zs, m, part);
+        R.launches += 1;
+        SF dots[2];
+        if (int e = sum_partials<S>(part, g, dots, 2)) return e;
+        // one pipeline, two MSMs: [0] = R = <l(c), r(G)>, [1] = L = <r(c), l(G)>  (pcdl.rs:412-418)
+        uint64_t lr[24];
+        if (int e = msm_device<C>(gs + m, cs, m, 2, lr, -(ptrdiff_t)m)) return e;
+        Pt Rp = H::add(H::from_words(lr), Hp.mul(dots[1]));
+        Pt Lp = H::add(H::from_words(lr + 12), Hp.mul(dots[0]));
+        H::to_words(Lp, out_proof + 12 * r);
+        H::to_words(Rp, out_proof + 12 * (L + r));
+        // xi_{i+1} = rho(xi_i, L, R)  (pcdl.rs:421-425)
+        tr.absorb_scalar(xi);
+        tr.absorb_point(Lp); tr.absorb_point(Rp);
+        const SF xi_next = tr.challenge();
+        HALO_CHECK(!fe_is_zero<S>(xi_next), HALO_EINVAL, "open: zero challenge has no inverse");
+        const SF xi_inv = fe_inv<S>(xi_next);
+        xi = xi_next;
+        ipa_fold_kernel<C><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(gs, cs, zs, m, H::bits(xi_next), xi_next, xi_inv);
+        R.launches += 1;
+        HALO_CUDA(cudaGetLastError());
+    }
+    // U = G_(lg n), c = c_(lg n)  (pcdl.rs:441-450)
+    Affine<C> U; SF c;
+    HALO_CUDA(cudaMemcpyAsync(&U, gs, 64, cudaMemcpyDeviceToHost, st));
+    HALO_CUDA(cudaMemcpyAsync(&c, cs, 32, cudaMemcpyDeviceToHost, st));
+    HALO_CUDA(cudaStreamSynchronize(st));
+    H::to_words(xyzz_from_affine<C>(U), out_proof + 24 * L);
+    H::put_scalar(c, out_proof + 24 * L + 12);
+    return HALO_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// HPoly::eval (pcdl.rs:221-233): h(z) = prod_{i<lg n} (1 + xi_{lg n - i} z^{2^i})
+// ---------------------------------------------------------------------------------------------------------
+template <int S>
+static Fe<S> hpoly_eval(const Fe<S>* xis, unsigned lg_n, const Fe<S>& z) {
+    Fe<S> one = fe_one<S>(), v = one, zi = z;
+    for (unsigned i = 0; i < lg_n; ++i) {
+        v = fe_mul<S>(v, fe_add<S>(one, fe_mul<S>(xis[lg_n - i], zi)));
+        zi = fe_sqr<S>(zi);
+    }
+    return v;
+}
+
+// flat instance (u64 words): C[12] d[1] z[4] v[4] | proof (see pcdl_open)
+template <int C>
+struct InstanceView {
+    typedef Host<C> H;
+    const uint64_t* w;
+    size_t d;
+    unsigned lg_n;
+    explicit InstanceView(const uint64_t* words) : w(words), d((size_t)words[12]), lg_n(ilog2((size_t)words[12] + 1)) {}
+    typename H::Pt Cm() const { return H::from_words(w); }
+    typename H::SF z() const { return H::scalar(w + 13); }
+    typename H::SF v() const { return H::scalar(w + 17); }
+    const uint64_t* proof() const { return w + 21; }
+    typename H::Pt Lr(unsigned i) const { return H::from_words(proof() + 12 * i); }
+    typename H::Pt Rr(unsigned i) const { return H::from_words(proof() + 12 * (lg_n + i)); }
+    typename H::Pt U() const { return H::from_words(proof() + 24 * lg_n); }
+    typename H::SF c() const { return H::scalar(proof() + 24 * lg_n + 12); }
+    bool hiding() const { return proof()[24 * lg_n + 16] != 0; }
+    typename H::Pt Cbar() const { return H::from_words(proof() + 24 * lg_n + 17); }
+    typename H::SF wprime() const { return H::scalar(proof() + 24 * lg_n + 29); }
+};
+
+// pcdl::succinct_check (pcdl.rs:483-554).  xis_out: (lg n + 1) elements.  HALO_EREJECT when the verifier rejects.
+template <int C>
+int pcdl_succinct_check(const uint64_t* inst, uint64_t* xis_out, uint64_t* U_out) {
+    typedef Host<C> H;
+    typedef typename H::SF SF;
+    typedef typename H::Pt Pt;
+    constexpr int S = H::S;
+    Runtime& R = rt();
+    InstanceView<C> q(inst);
+    const size_t n = q.d + 1;
+    HALO_CHECK((n & (n - 1)) == 0, HALO_EINVAL, "succinct_check: n is not a power of two");
+    HALO_CHECK(R.pp[C].n > 0, HALO_EPARAMS, "succinct_check: public parameters not loaded");
+    HALO_CHECK(q.d <= R.pp[C].n - 1, HALO_EREJECT, "d was larger than D!");
+    const unsigned lg_n = q.lg_n;
+    const SF z = q.z(), v = q.v();
+    Transcript<C> tr(LABEL_PCDL);
+    Pt Cp = q.Cm();
+    if (q.hiding()) {
+        const Pt Cbar = q.Cbar();
+        tr.absorb_point(Cp); tr.absorb_point(Cbar);
+        tr.absorb_scalar(z); tr.absorb_scalar(v);
+        const SF a = tr.challenge();
+        Cp = H::add(H::add(Cp, H::mul(Cbar, a)), H::neg(H::mul(H::from_affine_words(R.pp[C].s_xy), q.wprime())));
+    }
+    tr.absorb_point(Cp);
+    tr.absorb_scalar(z); tr.absorb_scalar(v);
+    std::vector<SF> xis(lg_n + 1);
+    xis[0] = tr.challenge();
+    const Pt Hp = H::mul(H::from_affine_words(R.pp[C].h_xy), xis[0]);
+    Pt Ci = H::add(Cp, H::mul(Hp, v));
+    for (unsigned i = 0; i < lg_n; ++i) {
+        const Pt Li = q.Lr(i), Ri = q.Rr(i);
+        tr.absorb_scalar(xis[i]);
+        tr.absorb_point(Li); tr.absorb_point(Ri);
+        xis[i + 1] = tr.challenge();
+        HALO_CHECK(!fe_is_zero<S>(xis[i + 1]), HALO_EINVAL, "succinct_check: zero challenge has no inverse");
+        Ci = H::add(Ci, H::add(H::mul(Li, fe_inv<S>(xis[i + 1])), H::mul(Ri, xis[i + 1])));
+    }
+    const SF c = q.c();
+    const SF vprime = fe_mul<S>(c, hpoly_eval<S>(xis.data(), lg_n, z));
+    const Pt rhs = H::add(H::mul(q.U(), c), H::mul(Hp, vprime));
+    HALO_CHECK(xyzz_eq<C>(Ci, rhs), HALO_EREJECT, "C_(log_n) != CM.Commit_Sigma(c || v')");
+    if (xis_out) memcpy(xis_out, xis.data(), (lg_n + 1) * 32);
+    if (U_out) memcpy(U_out, q.proof() + 24 * lg_n, 96);
+    return HALO_OK;
+}
+
+// h(X) coefficients on the device: out[j] = sum_i alphas[i] * h_i[j]; xis/alphas are HOST arrays
+template <int S>
+static int hpoly_expand_dev(const Fe<S>* xis, const Fe<S>* alphas, size_t m, unsigned lg_n, Fe<S>* d_out) {
+    Runtime& R = rt();
+    Fe<S>* d_in;
+    const size_t words = m * (lg_n + 1) + m;
+    if (int e = ws_get(WS_TMP0, words * 32, (void**)&d_in)) return e;
+    HALO_CUDA(cudaMemcpyAsync(d_in, xis, m * (lg_n + 1) * 32, cudaMemcpyHostToDevice, R.stream));
+    HALO_CUDA(cudaMemcpyAsync(d_in + m * (lg_n + 1), alphas, m * 32, cudaMemcpyHostToDevice, R.stream));
+    const size_t n = (size_t)1 << lg_n;
+    ipa_hpoly_kernel<S><<<(unsigned)((n / 16 + 128) / 128), 128, 0, R.stream>>>(d_in, d_in + m * (lg_n + 1), m, (int)lg_n, d_out);
+    R.launches += 1;
+    HALO_CUDA(cudaGetLastError());
+    HALO_CUDA(cudaStreamSynchronize(R.stream));               // xis/alphas may be stack memory of the caller
+    return HALO_OK;
+}
+
+// commit(h) for one challenge vector: the size-n MSM of pcdl::check / acc::decider (pcdl.rs:577-580)
+template <int C>
+static int hpoly_commit(const typename Host<C>::SF* xis, unsigned lg_n, typename Host<C>::Pt* out) {
+    typedef Host<C> H;
+    constexpr int S = H::S;
+    const size_t n = (size_t)1 << lg_n;
+    typename H::SF* d_h;
+    if (int e = ws_get(WS_IPA_C, n * 32, (void**)&d_h)) return e;
+    typename H::SF one = fe_one<S>();
+    if (int e = hpoly_expand_dev<S>(xis, &one, 1, lg_n, d_h)) return e;
+    return commit_dev<C>(d_h, n, nullptr, out);
+}
+
+// pcdl::check (pcdl.rs:563-583) = acc::decider (acc.rs:215-217)
+template <int C>
+int pcdl_check(const uint64_t* inst) {
+    typedef Host<C> H;
+    InstanceView<C> q(inst);
+    std::vector<typename H::SF> xis(q.lg_n + 1);
+    uint64_t U[12];
+    if (int e = pcdl_succinct_check<C>(inst, (uint64_t*)xis.data(), U)) return e;
+    typename H::Pt comm;
+    if (int e = hpoly_commit<C>(xis.data(), q.lg_n, &comm)) return e;
+    HALO_CHECK(xyzz_eq<C>(H::from_words(U), comm), HALO_EREJECT, "U != CM.Commit(ck, h_vec)");
+    return HALO_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// AS_DL (acc.rs:128-217)
+// ---------------------------------------------------------------------------------------------------------
+template <int C>
+struct AccCommon {
+    typedef Host<C> H;
+    typename H::Pt Cbar;
+    size_t d;
+    unsigned lg_n;
+    typename H::SF z;
+    std::vector<typename H::SF> xis;      // m x (lg n + 1)
+    std::vector<typename H::SF> alphas;   // m
+    typename H::SF eval(const typename H::SF& x) const {          // AccumulatedHPolys::eval (acc.rs:95-101)
+        constexpr int S = H::S;
+        typename H::SF v = fe_zero<S>();
+        for (size_t i = 0; i < alphas.size(); ++i)
+            v = fe_add<S>(v, fe_mul<S>(hpoly_eval<S>(xis.data() + i * (lg_n + 1), lg_n, x), alphas[i]));
+        return v;
+    }
+};
+
+// acc::common_subroutine (acc.rs:128-176).  insts: m flat instances of the same d.
+template <int C>
+static int acc_common(const uint64_t* insts, size_t m, AccCommon<C>* out) {
+    typedef Host<C> H;
+    typedef typename H::SF SF;
+    constexpr int S = H::S;
+    HALO_CHECK(m > 0 && insts, HALO_EREJECT, "No instances given");
+    InstanceView<C> first(insts);
+    const size_t d = first.d;
+    const unsigned lg_n = first.lg_n;
+    const size_t iw = instance_words(lg_n);
+    out->d = d; out->lg_n = lg_n;
+    out->xis.resize(m * (lg_n + 1));
+    std::vector<uint64_t> Us(12 * m);
+    // 4. m independent succinct checks (each sequential inside): spread over host threads
+    std::vector<int> rc(m, HALO_OK);
+    std::vector<std::string> why(m);
+    {
+        unsigned nt = (unsigned)std::min<size_t>(m, std::max(1u, std::thread::hardware_concurrency()));
+        auto work = [&](unsigned t) {
+            for (size_t i = t; i < m; i += nt) {
+                const uint64_t* qi = insts + i * iw;
+                if ((size_t)qi[12] != d) { rc[i] = HALO_EREJECT; why[i] = "d_i != d"; continue; }
+                rc[i] = pcdl_succinct_check<C>(qi, (uint64_t*)(out->xis.data() + i * (lg_n + 1)), Us.data() + 12 * i);
+                if (rc[i]) why[i] = last_err();
+            }
+        };
+        if (nt <= 1) work(0);
+        else { std::vector<std::thread> th; for (unsigned t = 0; t < nt; ++t) th.emplace_back(work, t); for (auto& x : th) x.join(); }
+    }
+    for (size_t i = 0; i < m; ++i) if (rc[i]) { last_err() = why[i]; return rc[i]; }
+    // 6. alpha = rho1([h_i, U_i])
+    Transcript<C> tr(LABEL_ASDL);
+    for (const SF& x : out->xis) tr.absorb_scalar(x);
+    for (size_t i = 0; i < m; ++i) tr.absorb_point(H::from_words(Us.data() + 12 * i));
+    const SF alpha = tr.challenge();
+    out->alphas.resize(m);
+    SF cur = fe_one<S>();
+    for (size_t i = 0; i < m; ++i) { out->alphas[i] = cur; cur = fe_mul<S>(cur, alpha); }
+    // 8. C = sum alpha^i U_i  (point_dot, group.rs:53-56)
+    uint64_t Cw[12];
+    if (int e = halo_msm_proj(C, Us.data(), (const uint64_t*)out->alphas.data(), m, Cw)) return e;
+    out->Cbar = H::from_words(Cw);
+    // 9. z = rho1(C, h)
+    out->z = tr.challenge();
+    return HALO_OK;
+}
+
+// acc::prover (acc.rs:178-198): out_acc is a flat instance
+template <int C>
+int acc_prover(const uint64_t* insts, size_t m, uint64_t* out_acc) {
+    typedef Host<C> H;
+    typedef typename H::SF SF;
+    constexpr int S = H::S;
+    AccCommon<C> cs;
+    if (int e = acc_common<C>(insts, m, &cs)) return e;
+    const SF v = cs.eval(cs.z);
+    const size_t n = cs.d + 1;
+    // h(X) = sum alpha^i h_i(X), expanded straight into the opening's coefficient workspace
+    SF* d_h;
+    if (int e = ws_get(WS_IPA_C, n * 32, (void**)&d_h)) return e;
+    if (int e = hpoly_expand_dev<S>(cs.xis.data(), cs.alphas.data(), m, cs.lg_n, d_h)) return e;
+    H::to_words(cs.Cbar, out_acc);
+    out_acc[12] = cs.d;
+    H::put_scalar(cs.z, out_acc + 13);
+    H::put_scalar(v, out_acc + 17);
+    uint64_t Cw[12];
+    H::to_words(cs.Cbar, Cw);
+    // pcdl::open evaluates h(z) itself (pcdl.rs:471); numerically the same value as v
+    return pcdl_open<C>(nullptr, n, Cw, cs.d, (const uint64_t*)&cs.z, nullptr, nullptr, nullptr, nullptr, out_acc + 21,
+                        nullptr, true);
+}
+
+// acc::verifier (acc.rs:200-213)
+template <int C>
+int acc_verifier(const uint64_t* insts, size_t m, const uint64_t* acc) {
+    typedef Host<C> H;
+    constexpr int S = H::S;
+    AccCommon<C> cs;
+    if (int e = acc_common<C>(insts, m, &cs)) return e;
+    InstanceView<C> a(acc);
+    HALO_CHECK(xyzz_eq<C>(cs.Cbar, a.Cm()), HALO_EREJECT, "C_bar' != C_bar");
+    HALO_CHECK(fe_eq<S>(cs.z, a.z()), HALO_EREJECT, "z' = z");
+    HALO_CHECK(cs.d == a.d, HALO_EREJECT, "d' = d");
+    HALO_CHECK(fe_eq<S>(cs.eval(a.z()), a.v()), HALO_EREJECT, "h(z) = v");
+    return HALO_OK;
+}
+
+template int pcdl_commit<0>(const uint64_t*, size_t, size_t, const uint64_t*, uint64_t*);
+template int pcdl_commit<1>(const uint64_t*, size_t, size_t, const uint64_t*, uint64_t*);
+template int pcdl_open<0>(const uint64_t*, size_t, const uint64_t*, size_t, const uint64_t*, const uint64_t*, const uint64_t*,
+                          const uint64_t*, const uint64_t*, uint64_t*, uint64_t*, bool);
+template int pcdl_open<1>(const uint64_t*, size_t, const uint64_t*, size_t, const uint64_t*, const uint64_t*, const uint64_t*,
+                          const uint64_t*, const uint64_t*, uint64_t*, uint64_t*, bool);
+template int pcdl_succinct_check<0>(const uint64_t*, uint64_t*, uint64_t*);
+template int pcdl_succinct_check<1>(const uint64_t*, uint64_t*, uint64_t*);
+template int pcdl_check<0>(const uint64_t*);
+template int pcdl_check<1>(const uint64_t*);
+template int acc_prover<0>(const uint64_t*, size_t, uint64_t*);
+template int acc_prover<1>(const uint64_t*, size_t, uint64_t*);
+template int acc_verifier<0>(const uint64_t*, size_t, const uint64_t*);
+template int acc_verifier<1>(const uint64_t*, size_t, const uint64_t*);
+
+// h(X) coefficient vector for m accumulated instances, returned to the host (≙ AccumulatedHPolys::get_poly)
+template <int S>
+int hpoly_coeffs(const uint64_t* xis, const uint64_t* alphas, size_t m, unsigned lg_n, uint64_t* out) {
+    Runtime& R = rt();
+    const size_t n = (size_t)1 << lg_n;
+    Fe<S>* d_h;
+    if (int e = ws_get(WS_IPA_C, n * 32, (void**)&d_h)) return e;
+    if (int e = hpoly_expand_dev<S>((const Fe<S>*)xis, (const Fe<S>*)alphas, m, lg_n, d_h)) return e;
+    HALO_CUDA(cudaMemcpyAsync(out, d_h, n * 32, cudaMemcpyDeviceToHost, R.stream));
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
+    return HALO_OK;
+}
+template int hpoly_coeffs<0>(const uint64_t*, const uint64_t*, size_t, unsigned, uint64_t*);
+template int hpoly_coeffs<1>(const uint64_t*, const uint64_t*, size_t, unsigned, uint64_t*);
+
+template <int C>
+int hpoly_commit_words(const uint64_t* xis, unsigned lg_n, uint64_t* out_xyz) {
+    typename Host<C>::Pt p;
+    if (int e = hpoly_commit<C>((const typename Host<C>::SF*)xis, lg_n, &p)) return e;
+    Host<C>::to_words(p, out_xyz);
+    return HALO_OK;
+}
+template int hpoly_commit_words<0>(const uint64_t*, unsigned, uint64_t*);
+template int hpoly_commit_words<1>(const uint64_t*, unsigned, uint64_t*);
+
+template <int S>
+void hpoly_eval_words(const uint64_t* xis, unsigned lg_n, const uint64_t* z, uint64_t* out) {
+    Fe<S> zz; memcpy(&zz, z, 32);
+    Fe<S> v = hpoly_eval<S>((const Fe<S>*)xis, lg_n, zz);
+    memcpy(out, &v, 32);
+}
+template void hpoly_eval_words<0>(const uint64_t*, unsigned, const uint64_t*, uint64_t*);
+template void hpoly_eval_words<1>(const uint64_t*, unsigned, const uint64_t*, uint64_t*);
+
+}  // namespace halo

@@ -221,7 +221,8 @@ __global__ void __launch_bounds__(128, 4) msm_accumulate(const Affine<C>* __rest
                                                          const uint2* __restrict__ tasks,
                                                          const TaskMeta* __restrict__ meta, u32 L,
                                                          const u32* __restrict__ pslot,
-                                                         XYZZ<C>* __restrict__ buckets, XYZZ<C>* __restrict__ partial) {
+                                                         XYZZ<C>* __restrict__ buckets, XYZZ<C>* __restrict__ partial,
+                                                         u32 buckets_per_msm, ptrdiff_t base_stride) {
     size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (t >= meta->ntasks) return;
     const uint2 tk = tasks[t];
@@ -230,6 +231,7 @@ __global__ void __launch_bounds__(128, 4) msm_accumulate(const Affine<C>* __rest
     const u32 cnt = min(L, cnt_b - seg * L);
     const u32* my = idx + offsets[b] + seg * L;
     XYZZ<C>* dest = cnt_b > L ? partial + pslot[b] + seg : buckets + b;
+    if (base_stride) bases += (ptrdiff_t)(b / buckets_per_msm) * base_stride;      // MSM j of a batch reads bases + j*stride
     XYZZ<C> acc = xyzz_identity<C>();
     if (cnt) {
         u32 e = __ldg(my);
@@ -361,7 +363,7 @@ static int scan_u32(const u32* in, size_t n, u32* out, u32* out2, u32* bsum /*>=
 // Enqueues the whole device pipeline on the runtime stream and leaves nwt window sums (XYZZ) in *d_winsum_out.
 template <int C>
 static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR>* d_scalars, size_t k,
-                       const MsmPlan& P, XYZZ<C>** d_winsum_out) {
+                       const MsmPlan& P, ptrdiff_t base_stride, XYZZ<C>** d_winsum_out) {
     constexpr int SF = CurveTraits<C>::SCALAR;
     Runtime& R = rt();
     cudaStream_t st = R.stream;
@@ -407,7 +409,8 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     msm_task_emit<<<grid_b, 256, 0, st>>>(counts, P.nb, P.L, hist, tasks);
     prof_mark("tasks");
     msm_accumulate<C><<<(unsigned)((P.max_tasks + 127) / 128), 128, 0, st>>>(d_bases, idx, offsets, counts, tasks, meta,
-                                                                           P.L, pslot, buckets, partial);
+                                                                           P.L, pslot, buckets, partial,
+                                                                           (u32)(P.B * P.nwin), base_stride);
     prof_mark("accumulate");
     msm_fixup<C><<<R.sm_count * 2, 128, 0, st>>>(multi, meta, counts, pslot, P.L, partial, buckets);
     prof_mark("fixup");
@@ -454,9 +457,10 @@ static void msm_combine_host(const XYZZ<C>* win, const MsmPlan& P, uint64_t out_
     memcpy(out_xyz, &j, 96);
 }
 
-// nbatch MSMs of k points over the same bases; scalars: nbatch x k elements, out: nbatch x 12 words
+// nbatch MSMs of k points; MSM j uses bases + j*base_stride (0: all share one base set); scalars: nbatch x k
+// elements, out: nbatch x 12 words
 template <int C>
-int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, uint64_t* out_xyz) {
+int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, uint64_t* out_xyz, ptrdiff_t base_stride) {
     Runtime& R = rt();
     if (k == 0 || nbatch == 0) {
         Jac<C> j = xyzz_to_jac<C>(xyzz_identity<C>());
@@ -467,7 +471,7 @@ int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbat
     MsmPlan P = make_plan(k, nbatch);
     HALO_CHECK(P.nwt * k < ((size_t)1 << 32), HALO_EINVAL, "msm: batch too large (nbatch*nwin*k must be < 2^32)");
     XYZZ<C>* d_win = nullptr;
-    if (int e = msm_enqueue<C>((const Affine<C>*)d_bases, (const Fe<CurveTraits<C>::SCALAR>*)d_scalars, k, P, &d_win)) return e;
+    if (int e = msm_enqueue<C>((const Affine<C>*)d_bases, (const Fe<CurveTraits<C>::SCALAR>*)d_scalars, k, P, base_stride, &d_win)) return e;
     void* h = nullptr;
     if (int e = pinned_get(P.nwt * sizeof(XYZZ<C>), &h)) return e;
     HALO_CUDA(cudaMemcpyAsync(h, d_win, P.nwt * sizeof(XYZZ<C>), cudaMemcpyDeviceToHost, R.stream));
@@ -484,7 +488,7 @@ int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbat
     }
     return HALO_OK;
 }
-template int msm_device<0>(const void*, const void*, size_t, size_t, uint64_t*);
-template int msm_device<1>(const void*, const void*, size_t, size_t, uint64_t*);
+template int msm_device<0>(const void*, const void*, size_t, size_t, uint64_t*, ptrdiff_t);
+template int msm_device<1>(const void*, const void*, size_t, size_t, uint64_t*, ptrdiff_t);
 
 }  // namespace halo

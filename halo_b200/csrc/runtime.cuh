@@ -45,10 +45,11 @@ struct Runtime {
     void* ntt_tw[2] = {nullptr, nullptr};   // twiddle table per field: omega_max^k, k < 2^(logmax-1)
     int ntt_logmax[2] = {0, 0};
     std::recursive_mutex mu;
-    std::string err;
 };
 
 Runtime& rt();
+// last error message of the calling thread (halo_last_error)
+inline std::string& last_err() { static thread_local std::string e; return e; }
 
 #define HALO_CUDA(call)                                                                        \
     do {                                                                                       \
@@ -57,7 +58,7 @@ Runtime& rt();
             char buf__[512];                                                                   \
             snprintf(buf__, sizeof buf__, "%s:%d: %s -> %s", __FILE__, __LINE__, #call,        \
                      cudaGetErrorString(e__));                                                 \
-            halo::rt().err = buf__;                                                            \
+            halo::last_err() = buf__;                                                            \
             return HALO_ECUDA;                                                                 \
         }                                                                                      \
     } while (0)
@@ -65,7 +66,7 @@ Runtime& rt();
 #define HALO_CHECK(cond, code, msg)                 \
     do {                                            \
         if (!(cond)) {                              \
-            halo::rt().err = (msg);                 \
+            halo::last_err() = (msg);                 \
             return (code);                          \
         }                                           \
     } while (0)

@@ -70,6 +70,37 @@ int halo_set_tuning(int key, int value);
 /* window width override for experiments (0 = automatic) */
 int halo_msm_set_window(int c);
 
+/* ---- PC_DL and AS_DL  (crates/accumulation/src/pcdl.rs, acc.rs) ---------------------------------------------
+ * Flat layouts in u64 words, L = lg n = log2(d + 1):
+ *   proof    = Ls[12 L] Rs[12 L] U[12] c[4] hiding[1] C_bar[12] w_prime[4]              (24 L + 33 words, EvalProof)
+ *   instance = C[12] d[1] z[4] v[4] proof                                               (24 L + 54 words, Instance)
+ * Points are Jacobian, scalars Montgomery; hiding = 0 leaves C_bar / w_prime zero (Option::None).
+ * The Fiat-Shamir transcript (crates/poseidon) runs inside the library on the host. */
+size_t halo_instance_words(unsigned lg_n);
+size_t halo_proof_words(unsigned lg_n);
+/* ≙ pcdl::commit(p, d, w) (pcdl.rs:275-287) against the resident generators; asserts -> HALO_EINVAL */
+int halo_pcdl_commit(int curve, const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w_or_null, uint64_t out_xyz[12]);
+/* ≙ pcdl::open / open_without_eval (pcdl.rs:326-473).  v_or_null == NULL: v = p(z) is computed (open) and written to
+ * out_v_or_null.  Hiding (w_or_null != NULL) consumes the caller's randomness: hide_q = the d coefficients of the
+ * uniform polynomial q (pcdl.rs:348), hide_wbar = w_bar (pcdl.rs:352). */
+int halo_pcdl_open(int curve, const uint64_t* coeffs, size_t len, const uint64_t C_xyz[12], size_t d, const uint64_t z[4],
+                   const uint64_t* v_or_null, const uint64_t* w_or_null, const uint64_t* hide_q, const uint64_t* hide_wbar,
+                   uint64_t* out_proof, uint64_t* out_v_or_null);
+/* ≙ pcdl::succinct_check (pcdl.rs:483-554): HALO_OK and (h as its L+1 challenges, U), or HALO_EREJECT */
+int halo_pcdl_succinct_check(int curve, const uint64_t* instance, uint64_t* out_xis_or_null, uint64_t* out_U_or_null);
+/* ≙ pcdl::check (pcdl.rs:563-583) */
+int halo_pcdl_check(int curve, const uint64_t* instance);
+/* ≙ acc::prover / verifier / decider (acc.rs:178-217) over m instances of equal d; the accumulator is an instance */
+int halo_acc_prover(int curve, const uint64_t* instances, size_t m, uint64_t* out_acc);
+int halo_acc_verifier(int curve, const uint64_t* instances, size_t m, const uint64_t* acc);
+int halo_acc_decider(int curve, const uint64_t* acc);
+/* commit(h) for h(X) = prod (1 + xi_{L-i} X^{2^i}) expanded on the device  ≙ pcdl.rs:577 */
+int halo_hpoly_commit(int curve, const uint64_t* xis, size_t lg_n, uint64_t out_xyz[12]);
+/* coefficients of sum_i alphas[i] * h_i(X)  ≙ AccumulatedHPolys::get_poly (acc.rs:86-92); xis: m x (L+1) x 4 */
+int halo_acc_hpoly(int field, const uint64_t* xis, const uint64_t* alphas, size_t m, size_t lg_n, uint64_t* out_coeffs);
+/* ≙ HPoly::eval (pcdl.rs:221-233), host */
+int halo_hpoly_eval(int field, const uint64_t* xis, size_t lg_n, const uint64_t z[4], uint64_t out[4]);
+
 /* ---- NTT / iNTT  ≙ Evals::from_poly* / Evals::interpolate*  (crates/group/src/poly.rs:56-64,133-139) and the direct
  * evaluate_over_domain_by_ref / interpolate calls at crates/plonk/src/plonk/protocol.rs:82-106,140-141,158-159,195.
  * data: b vectors of 2^log_n elements of `field`, transformed in place, natural order in and out; the inverse
