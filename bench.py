@@ -191,7 +191,8 @@ def run_halo(args, rank, world, local_rank):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     halo_b200.init(local_rank)
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()      # torch's default stream has handle 0, which halo_set_stream reads as 'library stream'
+    torch.cuda.set_stream(stream)
     check(lib.halo_set_stream(ctypes.c_void_p(stream.cuda_stream)))
     lib.halo_launch_count.restype = ctypes.c_ulonglong
     u64p = ctypes.POINTER(ctypes.c_uint64)

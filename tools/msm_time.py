@@ -1,20 +1,18 @@
 """Quick MSM timing sweep on the GPU (inputs resident in HBM)."""
 import ctypes, sys, os, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 import numpy as np, torch
 import halo_b200
 from halo_b200._lib import lib, check
-import oracle_lib as O
 halo_b200.init()
-O.set_threads(os.cpu_count())
 lgs = [int(x) for x in sys.argv[1:]] or [12, 16, 18, 20]
 kmax = 1 << max(lgs)
-t = time.time(); pts = O.points_arith(0, kmax); print("points", time.time() - t, flush=True)
-sc = O.random_scalars(0, kmax, 1)
-d_pts = torch.from_numpy(pts.view(np.int64)).cuda()
-d_sc = torch.from_numpy(sc.view(np.int64)).cuda()
-s = torch.cuda.current_stream()
+d_pts = torch.empty((kmax, 8), dtype=torch.int64, device="cuda")
+check(lib.halo_gen_points_dev(0, ctypes.c_uint64(3), ctypes.c_size_t(0), ctypes.c_size_t(kmax), ctypes.c_void_p(d_pts.data_ptr())))
+d_sc = torch.randint(-(1 << 63), (1 << 63) - 1, (kmax, 4), dtype=torch.int64, device="cuda")
+d_sc[:, 3] &= (1 << 62) - 1
+s = torch.cuda.Stream()          # a real stream: handle 0 would mean 'library stream' to halo_set_stream
+torch.cuda.set_stream(s)
 check(lib.halo_set_stream(ctypes.c_void_p(s.cuda_stream)))
 out = np.empty(12, dtype=np.uint64)
 for lg in lgs:

@@ -11,7 +11,8 @@ d_pts = torch.empty((k, 8), dtype=torch.int64, device="cuda")
 check(lib.halo_gen_points_dev(0, ctypes.c_uint64(7), ctypes.c_size_t(0), ctypes.c_size_t(k), ctypes.c_void_p(d_pts.data_ptr())))
 d_sc = torch.randint(-(1 << 63), (1 << 63) - 1, (k, 4), dtype=torch.int64, device="cuda")
 d_sc[:, 3] &= (1 << 62) - 1
-s = torch.cuda.current_stream()
+s = torch.cuda.Stream()          # a real stream: handle 0 would mean 'library stream' to halo_set_stream
+torch.cuda.set_stream(s)
 check(lib.halo_set_stream(ctypes.c_void_p(s.cuda_stream)))
 check(lib.halo_profile_enable(1))
 out = np.empty(12, dtype=np.uint64)
