@@ -214,14 +214,20 @@ def run_halo(args, rank, world, local_rank):
     d_part = torch.zeros(12, dtype=torch.int64, device="cuda")
     gathered = torch.zeros((world, 12), dtype=torch.int64, device="cuda") if world > 1 else None
 
-    # Montgomery one of the scalar field, for summing the gathered partials with halo_msm_proj
-    one_m = int_to_limbs((1 << 256) % Q_SCALAR)
-    ones = np.tile(one_m, (world, 1)).copy()
     total = np.zeros(12, dtype=np.uint64)
+
+    prof = {"on": False, "ms": {}}
+    ms_buf = (ctypes.c_float * 24)()
+    nm_buf = (ctypes.c_char_p * 24)()
 
     def step_dev():
         check(lib.halo_msm_dev(PALLAS, ctypes.c_void_p(d_pts.data_ptr()), ctypes.c_size_t(0),
                                ctypes.c_void_p(d_sc.data_ptr()), ctypes.c_size_t(k), out.ctypes.data_as(u64p)))
+        if prof["on"]:                       # per-stage CUDA-event times of THIS MSM (before the combine runs another)
+            nst = lib.halo_profile_read(ms_buf, nm_buf, 24)
+            for j in range(max(nst, 0)):
+                nm = nm_buf[j].decode()
+                prof["ms"][nm] = prof["ms"].get(nm, 0.0) + ms_buf[j]
         combine()
 
     def step_e2e():
@@ -237,8 +243,7 @@ def run_halo(args, rank, world, local_rank):
         d_part.copy_(torch.from_numpy(out.view(np.int64)))
         dist.all_gather_into_tensor(gathered, d_part)
         parts = gathered.cpu().numpy().view(np.uint64).copy()
-        check(lib.halo_msm_proj(PALLAS, parts.ctypes.data_as(u64p), ones.ctypes.data_as(u64p),
-                                ctypes.c_size_t(world), total.ctypes.data_as(u64p)))
+        check(lib.halo_point_sum(PALLAS, parts.ctypes.data_as(u64p), ctypes.c_size_t(world), total.ctypes.data_as(u64p)))
 
     def barrier():
         if dist is not None:
@@ -248,22 +253,17 @@ def run_halo(args, rank, world, local_rank):
     def timed(fn, steps, collect_profile=False):
         """K steps, each bracketed by CUDA events on the launching stream with an L2 flush in between (outside the
         events); returns total ms (max over ranks) and per-stage sums."""
-        stage_ms = {}
+        prof["on"], prof["ms"] = collect_profile, {}
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
-        ms_buf = (ctypes.c_float * 24)()
-        nm_buf = (ctypes.c_char_p * 24)()
         barrier()
         for i in range(steps):
             flush.zero_()
             ev[i][0].record(stream)
             fn()
             ev[i][1].record(stream)
-            if collect_profile:
-                n = lib.halo_profile_read(ms_buf, nm_buf, 24)
-                for j in range(max(n, 0)):
-                    nm = nm_buf[j].decode()
-                    stage_ms[nm] = stage_ms.get(nm, 0.0) + ms_buf[j]
         barrier()
+        prof["on"] = False
+        stage_ms = dict(prof["ms"])
         tot = sum(a.elapsed_time(b) for a, b in ev)
         if dist is not None:
             t = torch.tensor([tot], dtype=torch.float64, device="cuda")

@@ -191,6 +191,14 @@ static int msm_proj_impl(const uint64_t* bases_xyz, const uint64_t* scalars, siz
     return halo_msm(C, (const uint64_t*)aff.data(), 0, scalars, k, out_xyz);
 }
 
+// sum of n Jacobian points on the host: the combine step of a point-range-sharded MSM (n = number of GPUs)
+template <int C> static void point_sum_impl(const uint64_t* pts, size_t n, uint64_t* out) {
+    XYZZ<C> acc = xyzz_identity<C>();
+    for (size_t i = 0; i < n; ++i) { Jac<C> j; memcpy(&j, pts + 12 * i, 96); xyzz_add<C>(acc, jac_to_xyzz<C>(j)); }
+    Jac<C> r = xyzz_to_jac<C>(acc);
+    memcpy(out, &r, 96);
+}
+
 extern "C" {
 
 const char* halo_last_error(void) { return last_err().c_str(); }
@@ -389,6 +397,12 @@ int halo_msm_proj(int curve, const uint64_t* bases_xyz, const uint64_t* scalars,
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
     HALO_CHECK(out_xyz && ((bases_xyz && scalars) || k == 0), HALO_EINVAL, "msm_proj: null pointer");
     return curve == 0 ? msm_proj_impl<0>(bases_xyz, scalars, k, out_xyz) : msm_proj_impl<1>(bases_xyz, scalars, k, out_xyz);
+}
+
+int halo_point_sum(int curve, const uint64_t* pts_xyz, size_t n, uint64_t out_xyz[12]) {
+    HALO_CHECK((curve == 0 || curve == 1) && out_xyz && (pts_xyz || n == 0), HALO_EINVAL, "point_sum: bad argument");
+    if (curve == 0) point_sum_impl<0>(pts_xyz, n, out_xyz); else point_sum_impl<1>(pts_xyz, n, out_xyz);
+    return HALO_OK;
 }
 
 int halo_field_op(int field, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {

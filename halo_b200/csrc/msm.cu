@@ -280,39 +280,48 @@ __global__ void __launch_bounds__(128, 2) msm_fixup(const u32* __restrict__ mult
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// 7. window sums  W = sum_b (b+1) * bucket_b  by recursive grouping.  At a level with items i = 0..n_in-1 per
-//    window, item i stands for  w_i + (i*M) * s_i  (level 0: s_i = w_i = bucket_i, M = 1).  A group of S items
-//    g*S + j becomes one item of the next level:  s' = sum_j s,  w' = sum_j w + M * sum_j j*s,  M' = S*M.
-//    One thread per group; when one item is left, W = w_0.
+// 7. window sums  W = sum_b (b+1) * bucket_b  as a binary tree with pending plain sums.
+//    Let s(l)_i be the sum of 2^l consecutive buckets.  Then  sum_b b*bucket_b = sum_l 2^l * A_l  with
+//    A_l = sum over ODD i of s(l)_i, and  sum_b bucket_b = T = s(c-1)_0.  Level kernel l halves the main array
+//    (s(l+1)_g = s(l)_2g + s(l)_2g+1), starts the pending array of A_l with the odd items, and halves every older
+//    pending array: (l+1) * n/2^(l+1) independent additions per window and a dependency depth of ONE addition per
+//    level (c-1 levels), instead of a chain of 2S-1 additions per level of a grouped running sum.  The last kernel
+//    doubles A_l l times and adds everything up inside one warp per window.
 // ---------------------------------------------------------------------------------------------------------
 template <int C> __device__ __forceinline__ void xyzz_dbl_n(XYZZ<C>& p, int n) {
     for (int i = 0; i < n; ++i) p = xyzz_dbl<C>(p);
 }
-template <int C, int MINB>
-__global__ void __launch_bounds__(128, MINB) msm_reduce_level(const XYZZ<C>* __restrict__ s_in, const XYZZ<C>* __restrict__ w_in,
-                                                           u32 n_in, u32 S, int log2M, size_t ngroups_total,
-                                                           XYZZ<C>* __restrict__ s_out, XYZZ<C>* __restrict__ w_out) {
+template <int C>
+__global__ void __launch_bounds__(128, 3) msm_tree_level(const XYZZ<C>* __restrict__ main_in, const XYZZ<C>* __restrict__ pend_in,
+                                                         XYZZ<C>* __restrict__ main_out, XYZZ<C>* __restrict__ pend_out,
+                                                         u32 n_in, u32 lvl, size_t nthreads) {
     size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (t >= ngroups_total) return;
-    const u32 n_out = n_in / S;
-    const size_t win = t / n_out, g = t - win * n_out;
-    const size_t base = win * n_in + g * S;
-    XYZZ<C> run = xyzz_identity<C>(), acc = xyzz_identity<C>(), wsum = xyzz_identity<C>();
-    for (u32 j = S - 1; j >= 1; --j) {
-        XYZZ<C> v = load_xyzz(s_in + base + j);
-        xyzz_add<C>(run, v);
-        xyzz_add<C>(acc, run);
-        if (w_in) { XYZZ<C> wv = load_xyzz(w_in + base + j); xyzz_add<C>(wsum, wv); }
-    }
-    {
-        XYZZ<C> v = load_xyzz(s_in + base);
-        xyzz_add<C>(run, v);
-        if (w_in) { XYZZ<C> wv = load_xyzz(w_in + base); xyzz_add<C>(wsum, wv); } else wsum = run;
-    }
-    xyzz_dbl_n<C>(acc, log2M);
-    xyzz_add<C>(wsum, acc);
-    if (n_out > 1) store_xyzz(s_out + t, run);
-    store_xyzz(w_out + t, wsum);
+    if (t >= nthreads) return;
+    const u32 n_out = n_in >> 1;
+    const size_t per_win = (size_t)(lvl + 1) * n_out;
+    const size_t win = t / per_win;
+    const u32 rem = (u32)(t - win * per_win);
+    const u32 r = rem / n_out, g = rem - r * n_out;
+    const XYZZ<C>* src = r < lvl ? pend_in + (win * lvl + r) * (size_t)n_in : main_in + win * (size_t)n_in;
+    XYZZ<C> a = load_xyzz(src + 2 * g), b = load_xyzz(src + 2 * g + 1);
+    XYZZ<C>* pout = pend_out + (win * (lvl + 1) + r) * (size_t)n_out + g;
+    if (r == lvl) store_xyzz(pout, b);                  // odd item of this level: first summand of A_lvl
+    xyzz_add<C>(a, b);
+    if (r < lvl) store_xyzz(pout, a);
+    else store_xyzz(main_out + win * (size_t)n_out + g, a);
+}
+// one warp per window: lane r < nlev holds A_r (weight 2^r), lane nlev holds T
+template <int C>
+__global__ void __launch_bounds__(128, 2) msm_tree_final(const XYZZ<C>* __restrict__ main_in, const XYZZ<C>* __restrict__ pend_in,
+                                                         u32 nlev, size_t nwt, XYZZ<C>* __restrict__ winsum) {
+    const u32 lane = threadIdx.x & 31;
+    const size_t win = blockIdx.x * (size_t)(blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (win >= nwt) return;
+    XYZZ<C> v = xyzz_identity<C>();
+    if (lane < nlev) { v = load_xyzz(pend_in + win * nlev + lane); xyzz_dbl_n<C>(v, (int)lane); }
+    else if (lane == nlev) v = load_xyzz(main_in + win);
+    for (int d = 16; d >= 1; d >>= 1) { XYZZ<C> o = xyzz_shfl_down<C>(v, d); xyzz_add<C>(v, o); }
+    if (lane == 0) store_xyzz(winsum + win, v);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -387,11 +396,12 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     multi = pslot + P.nb;
     if (int e = ws_get(WS_BUCKETS, P.nb * sizeof(XYZZ<C>), (void**)&buckets)) return e;
     if (int e = ws_get(WS_TMP3, P.max_partial * sizeof(XYZZ<C>), (void**)&partial)) return e;
-    const size_t l1 = P.nb / 2 + P.nwt, l2 = P.nb / 4 + P.nwt;
-    if (int e = ws_get(WS_SEGSUM, 2 * l1 * sizeof(XYZZ<C>), (void**)&lvl[0])) return e;
-    lvl[1] = lvl[0] + l1;
-    if (int e = ws_get(WS_SEGWGT, 2 * l2 * sizeof(XYZZ<C>), (void**)&lvl[2])) return e;
-    lvl[3] = lvl[2] + l2;
+    // tree reduction: main ping-pong (nb/2, nb/4) and pending ping-pong (nb/2 each)
+    const size_t half = P.nb / 2 + P.nwt;
+    if (int e = ws_get(WS_SEGSUM, (half + half / 2 + 1) * sizeof(XYZZ<C>), (void**)&lvl[0])) return e;
+    lvl[1] = lvl[0] + half;
+    if (int e = ws_get(WS_SEGWGT, 2 * half * sizeof(XYZZ<C>), (void**)&lvl[2])) return e;
+    lvl[3] = lvl[2] + half;
     if (int e = ws_get(WS_WINSUM, P.nwt * sizeof(XYZZ<C>), (void**)&winsum)) return e;
 
     if (int e = prof_begin()) return e;
@@ -415,29 +425,20 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     msm_fixup<C><<<R.sm_count * 2, 128, 0, st>>>(multi, meta, counts, pslot, P.L, partial, buckets);
     prof_mark("fixup");
     R.launches += 7;
-    // bucket reduction levels
+    // bucket reduction: c-1 tree levels, then the per-window combine
     {
-        const XYZZ<C>*s_in = buckets, *w_in = nullptr;
-        u32 n_in = (u32)P.B;
-        int log2M = 0, lv = 0;
+        const XYZZ<C>*m_in = buckets, *p_in = nullptr;
+        u32 n_in = (u32)P.B, lv = 0;
         while (n_in > 1) {
-            const u32 S0 = R.tune[1] > 0 ? (u32)R.tune[1] : 4u;        // group size (power of two)
-            const u32 S = n_in >= S0 ? S0 : n_in;
-            const u32 n_out = n_in / S;
-            const size_t groups = (size_t)n_out * P.nwt;
-            XYZZ<C>* s_out = lvl[(lv & 1) * 2];
-            XYZZ<C>* w_out = n_out > 1 ? lvl[(lv & 1) * 2 + 1] : winsum;
-            if (R.tune[0] == 1)
-                msm_reduce_level<C, 4><<<(unsigned)((groups + 127) / 128), 128, 0, st>>>(s_in, w_in, n_in, S, log2M, groups, s_out, w_out);
-            else if (R.tune[0] == 2)
-                msm_reduce_level<C, 3><<<(unsigned)((groups + 127) / 128), 128, 0, st>>>(s_in, w_in, n_in, S, log2M, groups, s_out, w_out);
-            else
-                msm_reduce_level<C, 2><<<(unsigned)((groups + 127) / 128), 128, 0, st>>>(s_in, w_in, n_in, S, log2M, groups, s_out, w_out);
+            XYZZ<C>* m_out = lvl[lv & 1];
+            XYZZ<C>* p_out = lvl[2 + (lv & 1)];
+            const size_t threads = (size_t)(lv + 1) * (n_in >> 1) * P.nwt;
+            msm_tree_level<C><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(m_in, p_in, m_out, p_out, n_in, lv, threads);
             R.launches += 1;
-            s_in = s_out; w_in = w_out; n_in = n_out;
-            for (u32 x = S; x > 1; x >>= 1) ++log2M;
-            ++lv;
+            m_in = m_out; p_in = p_out; n_in >>= 1; ++lv;
         }
+        msm_tree_final<C><<<(unsigned)((P.nwt + 3) / 4), 128, 0, st>>>(m_in, p_in, lv, P.nwt, winsum);
+        R.launches += 1;
     }
     prof_mark("reduce");
     HALO_CUDA(cudaGetLastError());

@@ -8,7 +8,7 @@ The collective calls are backend-agnostic (NCCL on the GPUs; gloo in the CPU tes
 local compute is injected)."""
 import numpy as np
 
-from . import consts, group
+from . import group
 
 
 def point_range(k, rank, world):
@@ -39,10 +39,13 @@ def all_gather_words(dist, words):
 
 
 def sum_points(curve, parts):
-    """Sum of Jacobian points on the device: a projective MSM with unit scalars (group.rs:53-56 shape)."""
+    """Sum of the per-rank Jacobian partial sums (host arithmetic inside the library: G - 1 additions)."""
+    import ctypes
+    from ._lib import lib, check, ptr
     parts = np.ascontiguousarray(parts, dtype=np.uint64).reshape(-1, 12)
-    ones = np.tile(consts.one(consts.SCALAR_FIELD[curve]), (parts.shape[0], 1))
-    return group.point_dot(curve, ones, parts)
+    out = np.empty(12, dtype=np.uint64)
+    check(lib.halo_point_sum(curve, ptr(parts.reshape(-1)), ctypes.c_size_t(parts.shape[0]), ptr(out)))
+    return out
 
 
 def msm_sharded(dist, curve, scalars, bases, local_msm=None, combine=None):

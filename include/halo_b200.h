@@ -59,6 +59,8 @@ int halo_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_
 int halo_msm_batch(int curve, size_t base_off, const uint64_t* scalars, size_t k, size_t b, uint64_t* out_xyz);
 /* projective bases  ≙ point_dot (group.rs:53-56): normalize_batch + MSM */
 int halo_msm_proj(int curve, const uint64_t* bases_xyz, const uint64_t* scalars, size_t k, uint64_t out_xyz[12]);
+/* sum of n Jacobian points (host arithmetic): combines the per-GPU partial sums of a point-range-sharded MSM */
+int halo_point_sum(int curve, const uint64_t* pts_xyz, size_t n, uint64_t out_xyz[12]);
 /* same as halo_msm with inputs already in device memory (d_bases may be NULL for resident Gs) */
 int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k,
                  uint64_t out_xyz[12]);
