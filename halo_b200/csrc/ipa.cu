@@ -124,6 +124,81 @@ __global__ void __launch_bounds__(128, 4) ipa_fold_kernel(Affine<C>* __restrict_
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// The same fold with the curve endomorphism: both Pasta curves have j = 0, so phi(x, y) = (beta*x, y) = lambda*(x, y)
+// and xi = k1 + k2*lambda with |k1|, |k2| < 2^128 (host: glv_decompose).  xi*P = k1*P + k2*phi(P) needs half the
+// doublings of the plain ladder.  The result stays in XYZZ form; xyzz_batch_affine_kernel normalises a run of
+// points per thread with ONE inversion (Montgomery's trick) instead of one Fermat inversion per point.
+// ---------------------------------------------------------------------------------------------------------
+struct GlvScalar {
+    u32 k1[5], k2[5];      // magnitudes, little-endian limbs
+    int neg1, neg2;        // signs
+    int nbits;             // max bit length of the two magnitudes
+};
+template <int C>
+__global__ void __launch_bounds__(128, 4) ipa_fold_glv_kernel(const Affine<C>* __restrict__ gs,
+                                                              Fe<CurveTraits<C>::SCALAR>* __restrict__ cs,
+                                                              Fe<CurveTraits<C>::SCALAR>* __restrict__ zs, size_t m, GlvScalar g,
+                                                              Fe<CurveTraits<C>::BASE> beta, Fe<CurveTraits<C>::SCALAR> xi,
+                                                              Fe<CurveTraits<C>::SCALAR> xi_inv, XYZZ<C>* __restrict__ out) {
+    constexpr int S = CurveTraits<C>::SCALAR, B = CurveTraits<C>::BASE;
+    size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (j >= m) return;
+    g_st(cs + j, fe_add<S>(g_ld(cs + j), fe_mul<S>(g_ld(cs + m + j), xi_inv)));
+    g_st(zs + j, fe_add<S>(g_ld(zs + j), fe_mul<S>(g_ld(zs + m + j), xi)));
+    Affine<C> P1, P2;
+    P1.x = g_ld(&gs[m + j].x); P1.y = g_ld(&gs[m + j].y);
+    P2.x = fe_mul<B>(P1.x, beta);                         // phi(P); the identity (0,0) maps to itself
+    P2.y = g.neg2 ? fe_neg<B>(P1.y) : P1.y;
+    if (g.neg1) P1.y = fe_neg<B>(P1.y);
+    if (fe_is_zero<B>(P1.x) && fe_is_zero<B>(P2.y)) { P1.y = fe_zero<B>(); P2.y = fe_zero<B>(); }   // keep (0,0) exact
+    XYZZ<C> acc = xyzz_identity<C>();
+    for (int b = g.nbits - 1; b >= 0; --b) {
+        acc = xyzz_dbl<C>(acc);
+        if ((g.k1[b >> 5] >> (b & 31)) & 1u) xyzz_madd<C>(acc, P1, false);
+        if ((g.k2[b >> 5] >> (b & 31)) & 1u) xyzz_madd<C>(acc, P2, false);
+    }
+    Affine<C> Q;
+    Q.x = g_ld(&gs[j].x); Q.y = g_ld(&gs[j].y);
+    xyzz_madd<C>(acc, Q, false);
+    XYZZ<C>* o = out + j;
+    g_st(&o->X, acc.X); g_st(&o->Y, acc.Y); g_st(&o->ZZ, acc.ZZ); g_st(&o->ZZZ, acc.ZZZ);
+}
+
+// XYZZ -> affine for `m` points, BATCH consecutive points per thread sharing one inversion; identity -> (0,0)
+template <int C, int BATCH>
+__global__ void __launch_bounds__(128) xyzz_batch_affine_kernel(const XYZZ<C>* __restrict__ in, size_t m, Affine<C>* __restrict__ out) {
+    constexpr int B = CurveTraits<C>::BASE;
+    const size_t lo = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) * BATCH;
+    if (lo >= m) return;
+    Fe<B> pre[BATCH];
+    Fe<B> run = fe_one<B>();
+#pragma unroll
+    for (int i = 0; i < BATCH; ++i) {
+        if (lo + i < m) {
+            Fe<B> zz = g_ld(&in[lo + i].ZZ), zzz = g_ld(&in[lo + i].ZZZ);
+            if (!fe_is_zero<B>(zz)) run = fe_mul<B>(run, fe_mul<B>(zz, zzz));
+        }
+        pre[i] = run;
+    }
+    Fe<B> inv = fe_inv<B>(run);
+#pragma unroll
+    for (int i = BATCH - 1; i >= 0; --i) {
+        if (lo + i < m) {
+            Fe<B> zz = g_ld(&in[lo + i].ZZ), zzz = g_ld(&in[lo + i].ZZZ);
+            Affine<C> a;
+            if (fe_is_zero<B>(zz)) { a.x = fe_zero<B>(); a.y = fe_zero<B>(); }
+            else {
+                Fe<B> dinv = i > 0 ? fe_mul<B>(inv, pre[i - 1]) : inv;       // 1 / (ZZ*ZZZ)
+                inv = fe_mul<B>(inv, fe_mul<B>(zz, zzz));
+                a.x = fe_mul<B>(g_ld(&in[lo + i].X), fe_mul<B>(dinv, zzz));
+                a.y = fe_mul<B>(g_ld(&in[lo + i].Y), fe_mul<B>(dinv, zz));
+            }
+            g_st(&out[lo + i].x, a.x); g_st(&out[lo + i].y, a.y);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // hiding helpers (pcdl.rs:344-366):  p_bar = q * (X - z)  ->  pbar[i] = q[i-1] - z*q[i]  (q has d = n-1 coefficients)
 // and  cs = p + a * p_bar
 // ---------------------------------------------------------------------------------------------------------
@@ -233,6 +308,67 @@ struct FixedBase {
         return acc;
     }
 };
+
+namespace glv_data {
+#include "glv_consts.inc"
+}
+typedef unsigned __int128 u128;
+// 4x4-limb schoolbook product
+static void mul_4x4(const u64 a[4], const u64 b[4], u64 out[8]) {
+    for (int i = 0; i < 8; ++i) out[i] = 0;
+    for (int i = 0; i < 4; ++i) {
+        u128 c = 0;
+        for (int j = 0; j < 4; ++j) { c += (u128)a[i] * b[j] + out[i + j]; out[i + j] = (u64)c; c >>= 64; }
+        out[i + 4] = (u64)c;
+    }
+}
+// (a*b) mod 2^256, a - b mod 2^256
+static void mul_lo4(const u64 a[4], const u64 b[4], u64 out[4]) { u64 t[8]; mul_4x4(a, b, t); for (int i = 0; i < 4; ++i) out[i] = t[i]; }
+static void sub4(u64 a[4], const u64 b[4]) { u64 br = 0; for (int i = 0; i < 4; ++i) { u128 d = (u128)a[i] - b[i] - br; a[i] = (u64)d; br = (u64)(d >> 64) & 1; } }
+static void neg4(u64 a[4]) { u64 z[4] = {0, 0, 0, 0}; sub4(z, a); for (int i = 0; i < 4; ++i) a[i] = z[i]; }
+
+// xi = k1 + k2*lambda (mod r), |k1|, |k2| < 2^130.  Returns false (caller falls back to the plain ladder) if the
+// split does not verify -- it always does for a correct constant table, the check is a guard, not a code path.
+template <int C>
+static bool glv_decompose(const Fe<CurveTraits<C>::SCALAR>& xi, GlvScalar* out) {
+    constexpr int S = CurveTraits<C>::SCALAR;
+    Fe<S> can = fe_to_canonical<S>(xi);
+    u64 k[4]; memcpy(k, can.l, 32);
+    u64 c[2][4];
+    const unsigned long long* G[2] = {glv_data::GLV_G1[C], glv_data::GLV_G2[C]};
+    for (int t = 0; t < 2; ++t) {                              // c_t = (k * g_t) >> 376
+        u64 prod[8]; mul_4x4(k, (const u64*)G[t], prod);
+        c[t][0] = (prod[5] >> 56) | (prod[6] << 8);
+        c[t][1] = (prod[6] >> 56) | (prod[7] << 8);
+        c[t][2] = prod[7] >> 56;
+        c[t][3] = 0;
+    }
+    u64 k1[4], k2[4], t1[4], t2[4];
+    memcpy(k1, k, 32);
+    mul_lo4(c[0], (const u64*)glv_data::GLV_A1[C], t1); sub4(k1, t1);
+    mul_lo4(c[1], (const u64*)glv_data::GLV_A2[C], t2); sub4(k1, t2);
+    for (int i = 0; i < 4; ++i) k2[i] = 0;
+    mul_lo4(c[0], (const u64*)glv_data::GLV_B1[C], t1); sub4(k2, t1);
+    mul_lo4(c[1], (const u64*)glv_data::GLV_B2[C], t2); sub4(k2, t2);
+    out->neg1 = (int)(k1[3] >> 63); if (out->neg1) neg4(k1);
+    out->neg2 = (int)(k2[3] >> 63); if (out->neg2) neg4(k2);
+    if (k1[3] || k2[3] || (k1[2] >> 32) || (k2[2] >> 32)) return false;
+    // verify k1 + k2*lambda == xi in the scalar field
+    auto to_fe = [](const u64 mag[4], int neg) {
+        Fe<S> v; memcpy(v.l, mag, 32);
+        v = fe_from_canonical<S>(v);
+        return neg ? fe_neg<S>(v) : v;
+    };
+    Fe<S> lam; memcpy(lam.l, glv_data::GLV_LAMBDA[C], 32);
+    lam = fe_from_canonical<S>(lam);
+    if (!fe_eq<S>(fe_add<S>(to_fe(k1, out->neg1), fe_mul<S>(to_fe(k2, out->neg2), lam)), xi)) return false;
+    memcpy(out->k1, k1, 20); memcpy(out->k2, k2, 20);
+    int nb = 0;
+    for (int b = 159; b >= 0; --b)
+        if (((out->k1[b >> 5] | out->k2[b >> 5]) >> (b & 31)) & 1u) { nb = b + 1; break; }
+    out->nbits = nb;
+    return true;
+}
 
 static inline unsigned ilog2(size_t n) { unsigned l = 0; while (((size_t)1 << (l + 1)) <= n) ++l; return l; }
 static inline size_t proof_words(unsigned lg_n) { return 24 * (size_t)lg_n + 33; }
@@ -408,8 +544,19 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
         HALO_CHECK(!fe_is_zero<S>(xi_next), HALO_EINVAL, "open: zero challenge has no inverse");
         const SF xi_inv = fe_inv<S>(xi_next);
         xi = xi_next;
-        ipa_fold_kernel<C><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(gs, cs, zs, m, H::bits(xi_next), xi_next, xi_inv);
-        R.launches += 1;
+        GlvScalar gk;
+        if (R.tune[2] != 1 && glv_decompose<C>(xi_next, &gk)) {
+            XYZZ<C>* folded;
+            if (int e = ws_get(WS_IPA_T1, m * sizeof(XYZZ<C>), (void**)&folded)) return e;
+            Fe<H::B> beta; memcpy(&beta, glv_data::GLV_BETA[C], 32);
+            ipa_fold_glv_kernel<C><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(gs, cs, zs, m, gk, beta, xi_next, xi_inv, folded);
+            if (m >= 8192) xyzz_batch_affine_kernel<C, 8><<<(unsigned)((m / 8 + 128) / 128), 128, 0, st>>>(folded, m, gs);
+            else xyzz_batch_affine_kernel<C, 1><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(folded, m, gs);
+            R.launches += 2;
+        } else {                                        // literal ladder (tuning knob 2 = 1 forces it; parity tests use both)
+            ipa_fold_kernel<C><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(gs, cs, zs, m, H::bits(xi_next), xi_next, xi_inv);
+            R.launches += 1;
+        }
         HALO_CUDA(cudaGetLastError());
     }
     // U = G_(lg n), c = c_(lg n)  (pcdl.rs:441-450)

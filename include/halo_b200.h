@@ -67,7 +67,8 @@ int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void*
 /* batched variant over device memory: b scalar vectors of k elements against the same k bases */
 int halo_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k, size_t b,
                        uint64_t* out_xyz);
-/* experiment knobs (0 = default): key 0 = bucket-reduction occupancy variant, key 1 = reduction group size */
+/* experiment knobs (0 = default): key 0 = bucket-reduction occupancy variant, key 1 = unused,
+ * key 2 = 1 forces the literal 255-bit ladder in the IPA fold instead of the endomorphism split */
 int halo_set_tuning(int key, int value);
 /* window width override for experiments (0 = automatic) */
 int halo_msm_set_window(int c);

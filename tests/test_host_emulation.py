@@ -46,6 +46,8 @@ def test_field_ops(emu, oracle, field):
         emu.emu_field_op(field, op, _p(a), _p(b), _p(out), ctypes.c_size_t(n))
         assert (out == ref(field, a, b)).all(), op
     out = np.empty_like(a)
+    emu.emu_field_op(field, 6, _p(a), _p(b), _p(out), ctypes.c_size_t(n))          # dedicated squaring
+    assert (out == O.field_mul(field, a, a)).all()
     emu.emu_field_op(field, 3, _p(a[:50].copy()), _p(b), _p(out), ctypes.c_size_t(50))
     assert (out[:50] == O.field_inv(field, a[:50])).all()
     emu.emu_field_op(field, 4, _p(a), _p(b), _p(out), ctypes.c_size_t(n))

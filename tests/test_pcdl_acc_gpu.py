@@ -138,7 +138,7 @@ def test_accumulation_round_trip_and_parity(hb, oracle, params, curve, lg_n, m):
 
 
 @pytest.mark.parametrize("curve,name", [(0, "pallas"), (1, "vesta")])
-def test_genesis_accumulator_matches_reference_golden(hb, oracle, golden_dir, curve, name):
+def test_genesis_accumulator_matches_reference_golden(hb, oracle, params, golden_dir, curve, name):
     """Accumulator::zero(65536, 1) on the reference's real generators reproduces the constants hard-coded at
     crates/plonk/src/frontend/ivc/mod.rs:196-292: C, z, v, all 16 (L, R) pairs, U and c."""
     O = oracle
@@ -160,3 +160,25 @@ def test_genesis_accumulator_matches_reference_golden(hb, oracle, golden_dir, cu
         hb.acc.decider(curve, acc)
     finally:
         hb.pp.reset(curve)
+        hb.pp.set_pp(curve, *params[curve])          # back to the module's small parameter set
+
+
+@pytest.mark.parametrize("curve", [0, 1])
+def test_fold_literal_ladder_equals_endomorphism_split(hb, oracle, params, curve):
+    """The generator fold is run both as the reference writes it (gs_l + xi*gs_r by a 255-bit ladder, pcdl.rs:427-429)
+    and with xi split as k1 + k2*lambda; both must give the oracle's proof bit for bit."""
+    import ctypes
+    O = oracle
+    sf = O.SCALAR_FIELD[curve]
+    n = 1 << 11
+    p = O.random_scalars(sf, n, 901)
+    z = O.random_scalars(sf, 1, 902)[0]
+    exp = O.instance_open(curve, p, n - 1, z)
+    lib = hb._lib.lib
+    for knob in (1, 0):
+        lib.halo_set_tuning(2, knob)
+        try:
+            q = hb.pcdl.Instance.open(curve, p, n - 1, z)
+        finally:
+            lib.halo_set_tuning(2, 0)
+        same_instance(O, curve, q.w, exp)
