@@ -131,8 +131,10 @@ __global__ void __launch_bounds__(128, 4) ipa_fold_kernel(Affine<C>* __restrict_
 // ---------------------------------------------------------------------------------------------------------
 struct GlvScalar {
     u32 k1[5], k2[5];      // magnitudes, little-endian limbs
+    u32 p1[5], n1[5];      // non-adjacent form of |k1|: digit +1 / -1 bit masks (a third of the digits are non-zero)
+    u32 p2[5], n2[5];      // ... of |k2|
     int neg1, neg2;        // signs
-    int nbits;             // max bit length of the two magnitudes
+    int nbits;             // number of NAF digits to scan
 };
 template <int C>
 __global__ void __launch_bounds__(128, 4) ipa_fold_glv_kernel(const Affine<C>* __restrict__ gs,
@@ -154,8 +156,10 @@ __global__ void __launch_bounds__(128, 4) ipa_fold_glv_kernel(const Affine<C>* _
     XYZZ<C> acc = xyzz_identity<C>();
     for (int b = g.nbits - 1; b >= 0; --b) {
         acc = xyzz_dbl<C>(acc);
-        if ((g.k1[b >> 5] >> (b & 31)) & 1u) xyzz_madd<C>(acc, P1, false);
-        if ((g.k2[b >> 5] >> (b & 31)) & 1u) xyzz_madd<C>(acc, P2, false);
+        const u32 w = (u32)b >> 5, sh = (u32)b & 31;
+        const u32 d1 = ((g.p1[w] | g.n1[w]) >> sh) & 1u, d2 = ((g.p2[w] | g.n2[w]) >> sh) & 1u;
+        if (d1) xyzz_madd<C>(acc, P1, ((g.n1[w] >> sh) & 1u) != 0);
+        if (d2) xyzz_madd<C>(acc, P2, ((g.n2[w] >> sh) & 1u) != 0);
     }
     Affine<C> Q;
     Q.x = g_ld(&gs[j].x); Q.y = g_ld(&gs[j].y);
@@ -363,10 +367,25 @@ static bool glv_decompose(const Fe<CurveTraits<C>::SCALAR>& xi, GlvScalar* out) 
     lam = fe_from_canonical<S>(lam);
     if (!fe_eq<S>(fe_add<S>(to_fe(k1, out->neg1), fe_mul<S>(to_fe(k2, out->neg2), lam)), xi)) return false;
     memcpy(out->k1, k1, 20); memcpy(out->k2, k2, 20);
-    int nb = 0;
-    for (int b = 159; b >= 0; --b)
-        if (((out->k1[b >> 5] | out->k2[b >> 5]) >> (b & 31)) & 1u) { nb = b + 1; break; }
-    out->nbits = nb;
+    // non-adjacent forms: k = sum d_i 2^i, d_i in {-1, 0, 1}, no two adjacent non-zero digits
+    auto naf = [](const u64 mag[4], u32 pos[5], u32 neg[5]) {
+        u128 k = ((u128)mag[1] << 64) | mag[0];
+        u64 top = mag[2];                                  // bits 128.. (< 2^32)
+        for (int i = 0; i < 5; ++i) pos[i] = neg[i] = 0;
+        int i = 0;
+        while ((k != 0 || top != 0) && i < 160) {
+            if (k & 1) {
+                if ((k & 3) == 1) { pos[i >> 5] |= 1u << (i & 31); k -= 1; }
+                else { neg[i >> 5] |= 1u << (i & 31); k += 1; if (k == 0) top += 1; }     // carry out of the low 128 bits
+            }
+            k = (k >> 1) | ((u128)(top & 1) << 127);
+            top >>= 1;
+            ++i;
+        }
+        return i;
+    };
+    int l1 = naf(k1, out->p1, out->n1), l2 = naf(k2, out->p2, out->n2);
+    out->nbits = l1 > l2 ? l1 : l2;
     return true;
 }
 
