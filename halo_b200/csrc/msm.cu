@@ -170,12 +170,14 @@ __global__ void __launch_bounds__(256) msm_scatter(const Fe<SF>* __restrict__ sc
 //    counting-sorted by size (descending: bin = L - size).  A bucket cut into several tasks ("multi") reserves a
 //    run of slots in the partial-result array.
 // ---------------------------------------------------------------------------------------------------------
-struct TaskMeta { u32 ntasks, npartial, nmulti, pad; };
-constexpr int MSM_MAX_L = 128;
+struct TaskMeta { u32 ntasks, npartial, nmulti, nchunks, nbig, pad[3]; };
+constexpr u32 FIXUP_CHUNK = 256;          // partial results one warp adds in the first fix-up pass
+constexpr int MSM_MAX_L = 512;
 
 __global__ void __launch_bounds__(256) msm_task_hist(const u32* __restrict__ counts, size_t nb, u32 L,
                                                      u32* __restrict__ hist, TaskMeta* __restrict__ meta,
-                                                     u32* __restrict__ pslot, u32* __restrict__ multi) {
+                                                     u32* __restrict__ pslot, u32* __restrict__ cbase,
+                                                     uint2* __restrict__ chunks, u32* __restrict__ big) {
     __shared__ u32 sh[MSM_MAX_L + 1];
     for (int i = threadIdx.x; i <= MSM_MAX_L; i += blockDim.x) sh[i] = 0;
     __syncthreads();
@@ -187,7 +189,12 @@ __global__ void __launch_bounds__(256) msm_task_hist(const u32* __restrict__ cou
         const u32 nt = full + (rem ? 1u : 0u);
         if (nt > 1) {
             pslot[b] = atomicAdd(&meta->npartial, nt);
-            multi[atomicAdd(&meta->nmulti, 1u)] = (u32)b;
+            // fix-up work list: one warp per chunk of FIXUP_CHUNK partial results
+            const u32 nch = (nt + FIXUP_CHUNK - 1) / FIXUP_CHUNK;
+            const u32 c0 = atomicAdd(&meta->nchunks, nch);
+            cbase[b] = c0;
+            for (u32 q = 0; q < nch; ++q) chunks[c0 + q] = make_uint2((u32)b, q);
+            if (nch > 1) big[atomicAdd(&meta->nbig, 1u)] = (u32)b;
         }
     }
     __syncthreads();
@@ -258,23 +265,49 @@ template <int C> __device__ __forceinline__ XYZZ<C> xyzz_shfl_down(const XYZZ<C>
     for (int i = 0; i < 32; ++i) o[i] = __shfl_down_sync(0xffffffffu, s[i], d);
     return r;
 }
+template <int C> __device__ __forceinline__ XYZZ<C> warp_sum_xyzz(XYZZ<C> acc, u32 live) {
+    int d0 = 16;
+    while (d0 >= 1 && (u32)d0 >= live) d0 >>= 1;            // lanes >= live hold the identity
+    for (int d = d0; d >= 1; d >>= 1) { XYZZ<C> o = xyzz_shfl_down<C>(acc, d); xyzz_add<C>(acc, o); }
+    return acc;
+}
+// pass 1: one warp per chunk of <= FIXUP_CHUNK partial results; a bucket with a single chunk is finished here
 template <int C>
-__global__ void __launch_bounds__(128, 2) msm_fixup(const u32* __restrict__ multi, const TaskMeta* __restrict__ meta,
+__global__ void __launch_bounds__(128, 2) msm_fixup(const uint2* __restrict__ chunks, const TaskMeta* __restrict__ meta,
                                                     const u32* __restrict__ counts, const u32* __restrict__ pslot,
-                                                    u32 L, const XYZZ<C>* __restrict__ partial,
-                                                    XYZZ<C>* __restrict__ buckets) {
+                                                    const u32* __restrict__ cbase, u32 L, const XYZZ<C>* __restrict__ partial,
+                                                    XYZZ<C>* __restrict__ partial2, XYZZ<C>* __restrict__ buckets) {
     const u32 lane = threadIdx.x & 31;
     const u32 nwarps = gridDim.x * (blockDim.x >> 5);
-    const u32 nmulti = meta->nmulti;
-    for (u32 m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); m < nmulti; m += nwarps) {
-        const u32 b = multi[m];
+    const u32 nchunks = meta->nchunks;
+    for (u32 w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w < nchunks; w += nwarps) {
+        const uint2 ch = chunks[w];
+        const u32 b = ch.x, q = ch.y;
         const u32 nt = (counts[b] + L - 1) / L;
+        const u32 lo = q * FIXUP_CHUNK, hi = min(nt, lo + FIXUP_CHUNK);
         const XYZZ<C>* src = partial + pslot[b];
         XYZZ<C> acc = xyzz_identity<C>();
-        for (u32 s = lane; s < nt; s += 32) { XYZZ<C> v = load_xyzz(src + s); xyzz_add<C>(acc, v); }
-        int d0 = 16;
-        while (d0 >= 1 && (u32)d0 >= nt) d0 >>= 1;          // lanes >= nt hold the identity
-        for (int d = d0; d >= 1; d >>= 1) { XYZZ<C> o = xyzz_shfl_down<C>(acc, d); xyzz_add<C>(acc, o); }
+        for (u32 s = lo + lane; s < hi; s += 32) { XYZZ<C> v = load_xyzz(src + s); xyzz_add<C>(acc, v); }
+        acc = warp_sum_xyzz<C>(acc, hi - lo);
+        if (lane == 0) store_xyzz(nt <= FIXUP_CHUNK ? buckets + b : partial2 + cbase[b] + q, acc);
+    }
+}
+// pass 2: buckets with more than FIXUP_CHUNK partial results: one warp adds the chunk sums
+template <int C>
+__global__ void __launch_bounds__(128, 2) msm_fixup2(const u32* __restrict__ big, const TaskMeta* __restrict__ meta,
+                                                     const u32* __restrict__ counts, const u32* __restrict__ cbase, u32 L,
+                                                     const XYZZ<C>* __restrict__ partial2, XYZZ<C>* __restrict__ buckets) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 nwarps = gridDim.x * (blockDim.x >> 5);
+    const u32 nbig = meta->nbig;
+    for (u32 m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); m < nbig; m += nwarps) {
+        const u32 b = big[m];
+        const u32 nt = (counts[b] + L - 1) / L;
+        const u32 nch = (nt + FIXUP_CHUNK - 1) / FIXUP_CHUNK;
+        const XYZZ<C>* src = partial2 + cbase[b];
+        XYZZ<C> acc = xyzz_identity<C>();
+        for (u32 s = lane; s < nch; s += 32) { XYZZ<C> v = load_xyzz(src + s); xyzz_add<C>(acc, v); }
+        acc = warp_sum_xyzz<C>(acc, nch);
         if (lane == 0) store_xyzz(buckets + b, acc);
     }
 }
@@ -327,14 +360,17 @@ __global__ void __launch_bounds__(128, 2) msm_tree_final(const XYZZ<C>* __restri
 // ---------------------------------------------------------------------------------------------------------
 // host orchestration
 // ---------------------------------------------------------------------------------------------------------
+// Window width.  Only widths whose TOP window is well populated are used: 255 = 15*16+15 = 17*15 = 19*13+8 =
+// 31*8+7, whereas c = 14, 12, 11, 9 ... leave a 2-3 bit top window whose handful of buckets receive every point
+// (same-address atomics in count/scatter, long fix-up chains).  Break-even sizes measured on B200 (tools/msm_tune.py).
 static int pick_window(size_t k) {
     int ov = rt().msm_window_override;
     if (ov >= 2 && ov <= 16) return ov;
     int lg = 0; while (((size_t)1 << (lg + 1)) <= k) ++lg;
-    int c = lg - 4;
-    if (c < 4) c = 4;
-    if (c > 16) c = 16;
-    return c;
+    if (lg >= 20) return 16;
+    if (lg >= 17) return 15;
+    if (lg >= 15) return 13;
+    return 8;
 }
 
 struct MsmPlan {
@@ -355,6 +391,10 @@ static MsmPlan make_plan(size_t k, size_t nbatch) {
     // long tasks amortise the bucket write; short tasks give small problems enough threads
     size_t work = k * p.nwt;
     p.L = work >= ((size_t)1 << 23) ? 128 : work >= ((size_t)1 << 20) ? 32 : 16;
+    if (work >= ((size_t)1 << 23)) {                     // keep ordinary buckets whole: L >= 4 x the mean bucket size
+        size_t mean4 = 4 * (k / p.B);
+        if (mean4 > p.L) p.L = (u32)std::min<size_t>(mean4, MSM_MAX_L);
+    }
     p.max_tasks = p.nb + work / p.L + 1;
     p.max_partial = 2 * (work / p.L) + 2;
     return p;
@@ -377,25 +417,29 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     Runtime& R = rt();
     cudaStream_t st = R.stream;
     const size_t total = k * P.nbatch;
-    u32 *counts, *offsets, *cursor, *bsum, *idx, *pslot, *multi, *hist;
-    uint2* tasks;
+    u32 *counts, *offsets, *cursor, *bsum, *idx, *pslot, *cbase, *big, *hist;
+    uint2 *tasks, *chunks;
     TaskMeta* meta;
-    XYZZ<C> *buckets, *partial, *lvl[4], *winsum;
-    // counts | hist (MSM_MAX_L+1, padded to 256) | meta share one zero-filled allocation
-    const size_t zero_words = P.nb + 256 + 4;
+    XYZZ<C> *buckets, *partial, *partial2, *lvl[4], *winsum;
+    // counts | hist (MSM_MAX_L+1, padded to 1024) | meta share one zero-filled allocation
+    const size_t zero_words = P.nb + 1024 + 8;
     if (int e = ws_get(WS_COUNTS, zero_words * 4, (void**)&counts)) return e;
     hist = counts + P.nb;
-    meta = (TaskMeta*)(hist + 256);
+    meta = (TaskMeta*)(hist + 1024);
     const size_t nblk = (P.nb + 1023) / 1024;
     if (int e = ws_get(WS_OFFSETS, (2 * P.nb + nblk + 1) * 4, (void**)&offsets)) return e;
     cursor = offsets + P.nb;
     bsum = cursor + P.nb;
     if (int e = ws_get(WS_IDX, P.nwt * k * 4, (void**)&idx)) return e;
     if (int e = ws_get(WS_ORDER, P.max_tasks * sizeof(uint2), (void**)&tasks)) return e;
-    if (int e = ws_get(WS_SIZEHIST, 2 * P.nb * 4, (void**)&pslot)) return e;
-    multi = pslot + P.nb;
+    // pslot | cbase | big (nb words each) | chunk list (max_partial entries)
+    if (int e = ws_get(WS_SIZEHIST, 3 * P.nb * 4 + P.max_partial * sizeof(uint2), (void**)&pslot)) return e;
+    cbase = pslot + P.nb;
+    big = cbase + P.nb;
+    chunks = (uint2*)(big + P.nb);
     if (int e = ws_get(WS_BUCKETS, P.nb * sizeof(XYZZ<C>), (void**)&buckets)) return e;
-    if (int e = ws_get(WS_TMP3, P.max_partial * sizeof(XYZZ<C>), (void**)&partial)) return e;
+    if (int e = ws_get(WS_TMP3, 2 * P.max_partial * sizeof(XYZZ<C>), (void**)&partial)) return e;
+    partial2 = partial + P.max_partial;
     // tree reduction: main ping-pong (nb/2, nb/4) and pending ping-pong (nb/2 each)
     const size_t half = P.nb / 2 + P.nwt;
     if (int e = ws_get(WS_SEGSUM, (half + half / 2 + 1) * sizeof(XYZZ<C>), (void**)&lvl[0])) return e;
@@ -414,7 +458,7 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     prof_mark("scan");
     msm_scatter<SF><<<grid_pts, 256, 0, st>>>(d_scalars, k, total, P.c, P.nwin, cursor, idx);
     prof_mark("scatter");
-    msm_task_hist<<<grid_b, 256, 0, st>>>(counts, P.nb, P.L, hist, meta, pslot, multi);
+    msm_task_hist<<<grid_b, 256, 0, st>>>(counts, P.nb, P.L, hist, meta, pslot, cbase, chunks, big);
     scan_partials<<<1, 256, 0, st>>>(hist, P.L + 1, &meta->ntasks);
     msm_task_emit<<<grid_b, 256, 0, st>>>(counts, P.nb, P.L, hist, tasks);
     prof_mark("tasks");
@@ -422,9 +466,10 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
                                                                            P.L, pslot, buckets, partial,
                                                                            (u32)(P.B * P.nwin), base_stride);
     prof_mark("accumulate");
-    msm_fixup<C><<<R.sm_count * 2, 128, 0, st>>>(multi, meta, counts, pslot, P.L, partial, buckets);
+    msm_fixup<C><<<R.sm_count * 4, 128, 0, st>>>(chunks, meta, counts, pslot, cbase, P.L, partial, partial2, buckets);
+    msm_fixup2<C><<<R.sm_count, 128, 0, st>>>(big, meta, counts, cbase, P.L, partial2, buckets);
     prof_mark("fixup");
-    R.launches += 7;
+    R.launches += 8;
     // bucket reduction: c-1 tree levels, then the per-window combine
     {
         const XYZZ<C>*m_in = buckets, *p_in = nullptr;

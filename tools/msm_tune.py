@@ -19,7 +19,7 @@ out = np.empty(12, dtype=np.uint64)
 ms_buf = (ctypes.c_float * 24)(); nm_buf = (ctypes.c_char_p * 24)()
 ref = None
 cs = [int(x) for x in os.environ.get("CS", "15,16").split(",")]
-for c, t0, t1 in itertools.product(cs, (0, 1, 2), (4, 8, 16)):
+for c, t0, t1 in itertools.product(cs, (0,), (0,)):
     lib.halo_msm_set_window(c); lib.halo_set_tuning(0, t0); lib.halo_set_tuning(1, t1)
     best = None
     for it in range(4):
