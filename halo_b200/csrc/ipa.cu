@@ -17,6 +17,8 @@
 #include <mutex>
 #include <string>
 #include <thread>
+#include <chrono>
+#include <cstdio>
 #include <vector>
 
 extern "C" int halo_msm_proj(int, const uint64_t*, const uint64_t*, size_t, uint64_t*);
@@ -200,6 +202,37 @@ __global__ void __launch_bounds__(128) xyzz_batch_affine_kernel(const XYZZ<C>* _
             g_st(&out[lo + i].x, a.x); g_st(&out[lo + i].y, a.y);
         }
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Fold-free tail.  Once the vectors are short, a round's fold is pure latency (a 128-step ladder per generator,
+// ~1.1 ms however few there are).  From then on the generators are never folded again: with B the T generators
+// at the switch and w the weights accumulated since (w = [1] at the switch),
+//     g[i] = sum_u w[u] * B[i + u*2m]          (2m = current vector length, u < T/2m)
+// so L = <r(c), l(g)> and R = <l(c), r(g)> are MSMs over the SAME T bases with complementary scalar vectors, one
+// two-MSM pipeline per round; a fold only updates w (w'[2u] = w[u], w'[2u+1] = xi*w[u]); U = <w, B> at the end.
+// The results are the same group elements as the reference's literal fold (pcdl.rs:427-429).
+// ---------------------------------------------------------------------------------------------------------
+template <int F>
+__global__ void __launch_bounds__(256) ipa_tail_scalars_kernel(const Fe<F>* __restrict__ cs, const Fe<F>* __restrict__ w,
+                                                               size_t m, size_t T, Fe<F>* __restrict__ sR, Fe<F>* __restrict__ sL) {
+    size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (idx >= T) return;
+    const size_t u = idx / (2 * m), i = idx - u * 2 * m;
+    const Fe<F> wu = g_ld(w + u);
+    if (i < m) { g_st(sL + idx, fe_mul<F>(g_ld(cs + m + i), wu)); g_st(sR + idx, fe_zero<F>()); }
+    else { g_st(sR + idx, fe_mul<F>(g_ld(cs + i - m), wu)); g_st(sL + idx, fe_zero<F>()); }
+}
+template <int F>
+__global__ void __launch_bounds__(256) ipa_tail_fold_kernel(Fe<F>* __restrict__ cs, Fe<F>* __restrict__ zs, size_t m,
+                                                            const Fe<F>* __restrict__ w_in, size_t nu, Fe<F>* __restrict__ w_out,
+                                                            Fe<F> xi, Fe<F> xi_inv) {
+    size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (j < m) {
+        g_st(cs + j, fe_add<F>(g_ld(cs + j), fe_mul<F>(g_ld(cs + m + j), xi_inv)));
+        g_st(zs + j, fe_add<F>(g_ld(zs + j), fe_mul<F>(g_ld(zs + m + j), xi)));
+    }
+    if (j < nu) { Fe<F> v = g_ld(w_in + j); g_st(w_out + 2 * j, v); g_st(w_out + 2 * j + 1, fe_mul<F>(v, xi)); }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -542,8 +575,20 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
     // gs = pp.Gs[0..n] (pcdl.rs:394)
     HALO_CUDA(cudaMemcpyAsync(gs, R.pp[C].d_gs, n * 64, cudaMemcpyDeviceToDevice, st));
 
+    // optional phase trace (tuning knob 7): wall clock with a stream sync at each phase boundary
+    const bool trace = R.tune[7] != 0;
+    double t_dots = 0, t_msm = 0, t_host = 0, t_fold = 0;
+    auto now = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    // fold-free tail below 2^tail_lg generators (tuning knob 3: 0 = default 15, -1 = never)
+    const int tail_lg = R.tune[3] == 0 ? 15 : R.tune[3];
+    const size_t tail_max = tail_lg < 0 ? 0 : (size_t)1 << tail_lg;
+    bool tail = false;
+    size_t T = 0, nu = 0;
+    int w_cur = 0;
+    SF *tail_s = nullptr, *tail_w = nullptr;
     size_t m = n / 2;
     for (unsigned r = 0; r < lg_n; ++r, m /= 2) {
+        double t0 = trace ? now() : 0;
         const int g = (int)std::min<size_t>(256, (m + 255) / 256);
         ipa_dots_kernel<S><<<g, 256, 0, st>>>(cs, zs, m, part);
         R.launches += 1;
@@ -551,7 +596,23 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
         if (int e = sum_partials<S>(part, g, dots, 2)) return e;
         // one pipeline, two MSMs: [0] = R = <l(c), r(G)>, [1] = L = <r(c), l(G)>  (pcdl.rs:412-418)
         uint64_t lr[24];
-        if (int e = msm_device<C>(gs + m, cs, m, 2, lr, -(ptrdiff_t)m)) return e;
+        double t1 = trace ? now() : 0;
+        if (!tail && 2 * m <= tail_max) {                 // switch: freeze the generators, start the weights at [1]
+            tail = true; T = 2 * m; nu = 1;
+            if (int e = ws_get(WS_IPA_S, 2 * T * 32, (void**)&tail_s)) return e;
+            if (int e = ws_get(WS_IPA_W, 2 * T * 32, (void**)&tail_w)) return e;
+            const SF one = fe_one<S>();
+            HALO_CUDA(cudaMemcpyAsync(tail_w, &one, 32, cudaMemcpyHostToDevice, st));
+            w_cur = 0;
+        }
+        if (tail) {
+            ipa_tail_scalars_kernel<S><<<(unsigned)((T + 255) / 256), 256, 0, st>>>(cs, tail_w + w_cur * T, m, T, tail_s, tail_s + T);
+            R.launches += 1;
+            if (int e = msm_device<C>(gs, tail_s, T, 2, lr, 0)) return e;
+        } else {
+            if (int e = msm_device<C>(gs + m, cs, m, 2, lr, -(ptrdiff_t)m)) return e;
+        }
+        double t2 = trace ? now() : 0;
         Pt Rp = H::add(H::from_words(lr), Hp.mul(dots[1]));
         Pt Lp = H::add(H::from_words(lr + 12), Hp.mul(dots[0]));
         H::to_words(Lp, out_proof + 12 * r);
@@ -563,8 +624,15 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
         HALO_CHECK(!fe_is_zero<S>(xi_next), HALO_EINVAL, "open: zero challenge has no inverse");
         const SF xi_inv = fe_inv<S>(xi_next);
         xi = xi_next;
+        double t3 = trace ? now() : 0;
         GlvScalar gk;
-        if (R.tune[2] != 1 && glv_decompose<C>(xi_next, &gk)) {
+        if (tail) {
+            const size_t th = std::max(m, nu);
+            ipa_tail_fold_kernel<S><<<(unsigned)((th + 255) / 256), 256, 0, st>>>(cs, zs, m, tail_w + w_cur * T, nu,
+                                                                                  tail_w + (1 - w_cur) * T, xi_next, xi_inv);
+            R.launches += 1;
+            w_cur = 1 - w_cur; nu *= 2;
+        } else if (R.tune[2] != 1 && glv_decompose<C>(xi_next, &gk)) {
             XYZZ<C>* folded;
             if (int e = ws_get(WS_IPA_T1, m * sizeof(XYZZ<C>), (void**)&folded)) return e;
             Fe<H::B> beta; memcpy(&beta, glv_data::GLV_BETA[C], 32);
@@ -577,11 +645,26 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
             R.launches += 1;
         }
         HALO_CUDA(cudaGetLastError());
+        if (trace) {
+            HALO_CUDA(cudaStreamSynchronize(st));
+            double t4 = now();
+            t_dots += t1 - t0; t_msm += t2 - t1; t_host += t3 - t2; t_fold += t4 - t3;
+            fprintf(stderr, "[halo trace] open round %u m=%zu: dots %.3f msm %.3f host %.3f fold %.3f ms\n", r, m, t1 - t0, t2 - t1, t3 - t2, t4 - t3);
+        }
     }
+    if (trace) fprintf(stderr, "[halo trace] open n=%zu totals: dots %.2f msm %.2f host %.2f fold %.2f ms\n", n, t_dots, t_msm, t_host, t_fold);
     // U = G_(lg n), c = c_(lg n)  (pcdl.rs:441-450)
     Affine<C> U; SF c;
-    HALO_CUDA(cudaMemcpyAsync(&U, gs, 64, cudaMemcpyDeviceToHost, st));
     HALO_CUDA(cudaMemcpyAsync(&c, cs, 32, cudaMemcpyDeviceToHost, st));
+    if (tail) {                                           // U = <w, B>
+        uint64_t uw[12];
+        if (int e = msm_device<C>(gs, tail_w + w_cur * T, T, 1, uw, 0)) return e;
+        HALO_CUDA(cudaStreamSynchronize(st));
+        memcpy(out_proof + 24 * L, uw, 96);
+        H::put_scalar(c, out_proof + 24 * L + 12);
+        return HALO_OK;
+    }
+    HALO_CUDA(cudaMemcpyAsync(&U, gs, 64, cudaMemcpyDeviceToHost, st));
     HALO_CUDA(cudaStreamSynchronize(st));
     H::to_words(xyzz_from_affine<C>(U), out_proof + 24 * L);
     H::put_scalar(c, out_proof + 24 * L + 12);

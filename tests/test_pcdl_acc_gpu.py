@@ -164,10 +164,10 @@ def test_genesis_accumulator_matches_reference_golden(hb, oracle, params, golden
 
 
 @pytest.mark.parametrize("curve", [0, 1])
-def test_fold_literal_ladder_equals_endomorphism_split(hb, oracle, params, curve):
-    """The generator fold is run both as the reference writes it (gs_l + xi*gs_r by a 255-bit ladder, pcdl.rs:427-429)
-    and with xi split as k1 + k2*lambda; both must give the oracle's proof bit for bit."""
-    import ctypes
+def test_fold_variants_give_the_same_proof(hb, oracle, params, curve):
+    """The generator fold is run (a) as the reference writes it, gs_l + xi*gs_r by a 255-bit ladder (pcdl.rs:427-429),
+    (b) with xi split as k1 + k2*lambda, and (c) with the fold-free tail starting at different lengths; every variant
+    must give the oracle's proof bit for bit."""
     O = oracle
     sf = O.SCALAR_FIELD[curve]
     n = 1 << 11
@@ -175,10 +175,10 @@ def test_fold_literal_ladder_equals_endomorphism_split(hb, oracle, params, curve
     z = O.random_scalars(sf, 1, 902)[0]
     exp = O.instance_open(curve, p, n - 1, z)
     lib = hb._lib.lib
-    for knob in (1, 0):
-        lib.halo_set_tuning(2, knob)
+    for ladder, tail in ((1, -1), (0, -1), (0, 0), (0, 5), (1, 8), (0, 1)):
+        lib.halo_set_tuning(2, ladder); lib.halo_set_tuning(3, tail)
         try:
             q = hb.pcdl.Instance.open(curve, p, n - 1, z)
         finally:
-            lib.halo_set_tuning(2, 0)
+            lib.halo_set_tuning(2, 0); lib.halo_set_tuning(3, 0)
         same_instance(O, curve, q.w, exp)
