@@ -33,6 +33,8 @@ P_BASE = 0x40000000000000000000000000000000224698fc094cf91b992d30ed00000001
 Q_SCALAR = 0x40000000000000000000000000000000224698fc0994a8dd8c46eb2100000001
 # XYZZ mixed addition = 8M + 2S (halo_b200/csrc/curve.cuh xyzz_madd); one per (point, window)
 MODMUL_PER_MADD = 10
+# dram__bytes_read.sum + dram__bytes_write.sum of one msm_accumulate launch at 2^20 (profiles/r1b_msm_accumulate_ncu_full.csv)
+TRAFFIC_BYTES_ACCUMULATE_2P20 = 563.4e6
 
 
 def parse_args():
@@ -43,6 +45,7 @@ def parse_args():
     ap.add_argument("--log-n", type=int, default=20)
     ap.add_argument("--impl", default="halo_b200", choices=["halo_b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-path", action="store_true", help="skip the secondary timings of the other rows of the path")
     return ap.parse_args()
 
 
@@ -175,6 +178,65 @@ def run_reference(args, rank):
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
+
+
+def measure_path(lib, check, halo_b200, torch, stream, d_pts, h_sc, log_n):
+    """Secondary timings of the other rows of the hot path at the same size (reported, not the headline): NTT / iNTT,
+    batched commit, IPA opening, succinct check and full check.  Device-resident where the ABI allows it."""
+    import numpy as np
+    n = 1 << log_n
+    u64p = ctypes.POINTER(ctypes.c_uint64)
+    out = {}
+
+    def ev_ms(fn, reps=3):
+        best = None
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream); fn(); e1.record(stream); e1.synchronize()
+            t = e0.elapsed_time(e1)
+            best = t if best is None else min(best, t)
+        return best
+
+    for b in (1, 16):
+        x = torch.randint(-(1 << 63), (1 << 63) - 1, (b * n, 4), dtype=torch.int64, device="cuda")
+        x[:, 3] &= (1 << 62) - 1
+        f = lambda: check(lib.halo_ntt_dev(0, ctypes.c_void_p(x.data_ptr()), ctypes.c_uint(log_n), ctypes.c_size_t(b), 0, None))
+        f()
+        ms = ev_ms(f)
+        out[f"ntt_2^{log_n}_x{b}"] = {"ms": ms, "elements_per_s": b * n / (ms * 1e-3),
+                                      "gbutterfly_per_s": b * n * log_n / 2 / (ms * 1e-3) / 1e9}
+        del x
+    # the points of the MSM benchmark double as generators; S and H are two more of them
+    gs = d_pts.cpu().numpy().view(np.uint64)
+    sh = np.zeros((2, 8), dtype=np.uint64)
+    check(lib.halo_gen_points(PALLAS, ctypes.c_uint64(5), ctypes.c_size_t(0), ctypes.c_size_t(2), sh.ctypes.data_as(u64p)))
+    halo_b200.pp.reset(PALLAS)
+    halo_b200.pp.set_pp(PALLAS, gs, sh[0], sh[1])
+    p = h_sc.numpy().view(np.uint64)
+    z = p[7].copy()
+    if n <= (1 << 20):
+        # the 16 commits of a prover round (protocol.rs:114,263) as one pipeline over the resident generators
+        b = 16
+        cols = torch.randint(-(1 << 63), (1 << 63) - 1, (b * n, 4), dtype=torch.int64, device="cuda")
+        cols[:, 3] &= (1 << 62) - 1
+        res = np.zeros((b, 12), dtype=np.uint64)
+        f = lambda: check(lib.halo_msm_batch_dev(PALLAS, None, ctypes.c_size_t(0), ctypes.c_void_p(cols.data_ptr()),
+                                                 ctypes.c_size_t(n), ctypes.c_size_t(b), res.ctypes.data_as(u64p)))
+        f()
+        ms = ev_ms(f, reps=2)
+        out[f"commit_batch16_2^{log_n}"] = {"ms": ms, "points_per_s": b * n / (ms * 1e-3)}
+        del cols
+    C = halo_b200.pcdl.commit(PALLAS, p, n - 1)
+    best = None
+    for _ in range(2):
+        t = time.perf_counter(); pi, v = halo_b200.pcdl.open_without_eval(PALLAS, p, C, n - 1, z, None); dt = time.perf_counter() - t
+        best = dt if best is None else min(best, dt)
+    out[f"pcdl_open_2^{log_n}_e2e"] = {"ms": best * 1e3}
+    q = halo_b200.pcdl.Instance.new(PALLAS, C, n - 1, z, v, pi)
+    t = time.perf_counter(); q.succinct_check(); out["pcdl_succinct_check"] = {"ms": (time.perf_counter() - t) * 1e3}
+    t = time.perf_counter(); q.check(); out[f"pcdl_check_2^{log_n}"] = {"ms": (time.perf_counter() - t) * 1e3}
+    halo_b200.pp.reset(PALLAS)
+    return out
 
 
 def run_halo(args, rank, world, local_rank):
@@ -330,7 +392,8 @@ def run_halo(args, rank, world, local_rank):
     value = n_pts * args.steps / (tot_ms * 1e-3)
     e2e_value = n_pts * args.steps / (e2e_ms * 1e-3)
     acc_ms = stage_ms.get("accumulate", 0.0) / args.steps
-    c = min(16, max(4, args.log_n - 4)); nw = 255 // c + 1          # msm.cu pick_window / make_plan
+    lg = args.log_n
+    c = 16 if lg >= 20 else 15 if lg >= 17 else 13 if lg >= 15 else 8; nw = 255 // c + 1     # msm.cu pick_window / make_plan
     roof = None
     if acc_ms > 0:
         # dominant kernel: bucket accumulation.  Algorithmic work per launch: one mixed addition (10 modmul) per
@@ -341,13 +404,18 @@ def run_halo(args, rank, world, local_rank):
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         roof = {"kernel": "msm_accumulate", "bound": "int32-pipe", "achieved": ach / 1e9, "peak": peak_modmul / 1e9,
-                "unit": "Gmodmul/s", "frac": ach / peak_modmul, "traffic": None,
+                "unit": "Gmodmul/s", "frac": ach / peak_modmul, "traffic": TRAFFIC_BYTES_ACCUMULATE_2P20 if args.log_n == 20 else None,
+                "traffic_source": "ncu --set full, profiles/r1b_msm_accumulate_ncu_full.csv (dram read + write per launch)",
                 "peak_source": "measured live: halo_bench_modmul (dependent 255-bit Montgomery multiplications)",
                 "ms_per_launch": acc_ms, "share_of_step": acc_ms / (tot_ms / args.steps),
                 "hbm": {"bound": "hbm", "achieved": abytes / (acc_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": abytes / (acc_ms * 1e-3) / 1e9 / hbm_peak,
                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
                 "stages_ms": {kk: v / args.steps for kk, v in stage_ms.items()}}
+
+    path = None
+    if world == 1 and not args.no_path:
+        path = measure_path(lib, check, halo_b200, torch, stream, d_pts, h_sc, args.log_n)
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
@@ -364,7 +432,7 @@ def run_halo(args, rank, world, local_rank):
                    "l2": "flushed between timed iterations (256 MiB memset outside the event pair)"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(k * 96), "d2h_bytes_per_step": int(nw * 128),
                 "ms_per_step": e2e_ms / args.steps},
-        "gpu_launches": int(launches), "verified": verified, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+        "gpu_launches": int(launches), "verified": verified, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu, "path": path,
     }))
     if dist is not None:
         dist.destroy_process_group()

@@ -213,6 +213,9 @@ int halo_init(int device) {
     HALO_CUDA(cudaGetDeviceProperties(&prop, R.device));
     R.sm_count = prop.multiProcessorCount;
     HALO_CUDA(cudaStreamCreateWithFlags(&R.own_stream, cudaStreamNonBlocking));
+    HALO_CUDA(cudaStreamCreateWithFlags(&R.copy_stream, cudaStreamNonBlocking));
+    HALO_CUDA(cudaEventCreateWithFlags(&R.copy_done, cudaEventDisableTiming));
+    HALO_CUDA(cudaEventCreateWithFlags(&R.copy_go, cudaEventDisableTiming));
     R.stream = R.own_stream;
     R.arena.resize(WS_COUNT);
     R.inited = true;
@@ -231,6 +234,10 @@ int halo_shutdown(void) {
     R.pinned = nullptr; R.pinned_cap = 0;
     for (int f = 0; f < 2; ++f) { if (R.ntt_tw[f]) cudaFree(R.ntt_tw[f]); R.ntt_tw[f] = nullptr; R.ntt_logmax[f] = 0; }
     cudaStreamDestroy(R.own_stream);
+    if (R.copy_stream) cudaStreamDestroy(R.copy_stream);
+    if (R.copy_done) cudaEventDestroy(R.copy_done);
+    if (R.copy_go) cudaEventDestroy(R.copy_go);
+    R.copy_stream = nullptr; R.copy_done = nullptr;
     R.own_stream = R.stream = nullptr;
     R.inited = false;
     return HALO_OK;
@@ -372,12 +379,21 @@ int halo_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_
         if (int e = ws_get(WS_SCALARS, k * 32, &d_s)) return e;
         HALO_CUDA(cudaMemcpyAsync(d_s, scalars, k * 32, cudaMemcpyHostToDevice, R.stream));
         if (bases_xy) {
+            // the bases go up on a second stream while the scalar half of the pipeline (digits, scan, scatter, task
+            // list) runs; only the accumulation waits for them.  The previous call has finished (MSM calls are
+            // synchronous), so the workspace is free to overwrite.
             if (int e = ws_get(WS_BASES, k * 64, &d_b)) return e;
-            HALO_CUDA(cudaMemcpyAsync(d_b, bases_xy + 8 * base_off, k * 64, cudaMemcpyHostToDevice, R.stream));
+            HALO_CUDA(cudaEventRecord(R.copy_go, R.stream));                 // scalars first: they gate the pipeline
+            HALO_CUDA(cudaStreamWaitEvent(R.copy_stream, R.copy_go, 0));
+            HALO_CUDA(cudaMemcpyAsync(d_b, bases_xy + 8 * base_off, k * 64, cudaMemcpyHostToDevice, R.copy_stream));
+            HALO_CUDA(cudaEventRecord(R.copy_done, R.copy_stream));
+            R.wait_copy = true;
             base_off = 0;
         }
     }
-    return halo_msm_dev(curve, d_b, base_off, d_s, k, out_xyz);
+    int rc = halo_msm_dev(curve, d_b, base_off, d_s, k, out_xyz);
+    if (R.wait_copy) { cudaStreamSynchronize(R.copy_stream); R.wait_copy = false; }   // error paths: never leave a copy in flight
+    return rc;
 }
 
 int halo_msm_batch(int curve, size_t base_off, const uint64_t* scalars, size_t k, size_t b, uint64_t* out_xyz) {

@@ -29,6 +29,9 @@ struct Runtime {
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
     int sm_count = 148;
+    cudaStream_t copy_stream = nullptr;   // second stream: the base-point upload of halo_msm overlaps the scalar pipeline
+    cudaEvent_t copy_done = nullptr, copy_go = nullptr;
+    bool wait_copy = false;               // the next MSM must wait for copy_done before touching its bases
     ResidentParams pp[2];
     std::vector<DeviceBuf> arena;   // indexed slots
     void* pinned = nullptr;         // pinned host staging
