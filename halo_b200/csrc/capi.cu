@@ -62,6 +62,9 @@ template <int C> int acc_verifier(const uint64_t*, size_t, const uint64_t*);
 template <int S> int hpoly_coeffs(const uint64_t*, const uint64_t*, size_t, unsigned, uint64_t*);
 template <int C> int hpoly_commit_words(const uint64_t*, unsigned, uint64_t*);
 template <int S> void hpoly_eval_words(const uint64_t*, unsigned, const uint64_t*, uint64_t*);
+template <int S> int scalar_dot_host(const uint64_t*, const uint64_t*, size_t, uint64_t*);
+template <int S> int construct_powers_host(const uint64_t*, size_t, uint64_t*);
+template <int F> int poly_mul_host(const uint64_t*, size_t, const uint64_t*, size_t, uint64_t*);
 
 // ---- synthetic inputs: P_i = k_i * G with k_i = splitmix64(seed, i) | 1  (distinct with overwhelming probability) ----
 __host__ __device__ inline u64 splitmix64(u64 x) {
@@ -611,5 +614,24 @@ int halo_hpoly_eval(int field, const uint64_t* xis, size_t lg_n, const uint64_t 
     HALO_CHECK((field == 0 || field == 1) && xis && z && out, HALO_EINVAL, "hpoly_eval: bad argument");
     if (field == 0) hpoly_eval_words<0>(xis, (unsigned)lg_n, z, out); else hpoly_eval_words<1>(xis, (unsigned)lg_n, z, out);
     return HALO_OK;
+}
+}  // extern "C"
+
+extern "C" {
+int halo_scalar_dot(int field, const uint64_t* xs, const uint64_t* ys, size_t n, uint64_t out[4]) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK((field == 0 || field == 1) && out && ((xs && ys) || n == 0), HALO_EINVAL, "scalar_dot: bad argument");
+    return field == 0 ? scalar_dot_host<0>(xs, ys, n, out) : scalar_dot_host<1>(xs, ys, n, out);
+}
+int halo_construct_powers(int field, const uint64_t z[4], size_t n, uint64_t* out) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK((field == 0 || field == 1) && z && (out || n == 0), HALO_EINVAL, "construct_powers: bad argument");
+    return field == 0 ? construct_powers_host<0>(z, n, out) : construct_powers_host<1>(z, n, out);
+}
+int halo_poly_mul(int field, const uint64_t* a, size_t la, const uint64_t* b, size_t lb, uint64_t* out) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK((field == 0 || field == 1) && ((a && b && out) || la == 0 || lb == 0), HALO_EINVAL, "poly_mul: bad argument");
+    HALO_CHECK(la + lb <= ((size_t)1 << 30), HALO_EINVAL, "poly_mul: product too long");
+    return field == 0 ? poly_mul_host<0>(a, la, b, lb, out) : poly_mul_host<1>(a, la, b, lb, out);
 }
 }  // extern "C"

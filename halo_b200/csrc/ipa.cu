@@ -954,4 +954,45 @@ void hpoly_eval_words(const uint64_t* xis, unsigned lg_n, const uint64_t* z, uin
 template void hpoly_eval_words<0>(const uint64_t*, unsigned, const uint64_t*, uint64_t*);
 template void hpoly_eval_words<1>(const uint64_t*, unsigned, const uint64_t*, uint64_t*);
 
+
+// ---- group.rs:43-66 exposed directly: scalar_dot and construct_powers on the device, host in / host out ----
+template <int S>
+int scalar_dot_host(const uint64_t* a, const uint64_t* b, size_t n, uint64_t* out) {
+    Runtime& R = rt();
+    Fe<S> acc = fe_zero<S>();
+    if (n) {
+        Fe<S>*da, *db, *part;
+        if (int e = ws_get(WS_IPA_C, n * 32, (void**)&da)) return e;
+        if (int e = ws_get(WS_IPA_Z, n * 32, (void**)&db)) return e;
+        if (int e = ws_get(WS_IPA_T0, 2 * 256 * 32 + 64, (void**)&part)) return e;
+        HALO_CUDA(cudaMemcpyAsync(da, a, n * 32, cudaMemcpyHostToDevice, R.stream));
+        HALO_CUDA(cudaMemcpyAsync(db, b, n * 32, cudaMemcpyHostToDevice, R.stream));
+        const int g = (int)std::min<size_t>(256, (n + 255) / 256);
+        ipa_dot1_kernel<S><<<g, 256, 0, R.stream>>>(da, db, n, part);
+        R.launches += 1;
+        if (int e = sum_partials<S>(part, g, &acc, 1)) return e;
+    }
+    memcpy(out, &acc, 32);
+    return HALO_OK;
+}
+template int scalar_dot_host<0>(const uint64_t*, const uint64_t*, size_t, uint64_t*);
+template int scalar_dot_host<1>(const uint64_t*, const uint64_t*, size_t, uint64_t*);
+
+template <int S>
+int construct_powers_host(const uint64_t* z, size_t n, uint64_t* out) {
+    Runtime& R = rt();
+    if (n == 0) return HALO_OK;
+    Fe<S>* d;
+    if (int e = ws_get(WS_IPA_Z, n * 32, (void**)&d)) return e;
+    Fe<S> zz; memcpy(&zz, z, 32);
+    ipa_powers_kernel<S><<<(unsigned)((n / 16 + 128) / 128), 128, 0, R.stream>>>(d, n, zz, fe_one<S>());
+    R.launches += 1;
+    HALO_CUDA(cudaGetLastError());
+    HALO_CUDA(cudaMemcpyAsync(out, d, n * 32, cudaMemcpyDeviceToHost, R.stream));
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
+    return HALO_OK;
+}
+template int construct_powers_host<0>(const uint64_t*, size_t, uint64_t*);
+template int construct_powers_host<1>(const uint64_t*, size_t, uint64_t*);
+
 }  // namespace halo

@@ -286,4 +286,40 @@ int ntt_fold_device(const Fe<F>* coeffs, size_t len, int log_n, Fe<F>* out) {
 template int ntt_fold_device<0>(const Fe<0>*, size_t, int, Fe<0>*);
 template int ntt_fold_device<1>(const Fe<1>*, size_t, int, Fe<1>*);
 
+
+// pointwise product of two evaluation vectors (the middle step of an FFT-based polynomial product)
+template <int F>
+__global__ void __launch_bounds__(256) ntt_pointwise_mul_kernel(Fe<F>* __restrict__ a, const Fe<F>* __restrict__ b, size_t n) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    st_fe(a + i, fe_mul<F>(ld_fe(a + i), ld_fe(b + i)));
+}
+
+// Product of two coefficient vectors as ark-poly's `&a * &b` computes it for DensePolynomial (protocol.rs:132-139,
+// 198-199; pcdl.rs:215): evaluate both on the domain of size next_pow2(la + lb - 1), multiply pointwise, interpolate.
+// out receives la + lb - 1 coefficients.  Everything stays on the device between the three transforms.
+template <int F>
+int poly_mul_host(const uint64_t* a, size_t la, const uint64_t* b, size_t lb, uint64_t* out) {
+    Runtime& R = rt();
+    if (la == 0 || lb == 0) return HALO_OK;
+    const size_t lo = la + lb - 1;
+    int log_n = 0; while (((size_t)1 << log_n) < lo) ++log_n;
+    const size_t N = (size_t)1 << log_n;
+    Fe<F>*buf, *scratch;
+    if (int e = ws_get(WS_NTT0, 2 * N * 32, (void**)&buf)) return e;
+    if (int e = ws_get(WS_NTT1, 2 * N * 32, (void**)&scratch)) return e;
+    HALO_CUDA(cudaMemsetAsync(buf, 0, 2 * N * 32, R.stream));
+    HALO_CUDA(cudaMemcpyAsync(buf, a, la * 32, cudaMemcpyHostToDevice, R.stream));
+    HALO_CUDA(cudaMemcpyAsync(buf + N, b, lb * 32, cudaMemcpyHostToDevice, R.stream));
+    if (int e = ntt_device<F>(buf, scratch, log_n, 2, false, nullptr)) return e;          // both forward transforms as a batch
+    ntt_pointwise_mul_kernel<F><<<(unsigned)((N + 255) / 256), 256, 0, R.stream>>>(scratch, scratch + N, N);
+    R.launches += 1;
+    if (int e = ntt_device<F>(scratch, buf, log_n, 1, true, nullptr)) return e;
+    HALO_CUDA(cudaMemcpyAsync(out, buf, lo * 32, cudaMemcpyDeviceToHost, R.stream));
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
+    return HALO_OK;
+}
+template int poly_mul_host<0>(const uint64_t*, size_t, const uint64_t*, size_t, uint64_t*);
+template int poly_mul_host<1>(const uint64_t*, size_t, const uint64_t*, size_t, uint64_t*);
+
 }  // namespace halo

@@ -58,3 +58,21 @@ def msm_batch_resident(curve, xs, base_off=0):
     check(lib.halo_msm_batch(curve, ctypes.c_size_t(base_off), ptr(xs.reshape(-1, 4)), ctypes.c_size_t(k),
                              ctypes.c_size_t(b), ptr(out)))
     return out
+
+
+def scalar_dot(field, xs, ys):
+    """≙ scalar_dot (group.rs:43-45): sum_i xs[i]*ys[i] over min(len) pairs (zip semantics)."""
+    _lib.ensure_init()
+    xs, ys = as_u64(xs, 4), as_u64(ys, 4)
+    n = min(xs.shape[0], ys.shape[0])
+    out = np.empty(4, dtype=np.uint64)
+    check(lib.halo_scalar_dot(field, ptr(xs) if n else None, ptr(ys) if n else None, ctypes.c_size_t(n), ptr(out)))
+    return out
+
+
+def construct_powers(field, z, n):
+    """≙ construct_powers (group.rs:58-66): (1, z, ..., z^(n-1))."""
+    _lib.ensure_init()
+    out = np.empty((n, 4), dtype=np.uint64)
+    check(lib.halo_construct_powers(field, ptr(as_u64(z, 4).reshape(4)), ctypes.c_size_t(n), ptr(out) if n else None))
+    return out

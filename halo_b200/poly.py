@@ -165,3 +165,15 @@ class Evals:
 
     def __eq__(self, o):
         return isinstance(o, Evals) and self.dom == o.dom and bool((self.evals == o.evals).all())
+
+
+def poly_mul(field, a, b):
+    """≙ `&a * &b` on DensePolynomial (FFT-based product inside ark-poly; protocol.rs:132-139,198-199, pcdl.rs:215).
+    Returns the coefficients with trailing zeros stripped."""
+    _lib.ensure_init()
+    a, b = _strip(as_u64(a, 4)), _strip(as_u64(b, 4))
+    if a.shape[0] == 0 or b.shape[0] == 0:
+        return np.zeros((0, 4), dtype=np.uint64)
+    out = np.empty((a.shape[0] + b.shape[0] - 1, 4), dtype=np.uint64)
+    check(lib.halo_poly_mul(field, ptr(a), ctypes.c_size_t(a.shape[0]), ptr(b), ctypes.c_size_t(b.shape[0]), ptr(out)))
+    return _strip(out)

@@ -118,6 +118,13 @@ int halo_ntt_dev(int field, void* d_data, unsigned log_n, size_t b, int inverse,
  * when len > N, as ark-poly's evaluate_over_domain_by_ref does (protocol.rs:140-141 relies on the latter). */
 int halo_poly_evaluate(int field, const uint64_t* coeffs, size_t len, unsigned log_n, uint64_t* out_evals);
 
+/* coefficients of a*b (la + lb - 1 of them)  ≙ `&a * &b` on DensePolynomial (protocol.rs:132-139,198-199; pcdl.rs:215):
+ * two forward transforms, a pointwise product and one inverse transform on the domain of size next_pow2(la+lb-1) */
+int halo_poly_mul(int field, const uint64_t* a, size_t la, const uint64_t* b, size_t lb, uint64_t* out);
+/* ≙ scalar_dot (group.rs:43-45) and construct_powers (group.rs:58-66): out[i] = z^i, i < n */
+int halo_scalar_dot(int field, const uint64_t* xs, const uint64_t* ys, size_t n, uint64_t out[4]);
+int halo_construct_powers(int field, const uint64_t z[4], size_t n, uint64_t* out);
+
 /* ---- benchmarks of the arithmetic itself (denominator of the integer roofline) -------------------------- */
 /* Runs `iters` dependent Montgomery multiplications in each of blocks*threads threads (4 independent chains per
  * thread); returns elapsed milliseconds measured with CUDA events in *ms and a checksum in out[4]. */

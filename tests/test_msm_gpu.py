@@ -198,3 +198,38 @@ def test_msm_degenerate_scalar_distributions(hb, oracle, kind):
     sc = np.ascontiguousarray(sc, dtype=np.uint64)
     got = hb.group.point_dot_affine(0, sc, pts)
     assert (_aff(O, 0, got) == _aff(O, 0, O.msm(0, pts, sc))).all()
+
+
+@pytest.mark.parametrize("curve", [0, 1])
+@pytest.mark.parametrize("log_k", [21, 22])
+def test_msm_beyond_oracle_sizes_known_discrete_logs(hb, oracle, curve, log_k):
+    """BASELINE's largest sizes (2^21, 2^22) are out of the CPU oracle's reach in a test; the points are generated as
+    m_i*G on the device with known 64-bit m_i, so sum s_i*P_i must equal (sum s_i*m_i mod r)*G — one scalar
+    multiplication, checked with the oracle."""
+    import ctypes
+    O = oracle
+    lib = hb._lib.lib
+    lib.halo_gen_point_multiplier.restype = ctypes.c_uint64
+    sf = O.SCALAR_FIELD[curve]
+    r = O.MODULUS[sf]
+    k = 1 << log_k
+    seed = 77 + log_k
+    pts = np.empty((k, 8), dtype=np.uint64)
+    hb._lib.check(lib.halo_gen_points(curve, ctypes.c_uint64(seed), ctypes.c_size_t(0), ctypes.c_size_t(k), hb._lib.ptr(pts.reshape(-1))))
+    for i in (0, 1, k - 1):                              # spot-check the generator against the oracle
+        m = lib.halo_gen_point_multiplier(ctypes.c_uint64(seed), ctypes.c_uint64(i))
+        e = O.point_mul(curve, O.generator(curve), O.ints_to_mont(sf, [m])[0])
+        assert (_aff(O, curve, e)[0] == pts[i]).all()
+    sc = O.random_scalars(sf, k, log_k)
+    got = hb.group.point_dot_affine(curve, sc, pts)
+    # sum s_i m_i with numpy object arithmetic (scalars are Montgomery limbs: value * R^-1)
+    with np.errstate(over="ignore"):
+        x = np.uint64(seed) + np.arange(k, dtype=np.uint64) * np.uint64(0x2545F4914F6CDD1D) + np.uint64(0x9E3779B97F4A7C15)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        ms = (x ^ (x >> np.uint64(31))) | np.uint64(1)
+    s = sc.astype(object)
+    vals = s[:, 0] + (s[:, 1] << 64) + (s[:, 2] << 128) + (s[:, 3] << 192)
+    t = int((vals * ms.astype(object)).sum()) % r * pow(1 << 256, -1, r) % r
+    exp = O.point_mul(curve, O.generator(curve), O.ints_to_mont(sf, [t])[0])
+    assert (_aff(O, curve, got) == _aff(O, curve, exp)).all()

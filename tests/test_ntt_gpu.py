@@ -122,3 +122,43 @@ def test_evals_wrapper(hb, oracle, field):
     # divide_by_vanishing: Z_H is zero on H itself -> the reference panics; on a larger domain it divides
     with pytest.raises(hb.PreconditionError):
         ea.divide_by_vanishing(dom)
+
+
+@pytest.mark.parametrize("field", [0, 1])
+@pytest.mark.parametrize("la,lb", [(1, 1), (2, 3), (20, 30), (257, 255), (1000, 24), (4096, 4096)])
+def test_poly_mul_matches_schoolbook(hb, oracle, field, la, lb):
+    """`&a * &b` (protocol.rs:132-139,198-199): exact product coefficients."""
+    O = oracle
+    p = O.MODULUS[field]
+    a, b = O.random_scalars(field, la, la), O.random_scalars(field, lb, 7 * lb)
+    got = hb.poly.poly_mul(field, a, b)
+    ai = [O.from_mont(field, x) for x in a]
+    bi = [O.from_mont(field, x) for x in b]
+    if la * lb <= 1 << 16:
+        exp = [0] * (la + lb - 1)
+        for i, x in enumerate(ai):
+            for j, y in enumerate(bi):
+                exp[i + j] = (exp[i + j] + x * y) % p
+        assert (got == O.ints_to_mont(field, exp)).all()
+    else:                                   # large: check the product at a random point instead
+        z = 0x1234567890abcdef1234567
+        ev = lambda c: sum(v * pow(z, k, p) for k, v in enumerate(c)) % p
+        assert ev([O.from_mont(field, x) for x in got]) == ev(ai) * ev(bi) % p
+    assert hb.poly.poly_mul(field, a, np.zeros((3, 4), dtype=np.uint64)).shape[0] == 0
+
+
+@pytest.mark.parametrize("field", [0, 1])
+def test_scalar_dot_and_construct_powers(hb, oracle, field):
+    """group.rs:43-45 and :58-66."""
+    O = oracle
+    p = O.MODULUS[field]
+    for n in (0, 1, 5, 1000, 70001):
+        a, b = O.random_scalars(field, max(n, 1), 3)[:n], O.random_scalars(field, max(n, 1), 4)[:n]
+        exp = sum(O.from_mont(field, x) * O.from_mont(field, y) for x, y in zip(a, b)) % p
+        assert O.from_mont(field, hb.group.scalar_dot(field, a, b)) == exp
+    z = O.random_scalars(field, 1, 9)[0]
+    zi = O.from_mont(field, z)
+    pw = hb.group.construct_powers(field, z, 1000)
+    assert [O.from_mont(field, x) for x in pw[:40]] == [pow(zi, k, p) for k in range(40)]
+    assert O.from_mont(field, pw[999]) == pow(zi, 999, p)
+    assert hb.group.construct_powers(field, z, 0).shape == (0, 4)
