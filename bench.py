@@ -235,7 +235,29 @@ def measure_path(lib, check, halo_b200, torch, stream, d_pts, h_sc, log_n):
     q = halo_b200.pcdl.Instance.new(PALLAS, C, n - 1, z, v, pi)
     t = time.perf_counter(); q.succinct_check(); out["pcdl_succinct_check"] = {"ms": (time.perf_counter() - t) * 1e3}
     t = time.perf_counter(); q.check(); out[f"pcdl_check_2^{log_n}"] = {"ms": (time.perf_counter() - t) * 1e3}
+    if log_n > 14:                                   # the size the CPU leg opens (bounded sample)
+        ps = p[: 1 << 14]
+        Cs = halo_b200.pcdl.commit(PALLAS, ps, (1 << 14) - 1)
+        t = time.perf_counter(); halo_b200.pcdl.open_without_eval(PALLAS, ps, Cs, (1 << 14) - 1, z, None)
+        out["pcdl_open_2^14_e2e"] = {"ms": (time.perf_counter() - t) * 1e3}
     halo_b200.pp.reset(PALLAS)
+    return out
+
+
+def cpu_path_leg():
+    """CPU restatement timings for the other rows (bounded samples): NTT 2^20 and a PC_DL opening at 2^14."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import numpy as np
+    import oracle_lib as O
+    O.set_threads(os.cpu_count() or 1)
+    out = {}
+    x = O.random_scalars(0, 1 << 20, 3)
+    t = time.perf_counter(); O.ntt(0, x); out["ntt_2^20_ms"] = (time.perf_counter() - t) * 1e3
+    n = 1 << 14
+    gs = O.points_arith(PALLAS, n + 2)
+    O.pp_set(PALLAS, gs[:n], gs[n], gs[n + 1])
+    p = O.random_scalars(0, n, 4)
+    t = time.perf_counter(); O.instance_open(PALLAS, p, n - 1, p[3]); out["pcdl_instance_open_2^14_ms"] = (time.perf_counter() - t) * 1e3
     return out
 
 
@@ -422,6 +444,8 @@ def run_halo(args, rank, world, local_rank):
         kk, cores, times = cpu_msm_leg(min(args.log_n, 20), 2)
         cpu = {"value": kk / min(times), "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"best of 2 x MSM of 2^{min(args.log_n, 20)} points, CPU restatement (oracle/msm.hpp), all host threads"}
+        if not args.no_path:
+            cpu["path"] = cpu_path_leg()
 
     print(json.dumps({
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),

@@ -70,6 +70,7 @@ int halo_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const
 /* experiment knobs (0 = default): key 0 = bucket-reduction occupancy variant, key 1 = unused,
  * key 2 = 1 forces the literal 255-bit ladder in the IPA fold instead of the endomorphism split,
  * key 3 = log2 of the vector length below which the IPA stops folding generators (-1 never, 0 default),
+ * key 4 = 1 disables the radix-4 (two-at-once) generator folds of the IPA,
  * key 7 = 1 prints a per-round phase trace of halo_pcdl_open to stderr */
 int halo_set_tuning(int key, int value);
 /* window width override for experiments (0 = automatic) */

@@ -175,10 +175,11 @@ def test_fold_variants_give_the_same_proof(hb, oracle, params, curve):
     z = O.random_scalars(sf, 1, 902)[0]
     exp = O.instance_open(curve, p, n - 1, z)
     lib = hb._lib.lib
-    for ladder, tail in ((1, -1), (0, -1), (0, 0), (0, 5), (1, 8), (0, 1)):
-        lib.halo_set_tuning(2, ladder); lib.halo_set_tuning(3, tail)
+    # (literal ladder?, log2 of the tail length or -1 = never / 0 = default, radix-4 folds off?)
+    for ladder, tail, no_r4 in ((1, -1, 0), (0, -1, 1), (0, -1, 0), (0, 0, 0), (0, 5, 1), (0, 3, 0), (0, 4, 0), (1, 8, 0), (0, 1, 0)):
+        lib.halo_set_tuning(2, ladder); lib.halo_set_tuning(3, tail); lib.halo_set_tuning(4, no_r4)
         try:
             q = hb.pcdl.Instance.open(curve, p, n - 1, z)
         finally:
-            lib.halo_set_tuning(2, 0); lib.halo_set_tuning(3, 0)
+            lib.halo_set_tuning(2, 0); lib.halo_set_tuning(3, 0); lib.halo_set_tuning(4, 0)
         same_instance(O, curve, q.w, exp)
