@@ -158,6 +158,60 @@ __global__ void bench_imad_kernel(int iters, unsigned long long* out) {
     if (tid == 0) out[0] = s;
 }
 
+// issue-rate probes for the pipes a field multiplication could use: mode 1 = DFMA, 2 = DFMA and IMAD.WIDE interleaved
+// 1:1, 3 = 32-bit IMAD, 4 = IADD3 with carry chains
+__global__ void bench_pipe_kernel(int mode, int iters, unsigned long long* out) {
+    u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long acc[8];
+    double f[8];
+    u32 x = tid * 2654435761u + 12345u, y = tid ^ 0x9e3779b9u;
+    double fx = 1.0 + tid * 1e-9, fy = 0.999999 + tid * 1e-12;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { acc[j] = tid + j; f[j] = 1.0 + j; }
+    if (mode == 1) {
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = __fma_rz(fx, f[j], fy);
+        }
+    } else if (mode == 2) {
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                f[j] = __fma_rz(fx, f[j], fy);
+                acc[j] = (unsigned long long)x * (u32)(y + j) + acc[j];
+            }
+            x += (u32)acc[0];
+        }
+    } else if (mode == 3) {
+        u32 a[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] = tid + j;
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = a[j] * x + y;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] ^= a[j];
+    } else {
+        u32 a[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] = tid + j;
+        for (int it = 0; it < iters; ++it) {
+            asm volatile("add.cc.u32 %0, %0, %8; addc.cc.u32 %1, %1, %9; addc.cc.u32 %2, %2, %8; addc.cc.u32 %3, %3, %9;"
+                         "addc.cc.u32 %4, %4, %8; addc.cc.u32 %5, %5, %9; addc.cc.u32 %6, %6, %8; addc.u32 %7, %7, %9;"
+                         : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7])
+                         : "r"(x), "r"(y));
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] ^= a[j];
+    }
+    unsigned long long s = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s ^= acc[j] ^ (unsigned long long)__double_as_longlong(f[j]);
+    if (s == 0x123456789abcdefULL) out[tid & 1023] = s;
+    if (tid == 0) out[0] = s;
+}
+
 }  // namespace halo
 
 using namespace halo;
@@ -476,6 +530,26 @@ int halo_bench_imad(int blocks, int threads, int iters, float* ms, uint64_t* out
     for (int rep = 0; rep < 2; ++rep) {
         HALO_CUDA(cudaEventRecord(e0, R.stream));
         bench_imad_kernel<<<blocks, threads, 0, R.stream>>>(iters, (unsigned long long*)d);
+        HALO_CUDA(cudaEventRecord(e1, R.stream));
+        HALO_CUDA(cudaStreamSynchronize(R.stream));
+    }
+    HALO_CUDA(cudaGetLastError());
+    HALO_CUDA(cudaEventElapsedTime(ms, e0, e1));
+    HALO_CUDA(cudaMemcpy(out, d, 8, cudaMemcpyDeviceToHost));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return HALO_OK;
+}
+
+int halo_bench_pipe(int mode, int blocks, int threads, int iters, float* ms, uint64_t* out) {
+    LOCK(); NEED_INIT();
+    Runtime& R = rt();
+    void* d;
+    if (int e = ws_get(WS_TMP0, 1024 * 32, &d)) return e;
+    cudaEvent_t e0, e1;
+    HALO_CUDA(cudaEventCreate(&e0)); HALO_CUDA(cudaEventCreate(&e1));
+    for (int rep = 0; rep < 2; ++rep) {
+        HALO_CUDA(cudaEventRecord(e0, R.stream));
+        bench_pipe_kernel<<<blocks, threads, 0, R.stream>>>(mode, iters, (unsigned long long*)d);
         HALO_CUDA(cudaEventRecord(e1, R.stream));
         HALO_CUDA(cudaStreamSynchronize(R.stream));
     }

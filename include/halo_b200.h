@@ -132,6 +132,9 @@ int halo_construct_powers(int field, const uint64_t z[4], size_t n, uint64_t* ou
 int halo_bench_modmul(int field, int blocks, int threads, int iters, float* ms, uint64_t out[4]);
 /* raw IMAD.WIDE.U32 issue rate: `iters` x 8 independent wide multiply-adds per thread */
 int halo_bench_imad(int blocks, int threads, int iters, float* ms, uint64_t* out);
+/* issue rate of other candidate pipes, `iters` x 8 independent operations per thread: mode 1 = DFMA,
+ * 2 = DFMA and IMAD.WIDE interleaved 1:1 (8 + 8 per iteration), 3 = 32-bit IMAD, 4 = carry-chained IADD */
+int halo_bench_pipe(int mode, int blocks, int threads, int iters, float* ms, uint64_t* out);
 
 /* ---- instrumentation ------------------------------------------------------------------------------------- */
 /* When enabled, every MSM records CUDA events between its pipeline stages on the stream it launches on;

@@ -10,6 +10,7 @@
 // and the blob reader restates the bincode `standard()` varint layout consumed
 // at crates/group/src/pp.rs:36-53.
 #include "pcdl.hpp"
+#include "plonk.hpp"
 #include <cstdio>
 #include <map>
 
@@ -160,6 +161,29 @@ static int open_impl(const u64* coeffs, size_t len, size_t d, const u64* z, cons
     return 0;
 }
 
+
+template <int CID>
+static int plonk_prove_impl(unsigned lg_n, const u64* polys, const u64* w_evals, const u64* pub, size_t n_pub,
+                            const u64* acc_prev, u64* out) {
+    auto in = plonk::input_from_flat<CID>(lg_n, polys, w_evals, pub, n_pub, acc_prev);
+    auto pi = plonk::naive_prover<CID>(in);
+    plonk::proof_to_flat<CID>(pi, lg_n, out);
+    return 0;
+}
+template <int CID>
+static int plonk_verify_impl(unsigned lg_n, const u64* C_qs, const u64* pub, size_t n_pub, size_t count,
+                             const u64* acc_prev, const u64* proof, int succinct_only) {
+    typedef typename Jac<CID>::S SF;
+    auto pi = plonk::proof_from_flat<CID>(proof, lg_n);
+    Jac<CID> cq[plonk::Q_POLYS];
+    for (int i = 0; i < plonk::Q_POLYS; ++i) cq[i] = Jac<CID>::from_raw(C_qs + 12 * i);
+    std::string why;
+    auto acc = instance_from_flat<CID>(acc_prev);
+    bool ok = succinct_only ? plonk::verify_succinct<CID>(pi, lg_n, cq, (const SF*)pub, n_pub, count, acc, &why)
+                            : plonk::verify<CID>(pi, lg_n, cq, (const SF*)pub, n_pub, count, acc, &why);
+    if (!ok) { g_err = why; return 1; }
+    return 0;
+}
 
 #define DISPATCH_CURVE(curve, CALL0, CALL1) do { if ((curve) == 0) { CALL0; } else { CALL1; } } while (0)
 
@@ -373,6 +397,25 @@ int orc_acc_verifier(int curve, const u64* insts, size_t m, unsigned lg_n, const
         return 0;
     } catch (std::exception& e) { g_err = e.what(); return -1; }
 }
+// ---- PLONK prover / verifier (plonk.hpp) ----
+size_t orc_plonk_proof_words(unsigned lg_n) { return plonk::proof_words(lg_n); }
+
+// polys: 57 x n x 4 words (qs, ws, rs, ids, sigmas coefficient vectors, zero-padded); w_evals: 3 x n x 4
+int orc_plonk_prove(int curve, unsigned lg_n, const u64* polys, const u64* w_evals, const u64* pub, size_t n_pub,
+                    const u64* acc_prev, u64* out_proof) {
+    try { return curve == 0 ? plonk_prove_impl<0>(lg_n, polys, w_evals, pub, n_pub, acc_prev, out_proof)
+                            : plonk_prove_impl<1>(lg_n, polys, w_evals, pub, n_pub, acc_prev, out_proof); }
+    catch (std::exception& e) { g_err = e.what(); return -1; }
+}
+
+// 0 accept, 1 reject, -1 precondition failure
+int orc_plonk_verify(int curve, unsigned lg_n, const u64* C_qs, const u64* pub, size_t n_pub, size_t public_input_count,
+                     const u64* acc_prev, const u64* proof, int succinct_only) {
+    try { return curve == 0 ? plonk_verify_impl<0>(lg_n, C_qs, pub, n_pub, public_input_count, acc_prev, proof, succinct_only)
+                            : plonk_verify_impl<1>(lg_n, C_qs, pub, n_pub, public_input_count, acc_prev, proof, succinct_only); }
+    catch (std::exception& e) { g_err = e.what(); return -1; }
+}
+
 int orc_acc_decider(int curve, const u64* acc) { return orc_pcdl_check(curve, acc); }
 
 // literal generator fold of one IPA round (pcdl.rs:427-429) on raw affine arrays; for kernel parity tests

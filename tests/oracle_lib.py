@@ -417,3 +417,32 @@ def inst_fields(inst):
     f["C_bar"] = inst[o:o + 12]; o += 12
     f["w_prime"] = inst[o:o + 4]
     return f
+
+
+# ---------------- PLONK prover / verifier (oracle/plonk.hpp) ----------------
+def plonk_proof_words(lg_n):
+    return int(_lib.orc_plonk_proof_words(ctypes.c_uint(lg_n)))
+
+
+def plonk_prove(curve, lg_n, polys, w_evals, public_inputs, acc_prev):
+    """polys: (57, n, 4) coefficient columns in the order qs, ws, rs, ids, sigmas; w_evals: (3, n, 4)."""
+    n = 1 << lg_n
+    polys = _c(polys).reshape(57, n, 4)
+    w_evals = _c(w_evals).reshape(3, n, 4)
+    pub = _c(public_inputs).reshape(-1, 4)
+    out = np.zeros(plonk_proof_words(lg_n), dtype=np.uint64)
+    rc = _lib.orc_plonk_prove(curve, ctypes.c_uint(lg_n), _p(polys), _p(w_evals), _p(pub) if pub.shape[0] else None,
+                              ctypes.c_size_t(pub.shape[0]), _p(_c(acc_prev)), _p(out))
+    if rc != 0:
+        raise OracleError(last_error())
+    return out
+
+
+def plonk_verify(curve, lg_n, C_qs, public_inputs, public_input_count, acc_prev, proof, succinct_only=False):
+    pub = _c(public_inputs).reshape(-1, 4)
+    rc = _lib.orc_plonk_verify(curve, ctypes.c_uint(lg_n), _p(_c(C_qs).reshape(10, 12)), _p(pub) if pub.shape[0] else None,
+                               ctypes.c_size_t(pub.shape[0]), ctypes.c_size_t(public_input_count), _p(_c(acc_prev)),
+                               _p(_c(proof)), int(succinct_only))
+    if rc < 0:
+        raise OracleError(last_error())
+    return rc == 0

@@ -26,3 +26,16 @@ for lg in lgs:
             e1.record(s); e1.synchronize()
             ts.append(e0.elapsed_time(e1))
         print(f"k=2^{lg} ms: " + " ".join(f"{x:.3f}" for x in ts) + f"  -> {k / (min(ts) * 1e-3):.3e} pts/s", flush=True)
+    if os.environ.get("HALO_STAGES"):
+        lib.halo_profile_enable(1)
+        for nb in (1, 2):
+            outb = np.empty(12 * nb, dtype=np.uint64)
+            for it in range(3):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(s)
+                check(lib.halo_msm_batch_dev(0, ctypes.c_void_p(d_pts.data_ptr()), ctypes.c_size_t(0), ctypes.c_void_p(d_sc.data_ptr()), ctypes.c_size_t(k // nb), ctypes.c_size_t(nb), outb.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64))))
+                e1.record(s); e1.synchronize()
+            ms = (ctypes.c_float * 16)(); names = (ctypes.c_char_p * 16)()
+            ns = lib.halo_profile_read(ms, names, 16)
+            print(f"   batch={nb} x 2^{lg}/{nb}: total {e0.elapsed_time(e1):.3f} ms  " + "  ".join(f"{names[i].decode()} {ms[i]:.3f}" for i in range(ns)), flush=True)
+        lib.halo_profile_enable(0)
