@@ -58,6 +58,9 @@ template <int C> int pcdl_open(const uint64_t*, size_t, const uint64_t*, size_t,
 template <int C> int pcdl_succinct_check(const uint64_t*, uint64_t*, uint64_t*);
 template <int C> int pcdl_check(const uint64_t*);
 template <int C> int acc_prover(const uint64_t*, size_t, uint64_t*);
+size_t plonk_proof_words(unsigned lg_n);
+template <int C> int plonk_prove(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*);
+template <int C> int plonk_verify(unsigned, const uint64_t*, const uint64_t*, size_t, size_t, const uint64_t*, const uint64_t*, int);
 template <int C> int acc_verifier(const uint64_t*, size_t, const uint64_t*);
 template <int S> int hpoly_coeffs(const uint64_t*, const uint64_t*, size_t, unsigned, uint64_t*);
 template <int C> int hpoly_commit_words(const uint64_t*, unsigned, uint64_t*);
@@ -538,6 +541,27 @@ int halo_bench_imad(int blocks, int threads, int iters, float* ms, uint64_t* out
     HALO_CUDA(cudaMemcpy(out, d, 8, cudaMemcpyDeviceToHost));
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     return HALO_OK;
+}
+
+// ---- PLONK prover / verifier (plonk.cu) ----
+size_t halo_plonk_proof_words(unsigned lg_n) { return plonk_proof_words(lg_n); }
+
+int halo_plonk_prove(int curve, unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, const uint64_t* public_inputs,
+                     size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
+    HALO_CHECK(polys && w_evals && acc_prev && out_proof && (public_inputs || n_public == 0), HALO_EINVAL, "null argument");
+    return curve == 0 ? plonk_prove<0>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof)
+                      : plonk_prove<1>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof);
+}
+
+int halo_plonk_verify(int curve, unsigned lg_n, const uint64_t* circuit_C_qs, const uint64_t* public_inputs, size_t n_public,
+                      size_t public_input_count, const uint64_t* acc_prev, const uint64_t* proof, int succinct_only) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
+    HALO_CHECK(circuit_C_qs && acc_prev && proof && (public_inputs || n_public == 0), HALO_EINVAL, "null argument");
+    return curve == 0 ? plonk_verify<0>(lg_n, circuit_C_qs, public_inputs, n_public, public_input_count, acc_prev, proof, succinct_only)
+                      : plonk_verify<1>(lg_n, circuit_C_qs, public_inputs, n_public, public_input_count, acc_prev, proof, succinct_only);
 }
 
 int halo_bench_pipe(int mode, int blocks, int threads, int iters, float* ms, uint64_t* out) {

@@ -13,6 +13,7 @@
 // the host, which receives two points per round and sends one challenge back.
 #include "runtime.cuh"
 #include "transcript.cuh"
+#include "host.cuh"
 #include <algorithm>
 #include <mutex>
 #include <string>
@@ -39,7 +40,6 @@ template <int F> __device__ __forceinline__ void g_st(Fe<F>* p, const Fe<F>& v) 
     q[1] = make_uint4(v.l[4], v.l[5], v.l[6], v.l[7]);
 }
 
-struct Bits256 { u32 w[8]; };
 
 // ---------------------------------------------------------------------------------------------------------
 // construct_powers (group.rs:58-66): out[j] = c0 * z^j, 16 consecutive powers per thread
@@ -342,27 +342,6 @@ __global__ void __launch_bounds__(128) ipa_hpoly_kernel(const Fe<F>* __restrict_
 template <int C> int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, uint64_t* out_xyz,
                                 ptrdiff_t base_stride);
 
-template <int C>
-struct Host {
-    static constexpr int S = CurveTraits<C>::SCALAR, B = CurveTraits<C>::BASE;
-    typedef Fe<S> SF;
-    typedef XYZZ<C> Pt;
-
-    static Pt from_words(const uint64_t* w) { Jac<C> j; memcpy(&j, w, 96); return jac_to_xyzz<C>(j); }
-    static void to_words(const Pt& p, uint64_t* w) { Jac<C> j = xyzz_to_jac<C>(p); memcpy(w, &j, 96); }
-    static Pt from_affine_words(const uint64_t* w) { Affine<C> a; memcpy(&a, w, 64); return xyzz_from_affine<C>(a); }
-    static SF scalar(const uint64_t* w) { SF s; memcpy(&s, w, 32); return s; }
-    static void put_scalar(const SF& s, uint64_t* w) { memcpy(w, &s, 32); }
-    static Bits256 bits(const SF& k) { SF c = fe_to_canonical<S>(k); Bits256 b; memcpy(b.w, c.l, 32); return b; }
-    static Pt mul(const Pt& p, const SF& k) { Bits256 b = bits(k); return xyzz_mul_bits<C>(p, b.w, 255); }
-    static Pt add(Pt a, const Pt& b) { xyzz_add<C>(a, b); return a; }
-    static Pt neg(Pt a) { a.Y = fe_neg<B>(a.Y); return a; }
-    static bool scalar_is_valid(const SF& s) {           // canonical limbs below the modulus
-        for (int i = 7; i >= 0; --i) { u32 p = modulus_limb<S>(i); if (s.l[i] != p) return s.l[i] < p; }
-        return false;
-    }
-};
-
 // fixed-base table for the many multiplications by H' inside one opening: T[i][d-1] = d * 16^i * P
 template <int C>
 struct FixedBase {
@@ -536,7 +515,7 @@ int pcdl_commit(const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w,
 template <int C>
 int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t d, const uint64_t* z_w,
               const uint64_t* v_w, const uint64_t* w_w, const uint64_t* hide_q, const uint64_t* hide_wbar,
-              uint64_t* out_proof, uint64_t* out_v, bool coeffs_resident = false) {
+              uint64_t* out_proof, uint64_t* out_v, bool coeffs_resident) {
     // coeffs_resident: the n zero-padded coefficients are already in the WS_IPA_C workspace (acc::prover's h(X))
     typedef Host<C> H;
     typedef typename H::SF SF;

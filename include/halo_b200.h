@@ -126,6 +126,29 @@ int halo_poly_mul(int field, const uint64_t* a, size_t la, const uint64_t* b, si
 int halo_scalar_dot(int field, const uint64_t* xs, const uint64_t* ys, size_t n, uint64_t out[4]);
 int halo_construct_powers(int field, const uint64_t z[4], size_t n, uint64_t* out);
 
+/* ---- PLONK prover / verifier -------------------------------------------------------------------------------
+ * ≙ PlonkProof::naive_prover (crates/plonk/src/plonk/protocol.rs:64-355) on what Trace::consume produces
+ * (crates/plonk/src/circuit/trace.rs:234-283): `polys` = the coefficient vectors witness.polys.{qs[10], ws[16],
+ * rs[15], ids[8], sigmas[8]} in that order, each zero-padded to n = 2^lg_n elements (57 x n x 4 words);
+ * `w_evals` = witness.w_evals[0..3] (3 x n x 4 words, row i at omega^(i+1) as Evals stores them);
+ * `public_inputs` = public_inputs.public_inputs; `acc_prev` = public_inputs.acc_prev as a flat instance.
+ * No hiding is used on this path (protocol.rs:295-306 pass None), so no randomness is consumed.
+ * Proof layout (halo_plonk_proof_words(lg_n) = 828 + 72 lg_n words):
+ *   vs  = ws[16] rs[15] qs[10] ts[16] ids[8] sigmas[8] z z_omega w_omegas[3]        (4 words each)
+ *   Cs  = ws[16] ts[16] z                                                           (12 words each, Jacobian)
+ *   pis = r, r_omega   (EvalProof: Ls[12L] Rs[12L] U[12] c[4] hiding[1] C_bar[12] w_prime[4])
+ *   acc_next           (flat instance)
+ * Errors: HALO_EINVAL where the reference panics (a zero denominator in the grand product), HALO_EPARAMS without
+ * public parameters of at least n generators. */
+size_t halo_plonk_proof_words(unsigned lg_n);
+int halo_plonk_prove(int curve, unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, const uint64_t* public_inputs,
+                     size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof);
+/* ≙ verify_succinct (protocol.rs:357-491) when succinct_only != 0, else verify (:493-502 = succinct + acc::decider).
+ * circuit_C_qs = circuit.Cs.qs (10 x 12 words); public_input_count = circuit.public_input_count.
+ * HALO_OK accept, HALO_EREJECT where the reference's ensure! fails. */
+int halo_plonk_verify(int curve, unsigned lg_n, const uint64_t* circuit_C_qs, const uint64_t* public_inputs, size_t n_public,
+                      size_t public_input_count, const uint64_t* acc_prev, const uint64_t* proof, int succinct_only);
+
 /* ---- benchmarks of the arithmetic itself (denominator of the integer roofline) -------------------------- */
 /* Runs `iters` dependent Montgomery multiplications in each of blocks*threads threads (4 independent chains per
  * thread); returns elapsed milliseconds measured with CUDA events in *ms and a checksum in out[4]. */
