@@ -240,6 +240,26 @@ def measure_path(lib, check, halo_b200, torch, stream, d_pts, h_sc, log_n):
         Cs = halo_b200.pcdl.commit(PALLAS, ps, (1 << 14) - 1)
         t = time.perf_counter(); halo_b200.pcdl.open_without_eval(PALLAS, ps, Cs, (1 << 14) - 1, z, None)
         out["pcdl_open_2^14_e2e"] = {"ms": (time.perf_counter() - t) * 1e3}
+    # BASELINE.json's second headline: PLONK proof time at 2^log_n gates (synthetic
+    # multiplication circuit, genesis accumulator), through the public API with host buffers, plus the same size
+    # with every custom gate's selector non-zero, and 2^12 for the like-for-like CPU ratio
+    for lg in sorted({12, min(log_n, 20)}):
+        rows = 1 << lg
+        acc0 = halo_b200.acc.Accumulator.zero(PALLAS, rows)
+        pub = halo_b200.plonk.PlonkPublicInputs(np.zeros((0, 4), dtype=np.uint64), acc0)
+        for dense in (False, True):
+            polys, w_evals = halo_b200.plonk.synthetic_circuit(PALLAS, lg, seed=7, dense_gates=dense)
+            circuit = halo_b200.plonk.PlonkCircuit.from_polys(PALLAS, polys, 0)
+            wit = halo_b200.plonk.PlonkWitness(polys, w_evals)
+            best = None
+            for _ in range(2):
+                t = time.perf_counter(); pi = halo_b200.plonk.PlonkProof.naive_prover(circuit, pub, wit); dt = time.perf_counter() - t
+                best = dt if best is None else min(best, dt)
+            key = f"plonk_prove_2^{lg}" + ("_all_gates" if dense else "")
+            out[key] = {"ms": best * 1e3, "h2d_bytes": int(polys.nbytes + w_evals.nbytes)}
+            if not dense:
+                t = time.perf_counter(); pi.verify(circuit, pub); out[f"plonk_verify_2^{lg}"] = {"ms": (time.perf_counter() - t) * 1e3}
+            del polys, w_evals, wit
     halo_b200.pp.reset(PALLAS)
     return out
 
@@ -258,6 +278,15 @@ def cpu_path_leg():
     O.pp_set(PALLAS, gs[:n], gs[n], gs[n + 1])
     p = O.random_scalars(0, n, 4)
     t = time.perf_counter(); O.instance_open(PALLAS, p, n - 1, p[3]); out["pcdl_instance_open_2^14_ms"] = (time.perf_counter() - t) * 1e3
+    # the PLONK prover restatement on a 2^12-row multiplication circuit (bounded sample of config 4)
+    import plonk_fixture as F
+    lg = 12
+    rows = 1 << lg
+    c = F.make_circuit(O, PALLAS, lg, "mul", seed=7)
+    zero = O.instance_open(PALLAS, np.zeros((0, 4), dtype=np.uint64), rows - 1, np.zeros(4, dtype=np.uint64))
+    acc0 = O.acc_prover(PALLAS, zero.reshape(1, -1), lg)
+    t = time.perf_counter(); O.plonk_prove(PALLAS, lg, c["polys"], c["w_evals"], c["public_inputs"], acc0)
+    out["plonk_prove_2^12_ms"] = (time.perf_counter() - t) * 1e3
     return out
 
 

@@ -104,3 +104,41 @@ class PlonkProof:
 
     def verify(self, circuit, public_inputs):
         self._verify(circuit, public_inputs, False)
+
+
+def synthetic_circuit(curve, lg_n, seed=1, dense_gates=False):
+    """The synthetic workload of SURVEY §8(d) config 4, built with GPU arithmetic: rows w0 = a, w1 = b, w2 = a*b with
+    q_m = 1, q_o = -1, identity permutation, no public inputs.  dense_gates=True additionally fills the five custom
+    selectors, the round-constant columns and the remaining witnesses with random values (every gate expression
+    is then evaluated; the circuit is no longer satisfied).  Returns (polys (57, n, 4), w_evals (3, n, 4))."""
+    from . import consts, group, poly
+    field = curve
+    n = 1 << lg_n
+    rng = np.random.default_rng(seed)
+
+    def rand_elems(k):
+        t = rng.integers(0, 1 << 64, size=(k, 4), dtype=np.uint64)
+        t[:, 3] &= np.uint64((1 << 62) - 1)            # < 2^254 < p: a valid Montgomery residue
+        return t
+
+    one = consts.one(field)
+    neg_one = group.field_op(field, "sub", np.zeros((1, 4), dtype=np.uint64), one.reshape(1, 4))[0]
+    cols = np.zeros((N_COLUMNS, n, 4), dtype=np.uint64)
+    a, b = rand_elems(n), rand_elems(n)
+    cols[10], cols[11] = a, b
+    cols[12] = group.field_op(field, "mul", a, b)
+    cols[3] = one                                       # q_m
+    cols[2] = neg_one                                   # q_o
+    if dense_gates:
+        for i in list(range(5, 10)) + list(range(13, 26)) + list(range(26, 41)):
+            cols[i] = rand_elems(n)
+    idx = np.zeros((S_POLYS * n, 4), dtype=np.uint64)
+    idx[:, 0] = np.arange(1, S_POLYS * n + 1, dtype=np.uint64)    # SlotId::to_scalar: row + (column-1)*n, 1-based
+    ids = group.field_op(field, "from_canonical", idx)
+    cols[41:49] = ids.reshape(S_POLYS, n, 4)
+    cols[49:57] = cols[41:49]
+    evals = np.roll(cols, 1, axis=1)                    # Evals::from_vec_and_domain (poly.rs:21-24)
+    polys = np.empty_like(cols)
+    for lo in range(0, N_COLUMNS, 19):
+        polys[lo:lo + 19] = poly.ntt(field, evals[lo:lo + 19], inverse=True)
+    return polys, evals[10:13].copy()
