@@ -2,6 +2,8 @@
 // arithmetic micro-benchmarks.  Each entry point cites the reference interface it stands in for in the header.
 #include "runtime.cuh"
 #include <cstring>
+#include <algorithm>
+#include <thread>
 
 namespace halo {
 
@@ -29,6 +31,55 @@ int pinned_get(size_t bytes, void** out) {
         R.pinned_cap = cap;
     }
     *out = R.pinned;
+    return HALO_OK;
+}
+
+int upload_staged(void* d_dst, const void* h_src, size_t bytes) {
+    Runtime& R = rt();
+    if (bytes < 4 * Runtime::UP_CHUNK) {
+        HALO_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, R.stream));
+        return HALO_OK;
+    }
+    constexpr int T = Runtime::UP_THREADS, SL = Runtime::UP_SLOTS;
+    constexpr size_t CH = Runtime::UP_CHUNK;
+    if (!R.up_stream[0]) {
+        for (int t = 0; t < T; ++t) {
+            HALO_CUDA(cudaStreamCreateWithFlags(&R.up_stream[t], cudaStreamNonBlocking));
+            for (int k = 0; k < SL; ++k) {
+                HALO_CUDA(cudaMallocHost(&R.up_buf[t][k], CH));
+                HALO_CUDA(cudaEventCreateWithFlags(&R.up_ev[t][k], cudaEventDisableTiming));
+            }
+        }
+    }
+    // the destination may still be read by queued work: start after the library stream's current tail
+    cudaEvent_t go;
+    HALO_CUDA(cudaEventCreateWithFlags(&go, cudaEventDisableTiming));
+    HALO_CUDA(cudaEventRecord(go, R.stream));
+    int dev = 0;
+    HALO_CUDA(cudaGetDevice(&dev));
+    const size_t nchunks = (bytes + CH - 1) / CH;
+    int status[T];
+    std::thread th[T];
+    for (int t = 0; t < T; ++t) {
+        status[t] = 0;
+        th[t] = std::thread([&, t]() {
+            if (cudaSetDevice(dev) != cudaSuccess || cudaStreamWaitEvent(R.up_stream[t], go, 0) != cudaSuccess) { status[t] = 1; return; }
+            int slot = 0;
+            for (size_t c = t; c < nchunks; c += T, slot ^= 1) {
+                const size_t off = c * CH, len = std::min(CH, bytes - off);
+                if (cudaEventSynchronize(R.up_ev[t][slot]) != cudaSuccess) { status[t] = 1; return; }   // slot free again
+                memcpy(R.up_buf[t][slot], (const char*)h_src + off, len);
+                if (cudaMemcpyAsync((char*)d_dst + off, R.up_buf[t][slot], len, cudaMemcpyHostToDevice, R.up_stream[t]) != cudaSuccess ||
+                    cudaEventRecord(R.up_ev[t][slot], R.up_stream[t]) != cudaSuccess) { status[t] = 1; return; }
+            }
+        });
+    }
+    for (int t = 0; t < T; ++t) th[t].join();
+    cudaEventDestroy(go);
+    for (int t = 0; t < T; ++t) {
+        HALO_CHECK(status[t] == 0, HALO_ECUDA, "staged upload failed");
+        for (int k = 0; k < SL; ++k) HALO_CUDA(cudaStreamWaitEvent(R.stream, R.up_ev[t][k], 0));
+    }
     return HALO_OK;
 }
 
@@ -292,6 +343,15 @@ int halo_shutdown(void) {
     for (int c = 0; c < 2; ++c) { if (R.pp[c].d_gs) cudaFree(R.pp[c].d_gs); R.pp[c] = ResidentParams(); }
     if (R.pinned) cudaFreeHost(R.pinned);
     R.pinned = nullptr; R.pinned_cap = 0;
+    for (int t = 0; t < Runtime::UP_THREADS; ++t) {
+        for (int k = 0; k < Runtime::UP_SLOTS; ++k) {
+            if (R.up_buf[t][k]) cudaFreeHost(R.up_buf[t][k]);
+            if (R.up_ev[t][k]) cudaEventDestroy(R.up_ev[t][k]);
+            R.up_buf[t][k] = nullptr; R.up_ev[t][k] = nullptr;
+        }
+        if (R.up_stream[t]) cudaStreamDestroy(R.up_stream[t]);
+        R.up_stream[t] = nullptr;
+    }
     for (int f = 0; f < 2; ++f) { if (R.ntt_tw[f]) cudaFree(R.ntt_tw[f]); R.ntt_tw[f] = nullptr; R.ntt_logmax[f] = 0; }
     cudaStreamDestroy(R.own_stream);
     if (R.copy_stream) cudaStreamDestroy(R.copy_stream);

@@ -170,11 +170,11 @@ template <int F> struct ColView {
     HD Fe<F> pi() const { return col(COL_PI); }
 };
 
-// f on one coset: out[c + 16 j] = f(w16n^c * w_n^j)
+// f on one coset: out[coset + stride * j] = f(g * w_n^j) [* scale]
 template <int F>
 __global__ void __launch_bounds__(128) plonk_numerator_kernel(const Fe<F>* __restrict__ ev, size_t n, Challenges<F> ch,
                                                               unsigned gate_mask, Fe<F>* __restrict__ out,
-                                                              unsigned coset, unsigned stride) {
+                                                              unsigned coset, unsigned stride, Fe<F> scale, int scaled) {
     size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (j >= n) return;
     ColView<F> v{ev, n, j, j + 1 == n ? 0 : j + 1};
@@ -190,6 +190,7 @@ __global__ void __launch_bounds__(128) plonk_numerator_kernel(const Fe<F>* __res
     Fe<F> cc1 = fe_mul<F>(v.col(COL_L1), fe_sub<F>(z, fe_one<F>()));
     Fe<F> cc2 = fe_sub<F>(fe_mul<F>(z, fp), fe_mul<F>(v.col(COL_ZW), gp));
     f = fe_add<F>(f, fe_add<F>(fe_mul<F>(ch.alpha, cc1), fe_mul<F>(ch.alpha2, cc2)));
+    if (scaled) f = fe_mul<F>(f, scale);                  // 1 / Z_H on this coset (quotient path)
     p_st<F>(out + coset + (size_t)stride * j, f);
 }
 
@@ -429,7 +430,7 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     const SF omega = root_of_unity<S>((int)lg_n);
 
     // ---- round 0 (protocol.rs:74-109): resident coefficient columns
-    HALO_CUDA(cudaMemcpyAsync(cols, polys, (size_t)N_IN * n * 32, cudaMemcpyHostToDevice, st));
+    if (int e = upload_staged(cols, polys, (size_t)N_IN * n * 32)) return e;
     // staged evaluation vectors: PI (row i at omega^(i+1), negated), l1, and the three shifted witness columns
     SF* stage = tmp;                                       // [PI | l1 | wom0 wom1 wom2]
     HALO_CUDA(cudaMemsetAsync(stage, 0, 2 * n * 32, st));
@@ -502,21 +503,50 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     unsigned gate_mask = 0;
     for (int i = 0; i < 5; ++i) if (h_flags[5 + i]) gate_mask |= 1u << i;
     const SF w16n = root_of_unity<S>((int)lg_n + 4);
-    SF g = one;
-    for (unsigned c = 0; c < 16; ++c) {
+    auto numerator_on_coset = [&](unsigned c, SF* dst, unsigned slot, unsigned stride, const SF* scale) -> int {
+        SF g = one;                                        // w16n^c
+        for (unsigned i = 0; i < c; ++i) g = fe_mul<S>(g, w16n);
         HALO_CUDA(cudaMemcpyAsync(tmp, cols, (size_t)N_EVAL * n * 32, cudaMemcpyDeviceToDevice, st));
         if (int e = ntt_device<S>(tmp, ev, (int)lg_n, N_EVAL, false, c ? &g : nullptr)) return e;
-        plonk_numerator_kernel<S><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(ev, n, ch, gate_mask, f0, c, 16);
+        plonk_numerator_kernel<S><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(ev, n, ch, gate_mask, dst, slot, stride,
+                                                                              scale ? *scale : one, scale ? 1 : 0);
         R.launches += 1;
-        g = fe_mul<S>(g, w16n);
-    }
-    HALO_CUDA(cudaGetLastError());
-    lap("round 4 (numerator, 16 cosets)");
-    if (int e = ntt_device<S>(f0, f1, (int)lg_n + 4, 1, true, nullptr)) return e;
-    SF* tq = f0;                                           // 16 chunks of n coefficients (t_split, :509-517)
-    plonk_quotient_kernel<S><<<(unsigned)((16 * n + 255) / 256), 256, 0, st>>>(f1, 16 * n, n, tq);
+        HALO_CUDA(cudaGetLastError());
+        return HALO_OK;
+    };
+    // f vanishes on H exactly when X^n - 1 divides it (always, for a satisfying witness).  Then t = f / Z_H has
+    // degree < 8n and is interpolated from the 8 odd cosets, which form the coset w16n * (8n domain) and on which
+    // Z_H is the constant w16^c - 1.  Otherwise the reference still returns the polynomial quotient (protocol.rs:256
+    // drops the remainder), which takes f on all 16 cosets and the coefficient-form division.
+    if (int e = numerator_on_coset(0, f1, 0, 1, nullptr)) return e;
+    HALO_CUDA(cudaMemsetAsync(d_flags, 0, sizeof(int), st));
+    plonk_nonzero_kernel<S><<<dim3(64, 1), 256, 0, st>>>(f1, n, d_flags);
     R.launches += 1;
-    HALO_CUDA(cudaGetLastError());
+    int not_divisible = 0;
+    HALO_CUDA(cudaMemcpyAsync(&not_divisible, d_flags, sizeof(int), cudaMemcpyDeviceToHost, st));
+    HALO_CUDA(cudaStreamSynchronize(st));
+    SF* tq = f0;                                           // 16 chunks of n coefficients (t_split, :509-517)
+    if (!not_divisible && R.tune[5] != 1) {
+        const SF w16 = root_of_unity<S>(4);
+        SF zh = w16;                                       // w16^c for c = 1, 3, ...
+        const SF w16sq = fe_sqr<S>(w16);
+        for (unsigned k = 0; k < 8; ++k) {
+            SF inv = fe_inv<S>(fe_sub<S>(zh, one));
+            if (int e = numerator_on_coset(2 * k + 1, f1, k, 8, &inv)) return e;
+            zh = fe_mul<S>(zh, w16sq);
+        }
+        lap("round 4 (quotient on 8 cosets)");
+        if (int e = ntt_device<S>(f1, tq, (int)lg_n + 3, 1, true, &w16n)) return e;
+        HALO_CUDA(cudaMemsetAsync(tq + 8 * n, 0, 8 * n * 32, st));
+    } else {
+        for (unsigned c = 0; c < 16; ++c)
+            if (int e = numerator_on_coset(c, f0, c, 16, nullptr)) return e;
+        lap("round 4 (numerator, 16 cosets)");
+        if (int e = ntt_device<S>(f0, f1, (int)lg_n + 4, 1, true, nullptr)) return e;
+        plonk_quotient_kernel<S><<<(unsigned)((16 * n + 255) / 256), 256, 0, st>>>(f1, 16 * n, n, tq);
+        R.launches += 1;
+        HALO_CUDA(cudaGetLastError());
+    }
     if (int e = msm_device<C>(R.pp[C].d_gs, tq, n, NT, o_Cts, 0)) return e;
     for (int i = 0; i < NT; ++i) tr.absorb_point(H::from_words(o_Cts + 12 * i));
     lap("round 4 (quotient, 16 commits)");

@@ -36,6 +36,12 @@ struct Runtime {
     std::vector<DeviceBuf> arena;   // indexed slots
     void* pinned = nullptr;         // pinned host staging
     size_t pinned_cap = 0;
+    // staged upload of large pageable buffers: UP_THREADS workers, two pinned chunks and one stream each
+    static constexpr int UP_THREADS = 8, UP_SLOTS = 2;
+    static constexpr size_t UP_CHUNK = (size_t)8 << 20;
+    void* up_buf[UP_THREADS][UP_SLOTS] = {};
+    cudaEvent_t up_ev[UP_THREADS][UP_SLOTS] = {};
+    cudaStream_t up_stream[UP_THREADS] = {};
     int msm_window_override = 0;
     int tune[8] = {};               // experiment knobs (halo_set_tuning)
     // per-stage CUDA-event timing of the last MSM (halo_profile_*), and a count of kernels launched
@@ -81,6 +87,10 @@ int prof_mark(const char* name);
 // workspace slot: returns a device pointer with at least `bytes` capacity (contents undefined)
 int ws_get(int slot, size_t bytes, void** out);
 int pinned_get(size_t bytes, void** out);
+// host -> device copy of a (pageable) caller buffer, ordered after everything already queued on the library stream
+// and complete on that stream when it returns: worker threads stage chunks through pinned memory so the CPU copy
+// and the DMA overlap and several cores feed the link
+int upload_staged(void* d_dst, const void* h_src, size_t bytes);
 
 enum WsSlot {
     WS_SCALARS = 0, WS_BASES, WS_COUNTS, WS_OFFSETS, WS_CURSOR, WS_IDX, WS_ORDER, WS_SIZEHIST, WS_BUCKETS,

@@ -84,6 +84,14 @@ def test_proof_matches_oracle_and_verifies(hb, oracle, params, curve, lg_n, kind
     assert ok_oracle
     pi.verify_succinct(circuit, pub)
     pi.verify(circuit, pub)
+    # a satisfying witness takes the 8-coset quotient; the 16-coset coefficient division gives the same proof
+    from halo_b200._lib import lib
+    lib.halo_set_tuning(5, 1)
+    try:
+        slow = hb.plonk.PlonkProof.naive_prover(circuit, pub, wit)
+    finally:
+        lib.halo_set_tuning(5, 0)
+    same_proof(O, curve, lg_n, slow.w, exp)
     # the next accumulator is a valid one (protocol.rs:493-502) and chains into a second proof (IVC-style)
     hb.acc.decider(curve, pi.acc_next)
     pub2 = hb.plonk.PlonkPublicInputs(c["public_inputs"], pi.acc_next)
