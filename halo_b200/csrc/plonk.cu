@@ -342,6 +342,19 @@ __global__ void __launch_bounds__(256) plonk_eval_kernel(EvalSet<F> es, size_t n
     if (t == 0) p_st<F>(partial + (size_t)blockIdx.y * gridDim.x + blockIdx.x, acc);
 }
 
+// dst[c][k] = src[c][k] * g^k for every column c: the coset shift of a batched size-n NTT, fused with the copy into
+// the transform's scratch buffer.  g^k = hi[k >> 10] * lo[k & 1023]; one thread per k, coalesced across columns.
+template <int F>
+__global__ void __launch_bounds__(256) plonk_coset_stage_kernel(const Fe<F>* __restrict__ src, Fe<F>* __restrict__ dst, size_t n,
+                                                                int ncols, const Fe<F>* __restrict__ lo,
+                                                                const Fe<F>* __restrict__ hi) {
+    size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    Fe<F> w = p_ld<F>(lo + (k & 1023));
+    if (k >> 10) w = fe_mul<F>(w, p_ld<F>(hi + (k >> 10)));
+    for (int c = 0; c < ncols; ++c) p_st<F>(dst + (size_t)c * n + k, fe_mul<F>(p_ld<F>(src + (size_t)c * n + k), w));
+}
+
 // any nonzero coefficient in column c?  flags[c] |= 1
 template <int F>
 __global__ void __launch_bounds__(256) plonk_nonzero_kernel(const Fe<F>* __restrict__ cols, size_t n, int* __restrict__ flags) {
@@ -422,9 +435,11 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     if (int e = ws_get(WS_PLONK_EV, (size_t)N_EVAL * n * 32, (void**)&ev)) return e;
     if (int e = ws_get(WS_PLONK_F0, 16 * n * 32, (void**)&f0)) return e;
     if (int e = ws_get(WS_PLONK_F1, 16 * n * 32, (void**)&f1)) return e;
-    const size_t misc_elems = 2 * (size_t)SCAN_SEG + 64 + (size_t)EV_MAX * EV_BLOCKS;
+    const size_t gtab_elems = 1024 + n / 1024 + 16;
+    const size_t misc_elems = 2 * (size_t)SCAN_SEG + 64 + (size_t)EV_MAX * EV_BLOCKS + gtab_elems;
     if (int e = ws_get(WS_PLONK_MISC, misc_elems * 32 + 256, (void**)&misc)) return e;
     int* d_flags = (int*)(misc + misc_elems);
+    SF* gtab = misc + 2 * (size_t)SCAN_SEG + 64 + (size_t)EV_MAX * EV_BLOCKS;      // g^i, i < 1024 | (g^1024)^i
     auto col = [&](int c) { return cols + (size_t)c * n; };
     const SF one = fe_one<S>();
     const SF omega = root_of_unity<S>((int)lg_n);
@@ -506,8 +521,17 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     auto numerator_on_coset = [&](unsigned c, SF* dst, unsigned slot, unsigned stride, const SF* scale) -> int {
         SF g = one;                                        // w16n^c
         for (unsigned i = 0; i < c; ++i) g = fe_mul<S>(g, w16n);
-        HALO_CUDA(cudaMemcpyAsync(tmp, cols, (size_t)N_EVAL * n * 32, cudaMemcpyDeviceToDevice, st));
-        if (int e = ntt_device<S>(tmp, ev, (int)lg_n, N_EVAL, false, c ? &g : nullptr)) return e;
+        if (c == 0) {
+            HALO_CUDA(cudaMemcpyAsync(tmp, cols, (size_t)N_EVAL * n * 32, cudaMemcpyDeviceToDevice, st));
+        } else {
+            SF g1024 = g;
+            for (int i = 0; i < 10; ++i) g1024 = fe_sqr<S>(g1024);
+            plonk_powers_kernel<S><<<1, 128, 0, st>>>(gtab, 1024, g);
+            plonk_powers_kernel<S><<<(unsigned)((n / 1024 / 16 + 128) / 128), 128, 0, st>>>(gtab + 1024, (n + 1023) / 1024, g1024);
+            plonk_coset_stage_kernel<S><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(cols, tmp, n, N_EVAL, gtab, gtab + 1024);
+            R.launches += 3;
+        }
+        if (int e = ntt_device<S>(tmp, ev, (int)lg_n, N_EVAL, false, nullptr)) return e;
         plonk_numerator_kernel<S><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(ev, n, ch, gate_mask, dst, slot, stride,
                                                                               scale ? *scale : one, scale ? 1 : 0);
         R.launches += 1;
