@@ -142,3 +142,64 @@ def synthetic_circuit(curve, lg_n, seed=1, dense_gates=False):
     for lo in range(0, N_COLUMNS, 19):
         polys[lo:lo + 19] = poly.ntt(field, evals[lo:lo + 19], inverse=True)
     return polys, evals[10:13].copy()
+
+
+class Trace:
+    """≙ Trace::new / Trace::consume (crates/plonk/src/circuit/trace.rs:137-283): column vectors -> Evals (row i at
+    omega^(i+1)) -> coefficient polynomials by ONE batched iNTT of the 57 columns, and the circuit commitments
+    (10 + 15 + 8 + 8) by batched MSMs over the resident generators instead of 41 sequential commits.
+
+    copy_constraints: list of equivalence classes of 1-based (row, column) slots, as build_sigma takes them
+    (trace.rs:64-104); ws / rs / qs: (16|15|10, n, 4) Montgomery column vectors; public_inputs: (k, 4)."""
+
+    def __init__(self, curve, copy_constraints, public_inputs, ws, rs, qs, n, acc_prev, circuit=None):
+        from . import group, poly, pedersen
+        _lib.ensure_init()
+        field = curve
+        lg_n = n.bit_length() - 1
+        if n != 1 << lg_n:
+            raise _lib.PreconditionError(_lib.HALO_EINVAL, "rows must be a power of two (build_sigma asserts it)")
+        ws, rs, qs = (np.ascontiguousarray(x, dtype=np.uint64) for x in (ws, rs, qs))
+        assert ws.shape == (W_POLYS, n, 4) and rs.shape == (R_POLYS, n, 4) and qs.shape == (Q_POLYS, n, 4)
+        # build_sigma: identity permutation over the 8 n slots, then one cycle per equivalence class
+        sigma = np.arange(S_POLYS * n, dtype=np.uint64)
+        slot = lambda rc: (rc[0] - 1) + (rc[1] - 1) * n                       # SlotId::to_usize
+        for wires in copy_constraints:
+            if len(wires) <= 1:
+                continue
+            for i, frm in enumerate(wires):
+                sigma[slot(frm)] = slot(wires[(i + 1) % len(wires)])
+        self.sigma = sigma
+        canon = np.zeros((2 * S_POLYS * n, 4), dtype=np.uint64)
+        canon[:S_POLYS * n, 0] = np.arange(1, S_POLYS * n + 1, dtype=np.uint64)   # SlotId::to_scalar, 1-based
+        canon[S_POLYS * n:, 0] = sigma + np.uint64(1)
+        idsig = group.field_op(field, "from_canonical", canon).reshape(2 * S_POLYS, n, 4)
+        cols = np.concatenate([qs, ws, rs, idsig])                            # flat order of the C ABI
+        evals = np.roll(cols, 1, axis=1)                                      # Evals::from_vec_and_domain
+        polys = np.empty_like(cols)
+        for lo in range(0, N_COLUMNS, 19):
+            polys[lo:lo + 19] = poly.ntt(field, evals[lo:lo + 19], inverse=True)
+        self.curve, self.rows = curve, n
+        self.polys, self.w_evals = polys, evals[Q_POLYS:Q_POLYS + W_POLYS].copy()
+        self.public_inputs = as_u64(public_inputs, 4)
+        self.acc_prev = acc_prev
+        if circuit is not None:
+            self.C_qs, self.C_rs, self.C_ids, self.C_sigmas = circuit.C_qs, circuit.C_rs, circuit.C_ids, circuit.C_sigmas
+        else:
+            if pp_len(curve) < n:
+                raise _lib.ParamsError(_lib.HALO_EPARAMS, "public parameters not loaded for this many rows")
+            C = group.msm_batch_resident(curve, np.concatenate([polys[:Q_POLYS], polys[26:41], polys[41:57]]))
+            self.C_qs, self.C_rs, self.C_ids, self.C_sigmas = C[:10], C[10:25], C[25:33], C[33:41]
+        # C_public_inputs = pedersen::commit(None, &pp.Gs, &public_inputs) (trace.rs:195-196)
+        k = self.public_inputs.shape[0]
+        self.C_public_inputs = pedersen.commit(curve, None, (0, pp_len(curve)), self.public_inputs) if k else None
+
+    def consume(self):
+        circuit = PlonkCircuit(self.curve, self.rows, self.public_inputs.shape[0], self.C_qs)
+        circuit.C_rs, circuit.C_ids, circuit.C_sigmas = self.C_rs, self.C_ids, self.C_sigmas
+        return circuit, PlonkPublicInputs(self.public_inputs, self.acc_prev), PlonkWitness(self.polys, self.w_evals)
+
+
+def pp_len(curve):
+    lib.halo_pp_len.restype = ctypes.c_size_t
+    return int(lib.halo_pp_len(curve))

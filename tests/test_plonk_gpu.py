@@ -149,3 +149,31 @@ def test_zero_columns_and_bad_row_count(hb, oracle, params):
     same_proof(O, curve, lg_n, pi.w, exp)
     with pytest.raises(hb.PreconditionError):
         hb.plonk.PlonkProof.naive_prover(hb.plonk.PlonkCircuit(curve, 3, 0, circuit.C_qs), pub, hb.plonk.PlonkWitness(polys, w_evals))
+
+
+@pytest.mark.parametrize("curve", [0, 1])
+def test_trace_new_matches_the_fixture_and_proves(hb, oracle, params, curve):
+    """Trace::new / consume (trace.rs:137-283) from raw columns and copy-constraint classes: the polynomials equal the
+    ones the fixture interpolates with the oracle, the 41 circuit commitments equal the oracle's commits, and the
+    consumed triple proves and verifies."""
+    O = oracle
+    lg_n = 6
+    n = 1 << lg_n
+    c = F.make_circuit(O, curve, lg_n, "copy", seed=21)
+    field = c["field"]
+    # recover the column vectors from the fixture's polynomials (evaluate, undo the Evals rotation)
+    cols = np.roll(O.ntt(field, c["polys"].copy()).reshape(57, n, 4), -1, axis=1)
+    classes = [[(j + 2, 1), (j + 1, 3)] for j in range(0, n - 1, 2)]          # row j+1's a tied to row j's c (1-based)
+    acc0 = genesis(hb, curve, n)
+    tr = hb.plonk.Trace(curve, classes, c["public_inputs"], cols[10:26], cols[26:41], cols[0:10], n, acc0)
+    assert (tr.polys == c["polys"]).all()
+    assert (tr.w_evals[:3] == c["w_evals"]).all()
+    exp_C = np.stack([O.pcdl_commit(curve, c["polys"][i], n - 1) for i in list(range(10)) + list(range(26, 57))])
+    got_C = np.concatenate([tr.C_qs, tr.C_rs, tr.C_ids, tr.C_sigmas])
+    assert (O.point_to_affine(curve, got_C) == O.point_to_affine(curve, exp_C)).all()
+    circuit, pub, wit = tr.consume()
+    pi = hb.plonk.PlonkProof.naive_prover(circuit, pub, wit)
+    pi.verify(circuit, pub)
+    assert O.plonk_verify(curve, lg_n, circuit.C_qs, c["public_inputs"], 0, acc0.q.w, pi.w)
+    with pytest.raises(hb.PreconditionError):
+        hb.plonk.Trace(curve, [], c["public_inputs"], cols[10:26, :48], cols[26:41, :48], cols[0:10, :48], 48, acc0)
