@@ -324,25 +324,78 @@ template <int FID> HD Fe<FID> fe_sub(const Fe<FID>& a, const Fe<FID>& b) {
 }
 template <int FID> HD Fe<FID> fe_neg(const Fe<FID>& a) { return fe_sub<FID>(fe_zero<FID>(), a); }
 template <int FID> HD Fe<FID> fe_dbl(const Fe<FID>& a) { return fe_add<FID>(a, a); }
+namespace hostimpl {
+// one Montgomery reduction step on 64-bit words: t = (t + m*p) >> 64 with m = -t[0]/p mod 2^64, for the moduli's
+// shape p = [p0, p1, 0, 2^62]: two multiplications and a shift instead of four multiplications
+template <int FID> HD void redc_step(u64* t /* 5 words + overflow in t[5] */) {
+    const u64 p0 = ((u64)FieldConst<FID>::P1 << 32) | 1u, p1 = ((u64)FieldConst<FID>::P3 << 32) | FieldConst<FID>::P2;
+    const u64 inv = (((u64)FieldConst<FID>::P1 - 1) << 32) | 0xffffffffULL;   // -p^{-1} mod 2^64
+    const u64 m = t[0] * inv;
+    u128 c = ((u128)m * p0 + t[0]) >> 64;
+    c += (u128)m * p1 + t[1]; t[0] = (u64)c; c >>= 64;
+    c += t[2]; t[1] = (u64)c; c >>= 64;
+    c += ((u128)m << 62) + t[3]; t[2] = (u64)c; c >>= 64;
+    c += t[4]; t[3] = (u64)c; t[4] = t[5] + (u64)(c >> 64);
+}
+// w[0..8) += x * y (schoolbook); returns the carry out of word 7
+HD u64 mac_wide(u64 w[8], const u64 x[4], const u64 y[4]) {
+    u64 carry_out = 0;
+    for (int i = 0; i < 4; ++i) {
+        u128 c = 0;
+        for (int j = 0; j < 4; ++j) { c += (u128)x[j] * y[i] + w[i + j]; w[i + j] = (u64)c; c >>= 64; }
+        for (int k = i + 4; k < 8 && c; ++k) { c += w[k]; w[k] = (u64)c; c >>= 64; }
+        carry_out += (u64)c;
+    }
+    return carry_out;
+}
+// Montgomery reduction of a 512-bit value T < 3 p^2 (so that the result is below 2p before the final subtraction)
+template <int FID> HD void redc_wide(u64 out[4], const u64 w[8]) {
+    u64 p[4]; modulus64<FID>(p);
+    u64 t[6] = {w[0], w[1], w[2], w[3], 0, 0};
+    for (int i = 0; i < 4; ++i) {
+        // bring in the next high word, then divide by 2^64
+        u128 c = (u128)t[4] + w[4 + i];
+        t[4] = (u64)c; t[5] = (u64)(c >> 64);
+        redc_step<FID>(t);
+    }
+    if (t[4] || geq(t, p)) sub(t, t, p);
+    for (int i = 0; i < 4; ++i) out[i] = t[i];
+}
+}  // namespace hostimpl
+
 template <int FID> HD Fe<FID> fe_mul(const Fe<FID>& a, const Fe<FID>& b) {
     using namespace hostimpl;
     u64 x[4], y[4], p[4]; load(x, a.l); load(y, b.l); modulus64<FID>(p);
-    const u64 inv = (((u64)FieldConst<FID>::P1 - 1) << 32) | 0xffffffffULL;   // -p^{-1} mod 2^64
     u64 t[6] = {0, 0, 0, 0, 0, 0};
     for (int i = 0; i < 4; ++i) {
         u128 c = 0;
         for (int j = 0; j < 4; ++j) { c += (u128)x[j] * y[i] + t[j]; t[j] = (u64)c; c >>= 64; }
         c += t[4]; t[4] = (u64)c; t[5] = (u64)(c >> 64);
-        u64 m = t[0] * inv;
-        c = ((u128)m * p[0] + t[0]) >> 64;
-        for (int j = 1; j < 4; ++j) { c += (u128)m * p[j] + t[j]; t[j - 1] = (u64)c; c >>= 64; }
-        c += t[4]; t[3] = (u64)c; t[4] = t[5] + (u64)(c >> 64);
+        redc_step<FID>(t);
     }
     if (t[4] || geq(t, p)) sub(t, t, p);
     Fe<FID> o; store(o.l, t); return o;
 }
+// a0*b0 + a1*b1 + a2*b2 with one reduction (the MDS rows of the host sponge)
+template <int FID> HD Fe<FID> fe_dot3(const Fe<FID>& a0, const Fe<FID>& b0, const Fe<FID>& a1, const Fe<FID>& b1,
+                                      const Fe<FID>& a2, const Fe<FID>& b2) {
+    using namespace hostimpl;
+    u64 x[4], y[4], w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    load(x, a0.l); load(y, b0.l); mac_wide(w, x, y);
+    load(x, a1.l); load(y, b1.l); mac_wide(w, x, y);
+    load(x, a2.l); load(y, b2.l); mac_wide(w, x, y);          // 3 p^2 < 2^512: no carry out
+    u64 r[4]; redc_wide<FID>(r, w);
+    Fe<FID> o; store(o.l, r); return o;
+}
 template <int FID> HD Fe<FID> fe_sqr(const Fe<FID>& a) { return fe_mul<FID>(a, a); }
 #endif  // !HALO_PTX_PATH
+
+#if defined(HALO_PTX_PATH)
+template <int FID> DEV Fe<FID> fe_dot3(const Fe<FID>& a0, const Fe<FID>& b0, const Fe<FID>& a1, const Fe<FID>& b1,
+                                       const Fe<FID>& a2, const Fe<FID>& b2) {
+    return fe_add<FID>(fe_add<FID>(fe_mul<FID>(a0, b0), fe_mul<FID>(a1, b1)), fe_mul<FID>(a2, b2));
+}
+#endif
 
 // ---------------------------------------------------------------------------------------------------------
 // constants and derived operations (all paths)

@@ -15,6 +15,7 @@
 #include "transcript.cuh"
 #include "host.cuh"
 #include <algorithm>
+#include <atomic>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -886,28 +887,55 @@ static int acc_common(const uint64_t* insts, size_t m, AccCommon<C>* out) {
     out->d = d; out->lg_n = lg_n;
     out->xis.resize(m * (lg_n + 1));
     std::vector<uint64_t> Us(12 * m);
-    // 4. m independent succinct checks (each sequential inside): spread over host threads
+    const bool trace = rt().tune[7] == 1;
+    auto t0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!trace) return;
+        auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[halo trace] acc_common m=%zu %-24s %9.3f ms\n", m, what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    };
+    // 4. m independent succinct checks (each sequential inside) on worker threads that take the instances in
+    // order, while this thread already feeds finished challenge vectors to the AS_DL sponge (step 6 is one serial
+    // chain of ~m lg n permutations - as long as all the checks together at m = 1024)
     std::vector<int> rc(m, HALO_OK);
     std::vector<std::string> why(m);
-    {
-        unsigned nt = (unsigned)std::min<size_t>(m, std::max(1u, std::thread::hardware_concurrency()));
-        auto work = [&](unsigned t) {
-            for (size_t i = t; i < m; i += nt) {
-                const uint64_t* qi = insts + i * iw;
-                if ((size_t)qi[12] != d) { rc[i] = HALO_EREJECT; why[i] = "d_i != d"; continue; }
+    std::vector<std::atomic<int>> done(m);
+    for (auto& f : done) f.store(0, std::memory_order_relaxed);
+    std::atomic<size_t> next{0};
+    auto work = [&]() {
+        for (;;) {
+            const size_t i = next.fetch_add(1, std::memory_order_relaxed);
+            if (i >= m) return;
+            const uint64_t* qi = insts + i * iw;
+            if ((size_t)qi[12] != d) { rc[i] = HALO_EREJECT; why[i] = "d_i != d"; }
+            else {
                 rc[i] = pcdl_succinct_check<C>(qi, (uint64_t*)(out->xis.data() + i * (lg_n + 1)), Us.data() + 12 * i);
                 if (rc[i]) why[i] = last_err();
             }
-        };
-        if (nt <= 1) work(0);
-        else { std::vector<std::thread> th; for (unsigned t = 0; t < nt; ++t) th.emplace_back(work, t); for (auto& x : th) x.join(); }
-    }
-    for (size_t i = 0; i < m; ++i) if (rc[i]) { last_err() = why[i]; return rc[i]; }
+            done[i].store(1, std::memory_order_release);
+        }
+    };
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const unsigned nt = (unsigned)std::min<size_t>(m, hw > 1 ? hw - 1 : 1);
+    std::vector<std::thread> th;
+    if (m > 1) for (unsigned t = 0; t < nt; ++t) th.emplace_back(work);
+    else work();
     // 6. alpha = rho1([h_i, U_i])
     Transcript<C> tr(LABEL_ASDL);
-    for (const SF& x : out->xis) tr.absorb_scalar(x);
+    int first_bad = -1;
+    for (size_t i = 0; i < m && first_bad < 0; ++i) {
+        while (!done[i].load(std::memory_order_acquire)) std::this_thread::yield();
+        if (rc[i]) { first_bad = (int)i; break; }
+        for (unsigned k = 0; k <= lg_n; ++k) tr.absorb_scalar(out->xis[i * (lg_n + 1) + k]);
+    }
+    for (auto& x : th) x.join();
+    if (first_bad < 0) for (size_t i = 0; i < m; ++i) if (rc[i]) { first_bad = (int)i; break; }
+    if (first_bad >= 0) { last_err() = why[first_bad]; return rc[first_bad]; }
+    lap("succinct checks + sponge");
     for (size_t i = 0; i < m; ++i) tr.absorb_point(H::from_words(Us.data() + 12 * i));
     const SF alpha = tr.challenge();
+    lap("transcript");
     out->alphas.resize(m);
     SF cur = fe_one<S>();
     for (size_t i = 0; i < m; ++i) { out->alphas[i] = cur; cur = fe_mul<S>(cur, alpha); }
@@ -917,6 +945,7 @@ static int acc_common(const uint64_t* insts, size_t m, AccCommon<C>* out) {
     out->Cbar = H::from_words(Cw);
     // 9. z = rho1(C, h)
     out->z = tr.challenge();
+    lap("C_bar, z");
     return HALO_OK;
 }
 

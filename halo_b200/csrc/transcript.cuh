@@ -53,10 +53,9 @@ private:
         for (int r = 0; r < 55; ++r) {
             Fe<F> t[3] = {pow7(s_[0]), pow7(s_[1]), pow7(s_[2])};
             for (int i = 0; i < 3; ++i) {
-                Fe<F> acc = fe_from_words<F>(poseidon_data::POSEIDON_RC[F][3 * r + i]);
-                for (int j = 0; j < 3; ++j)
-                    acc = fe_add<F>(acc, fe_mul<F>(t[j], fe_from_words<F>(poseidon_data::POSEIDON_MDS[F][3 * i + j])));
-                s_[i] = acc;
+                const unsigned long long (*M)[4] = poseidon_data::POSEIDON_MDS[F] + 3 * i;
+                s_[i] = fe_add<F>(fe_from_words<F>(poseidon_data::POSEIDON_RC[F][3 * r + i]),
+                                  fe_dot3<F>(t[0], fe_from_words<F>(M[0]), t[1], fe_from_words<F>(M[1]), t[2], fe_from_words<F>(M[2])));
             }
         }
     }

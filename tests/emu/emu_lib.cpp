@@ -5,6 +5,7 @@
 #define HALO_EMULATE_PTX 1
 #endif
 #include "curve.cuh"
+#include "transcript.cuh"
 #include <cstring>
 #include <cstddef>
 using namespace halo;
@@ -45,7 +46,29 @@ template <int C> static void mulk(const u64* a_xyz, const u64* k_canon, u64* out
     XYZZ<C> r = xyzz_mul_bits<C>(jac_to_xyzz<C>(a), (const u32*)k_canon);
     Jac<C> j = xyzz_to_jac<C>(r); memcpy(out_xyz, &j, 96);
 }
+template <int F> static void sponge_hash(const u64* in, size_t n, u64* out) {
+    PoseidonHost<F> sp;
+    for (size_t i = 0; i < n; ++i) { Fe<F> x; memcpy(x.l, in + 4 * i, 32); sp.absorb(x); }
+    Fe<F> r = sp.squeeze();
+    memcpy(out, r.l, 32);
+}
+template <int F> static void dot3(const u64* a, const u64* b, u64* o, size_t n) {
+    for (size_t i = 0; i + 3 <= n; i += 3) {
+        Fe<F> x[3], y[3];
+        for (int k = 0; k < 3; ++k) { memcpy(x[k].l, a + 4 * (i + k), 32); memcpy(y[k].l, b + 4 * (i + k), 32); }
+        Fe<F> r = fe_dot3<F>(x[0], y[0], x[1], y[1], x[2], y[2]);
+        memcpy(o + 4 * (i / 3), r.l, 32);
+    }
+}
 extern "C" {
+// the product's host sponge (transcript.cuh): absorb n elements, squeeze one
+void emu_poseidon_hash(int field, const u64* in, size_t n, u64* out) {
+    if (field == 0) sponge_hash<0>(in, n, out); else sponge_hash<1>(in, n, out);
+}
+// out[i] = a[3i]*b[3i] + a[3i+1]*b[3i+1] + a[3i+2]*b[3i+2]
+void emu_dot3(int field, const u64* a, const u64* b, u64* o, size_t n) {
+    if (field == 0) dot3<0>(a, b, o, n); else dot3<1>(a, b, o, n);
+}
 void emu_field_op(int field, int op, const u64* a, const u64* b, u64* o, size_t n) {
     if (field == 0) binop<0>(op, a, b, o, n); else binop<1>(op, a, b, o, n);
 }

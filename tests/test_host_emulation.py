@@ -15,7 +15,7 @@ _u64p = ctypes.POINTER(ctypes.c_uint64)
 def _build(tag, flags):
     so = os.path.join(HERE, "emu", f"libemu_{tag}.so")
     src = os.path.join(HERE, "emu", "emu_lib.cpp")
-    deps = [src, os.path.join(ROOT, "halo_b200/csrc/field.cuh"), os.path.join(ROOT, "halo_b200/csrc/curve.cuh")]
+    deps = [src] + [os.path.join(ROOT, "halo_b200/csrc", h) for h in ("field.cuh", "curve.cuh", "transcript.cuh")]
     if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-I", os.path.join(ROOT, "halo_b200/csrc"),
                                *flags, "-o", so, src])
@@ -55,6 +55,29 @@ def test_field_ops(emu, oracle, field):
     back = np.empty_like(a)
     emu.emu_field_op(field, 5, _p(out), _p(b), _p(back), ctypes.c_size_t(n))
     assert (back == a).all()
+
+
+@pytest.mark.parametrize("field", [0, 1])
+def test_host_sponge_and_lazy_dot(emu, oracle, field):
+    """The product's host Poseidon sponge (transcript.cuh, with its one-reduction MDS rows) against the KAT-pinned
+    oracle sponge, and the three-term dot product on edge values (all operands p-1: the largest accumulator)."""
+    O = oracle
+    p = O.MODULUS[field]
+    for n in (0, 1, 2, 3, 5, 8):
+        x = O.random_scalars(field, max(n, 1), 300 + n)[:n]
+        out = np.empty(4, dtype=np.uint64)
+        emu.emu_poseidon_hash(field, _p(np.ascontiguousarray(x)), ctypes.c_size_t(n), _p(out))
+        assert (out == O.poseidon_hash(field, x)).all(), n
+    n = 3 * 400
+    a, b = O.random_scalars(field, n, 11), O.random_scalars(field, n, 12)
+    edge = O.ints_to_mont(field, [p - 1] * 6 + [0, 1, p - 1, p - 1, 0, 0])
+    a[: len(edge)] = edge
+    b[: len(edge)] = O.ints_to_mont(field, [p - 1] * 6 + [p - 1, p - 1, 1, 0, 0, 0])
+    out = np.empty((n // 3, 4), dtype=np.uint64)
+    emu.emu_dot3(field, _p(a), _p(b), _p(out), ctypes.c_size_t(n))
+    prod = O.field_mul(field, a, b).reshape(-1, 3, 4)
+    exp = O.field_add(field, O.field_add(field, prod[:, 0], prod[:, 1]), prod[:, 2])
+    assert (out == exp).all()
 
 
 @pytest.mark.parametrize("curve", [0, 1])

@@ -36,7 +36,10 @@ for m in ms_list:
     qs = [base[i % len(base)] for i in range(m)]
     best = {}
     for rep in range(2):
+        if os.environ.get("HALO_TRACE") and rep == 1:
+            lib.halo_set_tuning(7, 1)
         t = time.perf_counter(); acc = hb.acc.prover(0, qs); dt = time.perf_counter() - t
+        lib.halo_set_tuning(7, 0)
         best["prover"] = min(best.get("prover", 1e9), dt)
         t = time.perf_counter(); hb.acc.verifier(0, qs, acc); dt = time.perf_counter() - t
         best["verifier"] = min(best.get("verifier", 1e9), dt)
