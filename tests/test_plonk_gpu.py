@@ -177,3 +177,39 @@ def test_trace_new_matches_the_fixture_and_proves(hb, oracle, params, curve):
     assert O.plonk_verify(curve, lg_n, circuit.C_qs, c["public_inputs"], 0, acc0.q.w, pi.w)
     with pytest.raises(hb.PreconditionError):
         hb.plonk.Trace(curve, [], c["public_inputs"], cols[10:26, :48], cols[26:41, :48], cols[0:10, :48], 48, acc0)
+
+
+def test_large_proof_verifies_and_matches_commit_path(hb, oracle):
+    """2^15 rows (60 MB of columns: the staged multi-threaded upload path) on synthetic generators: the proof verifies,
+    its witness commitments equal stand-alone commits of the same columns, and a different witness is rejected
+    against it.  Size-independent properties only - the oracle prover is not run at this size."""
+    import ctypes
+    from halo_b200._lib import lib, check
+    curve, lg_n = 0, 15
+    n = 1 << lg_n
+    u64p = ctypes.POINTER(ctypes.c_uint64)
+    gs = np.zeros((n + 2, 8), dtype=np.uint64)
+    check(lib.halo_gen_points(curve, ctypes.c_uint64(77), ctypes.c_size_t(0), ctypes.c_size_t(n + 2), gs.ctypes.data_as(u64p)))
+    hb.pp.reset(curve)
+    hb.pp.set_pp(curve, gs[:n], gs[n], gs[n + 1])
+    try:
+        polys, w_evals = hb.plonk.synthetic_circuit(curve, lg_n, seed=3)
+        acc0 = hb.acc.Accumulator.zero(curve, n)
+        circuit = hb.plonk.PlonkCircuit.from_polys(curve, polys, 0)
+        pub = hb.plonk.PlonkPublicInputs(np.zeros((0, 4), dtype=np.uint64), acc0)
+        pi = hb.plonk.PlonkProof.naive_prover(circuit, pub, hb.plonk.PlonkWitness(polys, w_evals))
+        pi.verify(circuit, pub)
+        C_ws = pi.commitments()["ws"]
+        for i in (0, 1, 2):
+            exp = hb.pcdl.commit(curve, polys[10 + i], n - 1)
+            assert (oracle.point_to_affine(curve, C_ws[i].reshape(1, 12)) == oracle.point_to_affine(curve, exp.reshape(1, 12))).all()
+        # z = 1 for the identity permutation: its commitment is G_0 and its evaluations are one
+        one = hb.consts.one(curve)
+        ev = pi.evals()
+        assert (ev["z"] == one).all() and (ev["z_omega"] == one).all()
+        bad = pi.w.copy()
+        bad[4:8] = ev["ws"][0]                              # w_1(xi) := w_0(xi)
+        with pytest.raises(hb.Rejected):
+            hb.plonk.PlonkProof(curve, lg_n, bad).verify_succinct(circuit, pub)
+    finally:
+        hb.pp.reset(curve)
