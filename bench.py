@@ -434,6 +434,32 @@ def run_halo(args, rank, world, local_rank):
         if not verified:
             raise SystemExit("bench.py: MSM result does not match the known discrete-log check")
 
+    # whole proofs do not shard (replicas only): at N > 1 every rank proves its own 2^log_n-gate
+    # circuit at the same time; the time is the max over ranks
+    replicas = None
+    if world > 1 and not args.no_path:
+        lg = min(args.log_n, 20)
+        rows = 1 << lg
+        sh = np.zeros((2, 8), dtype=np.uint64)
+        check(lib.halo_gen_points(PALLAS, ctypes.c_uint64(5), ctypes.c_size_t(0), ctypes.c_size_t(2), sh.ctypes.data_as(u64p)))
+        halo_b200.pp.reset(PALLAS)
+        halo_b200.pp.set_pp(PALLAS, h_pts.numpy().view(np.uint64)[:rows], sh[0], sh[1])
+        polys, w_evals = halo_b200.plonk.synthetic_circuit(PALLAS, lg, seed=7 + rank)
+        acc0 = halo_b200.acc.Accumulator.zero(PALLAS, rows)
+        circuit = halo_b200.plonk.PlonkCircuit.from_polys(PALLAS, polys, 0)
+        pub = halo_b200.plonk.PlonkPublicInputs(np.zeros((0, 4), dtype=np.uint64), acc0)
+        wit = halo_b200.plonk.PlonkWitness(polys, w_evals)
+        best = None
+        for _ in range(2):
+            dist.barrier(); torch.cuda.synchronize()
+            t = time.perf_counter(); pi = halo_b200.plonk.PlonkProof.naive_prover(circuit, pub, wit); dt = time.perf_counter() - t
+            tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            best = float(tt.item()) if best is None else min(best, float(tt.item()))
+        pi.verify(circuit, pub)
+        replicas = {"ms": best * 1e3, "proofs_per_s": world / best, "note": "one independent proof per GPU, max over ranks"}
+        halo_b200.pp.reset(PALLAS)
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -467,6 +493,8 @@ def run_halo(args, rank, world, local_rank):
     path = None
     if world == 1 and not args.no_path:
         path = measure_path(lib, check, halo_b200, torch, stream, d_pts, h_sc, args.log_n)
+    elif replicas is not None:
+        path = {f"plonk_prove_2^{min(args.log_n, 20)}_replicas": replicas}
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
