@@ -68,6 +68,17 @@ int upload_staged(void* d_dst, const void* h_src, size_t bytes) {
             for (size_t c = t; c < nchunks; c += T, slot ^= 1) {
                 const size_t off = c * CH, len = std::min(CH, bytes - off);
                 if (cudaEventSynchronize(R.up_ev[t][slot]) != cudaSuccess) { status[t] = 1; return; }   // slot free again
+                // an all-zero chunk (unused columns of a circuit) is set on the device instead of crossing the link;
+                // the scan stops at the first nonzero word, so dense data pays nothing for it
+                const uint64_t* w = (const uint64_t*)((const char*)h_src + off);
+                size_t nz = 0;
+                const size_t words = ((uintptr_t)w % 8 == 0) ? len / 8 : 0;
+                while (nz < words && w[nz] == 0) ++nz;
+                if (words && nz == words && len % 8 == 0) {
+                    if (cudaMemsetAsync((char*)d_dst + off, 0, len, R.up_stream[t]) != cudaSuccess ||
+                        cudaEventRecord(R.up_ev[t][slot], R.up_stream[t]) != cudaSuccess) { status[t] = 1; return; }
+                    continue;
+                }
                 memcpy(R.up_buf[t][slot], (const char*)h_src + off, len);
                 if (cudaMemcpyAsync((char*)d_dst + off, R.up_buf[t][slot], len, cudaMemcpyHostToDevice, R.up_stream[t]) != cudaSuccess ||
                     cudaEventRecord(R.up_ev[t][slot], R.up_stream[t]) != cudaSuccess) { status[t] = 1; return; }

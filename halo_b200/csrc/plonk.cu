@@ -159,14 +159,19 @@ template <int F, class V> HD Fe<F> f_gc_point(const V& v, const Fe<F>* M, unsign
 // ---------------------------------------------------------------------------------------------------------
 template <int F> struct Challenges { Fe<F> beta, gamma, alpha, alpha2, M[9]; };
 
+// Columns that are the zero polynomial (unused selectors, witness and round-constant columns of a circuit) are not
+// transformed at all: slot[c] is the position of column c among the transformed ones, and every zero column reads
+// one shared column of zeros.
+struct ColMap { unsigned char slot[N_COLS]; };
+
 // values of the 61 columns at point j of the current coset; the omega-shift is index j+1 in the same coset
 template <int F> struct ColView {
-    const Fe<F>* ev; size_t n, j, jn;
-    HD Fe<F> col(int c) const { return p_ld<F>(ev + (size_t)c * n + j); }
+    const Fe<F>* ev; size_t n, j, jn; const ColMap& m;
+    HD Fe<F> col(int c) const { return p_ld<F>(ev + (size_t)m.slot[c] * n + j); }
     HD Fe<F> q(int i) const { return col(COL_Q + i); }
     HD Fe<F> w(int i) const { return col(COL_W + i); }
     HD Fe<F> r(int i) const { return col(COL_R + i); }
-    HD Fe<F> nw(int i) const { return p_ld<F>(ev + (size_t)(COL_W + i) * n + jn); }
+    HD Fe<F> nw(int i) const { return p_ld<F>(ev + (size_t)m.slot[COL_W + i] * n + jn); }
     HD Fe<F> pi() const { return col(COL_PI); }
 };
 
@@ -174,10 +179,11 @@ template <int F> struct ColView {
 template <int F>
 __global__ void __launch_bounds__(128) plonk_numerator_kernel(const Fe<F>* __restrict__ ev, size_t n, Challenges<F> ch,
                                                               unsigned gate_mask, Fe<F>* __restrict__ out,
-                                                              unsigned coset, unsigned stride, Fe<F> scale, int scaled) {
+                                                              unsigned coset, unsigned stride, Fe<F> scale, int scaled,
+                                                              const __grid_constant__ ColMap map) {
     size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (j >= n) return;
-    ColView<F> v{ev, n, j, j + 1 == n ? 0 : j + 1};
+    ColView<F> v{ev, n, j, j + 1 == n ? 0 : j + 1, map};
     Fe<F> f = f_gc_point<F, ColView<F>>(v, ch.M, gate_mask);
     // f' and g' (protocol.rs:132-139)
     Fe<F> fp = fe_one<F>(), gp = fe_one<F>();
@@ -342,17 +348,20 @@ __global__ void __launch_bounds__(256) plonk_eval_kernel(EvalSet<F> es, size_t n
     if (t == 0) p_st<F>(partial + (size_t)blockIdx.y * gridDim.x + blockIdx.x, acc);
 }
 
-// dst[c][k] = src[c][k] * g^k for every column c: the coset shift of a batched size-n NTT, fused with the copy into
-// the transform's scratch buffer.  g^k = hi[k >> 10] * lo[k & 1023]; one thread per k, coalesced across columns.
+// dst[c][k] = src[list[c]][k] * g^k for the ncols listed columns: the coset shift of a batched size-n NTT, fused with
+// the (compacting) copy into the transform's scratch buffer.  g^k = hi[k >> 10] * lo[k & 1023]; one thread per k,
+// coalesced across columns.
 template <int F>
 __global__ void __launch_bounds__(256) plonk_coset_stage_kernel(const Fe<F>* __restrict__ src, Fe<F>* __restrict__ dst, size_t n,
                                                                 int ncols, const Fe<F>* __restrict__ lo,
-                                                                const Fe<F>* __restrict__ hi) {
+                                                                const Fe<F>* __restrict__ hi,
+                                                                const __grid_constant__ ColMap list) {
     size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     Fe<F> w = p_ld<F>(lo + (k & 1023));
     if (k >> 10) w = fe_mul<F>(w, p_ld<F>(hi + (k >> 10)));
-    for (int c = 0; c < ncols; ++c) p_st<F>(dst + (size_t)c * n + k, fe_mul<F>(p_ld<F>(src + (size_t)c * n + k), w));
+    for (int c = 0; c < ncols; ++c)
+        p_st<F>(dst + (size_t)c * n + k, fe_mul<F>(p_ld<F>(src + (size_t)list.slot[c] * n + k), w));
 }
 
 // any nonzero coefficient in column c?  flags[c] |= 1
@@ -466,11 +475,28 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     HALO_CUDA(cudaStreamSynchronize(st));                  // neg_pub / one are host temporaries
     if (int e = ntt_device<S>(stage, col(COL_PI), (int)lg_n, 1, true, nullptr)) return e;
     if (int e = ntt_device<S>(stage + n, col(COL_L1), (int)lg_n, 4, true, nullptr)) return e;   // l1, wom0..2 are adjacent
-    HALO_CUDA(cudaMemsetAsync(d_flags, 0, NQ * sizeof(int), st));
-    plonk_nonzero_kernel<S><<<dim3(32, NQ), 256, 0, st>>>(col(COL_Q), n, d_flags);
+    // which columns are the zero polynomial: their commitments are the identity, their coset evaluations are zero,
+    // and the custom gates of an all-zero selector are switched off (tuning key 6 = 1 treats every column as dense)
+    const bool dense = R.tune[6] == 1;
+    HALO_CUDA(cudaMemsetAsync(d_flags, 0, N_COLS * sizeof(int), st));
+    plonk_nonzero_kernel<S><<<dim3(32, N_IN), 256, 0, st>>>(cols, n, d_flags);
     R.launches += 1;
-    int h_flags[NQ];
-    HALO_CUDA(cudaMemcpyAsync(h_flags, d_flags, sizeof(h_flags), cudaMemcpyDeviceToHost, st));
+    int h_flags[N_COLS];
+    HALO_CUDA(cudaMemcpyAsync(h_flags, d_flags, N_IN * sizeof(int), cudaMemcpyDeviceToHost, st));
+    HALO_CUDA(cudaStreamSynchronize(st));
+    auto nonzero = [&](int c) { return dense || h_flags[c] != 0; };
+    // commitments of `count` adjacent columns: one batched MSM per run of nonzero columns
+    auto commit_cols = [&](const SF* first, int count, int flag0, uint64_t* o) -> int {
+        const Jac<C> id = xyzz_to_jac<C>(xyzz_identity<C>());
+        for (int i = 0; i < count;) {
+            if (flag0 >= 0 && !nonzero(flag0 + i)) { memcpy(o + 12 * i, &id, 96); ++i; continue; }
+            int j = i + 1;
+            while (j < count && (flag0 < 0 || nonzero(flag0 + j))) ++j;
+            if (int e = msm_device<C>(R.pp[C].d_gs, first + (size_t)i * n, n, (size_t)(j - i), o + 12 * i, 0)) return e;
+            i = j;
+        }
+        return HALO_OK;
+    };
     lap("round 0 (upload, iNTTs)");
 
     Transcript<C> tr(LABEL_PLONK);
@@ -483,7 +509,7 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     uint64_t* o_acc = o_piro + evalproof_words(lg_n);
 
     // ---- round 1 (:114-115): the 16 witness commitments as one batched MSM over the resident generators
-    if (int e = msm_device<C>(R.pp[C].d_gs, col(COL_W), n, NW, o_Cws, 0)) return e;
+    if (int e = commit_cols(col(COL_W), NW, COL_W, o_Cws)) return e;
     for (int i = 0; i < NW; ++i) tr.absorb_point(H::from_words(o_Cws + 12 * i));
     lap("round 1 (16 commits)");
 
@@ -507,6 +533,9 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     R.launches += 1;
     HALO_CUDA(cudaGetLastError());
     if (int e = ntt_device<S>(tmp, col(COL_Z), (int)lg_n, 2, true, nullptr)) return e;          // z, z_omega
+    plonk_nonzero_kernel<S><<<dim3(32, N_COLS - N_IN), 256, 0, st>>>(col(N_IN), n, d_flags + N_IN);
+    R.launches += 1;
+    HALO_CUDA(cudaMemcpyAsync(h_flags + N_IN, d_flags + N_IN, (N_COLS - N_IN) * sizeof(int), cudaMemcpyDeviceToHost, st));
     if (int e = msm_device<C>(R.pp[C].d_gs, col(COL_Z), n, 1, o_Cz, 0)) return e;
     tr.absorb_point(H::from_words(o_Cz));
     lap("round 3 (z)");
@@ -516,24 +545,36 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     ch.alpha2 = fe_sqr<S>(ch.alpha);
     for (int i = 0; i < 9; ++i) ch.M[i] = fe_from_words<S>(poseidon_data::POSEIDON_MDS[S][i]);
     unsigned gate_mask = 0;
-    for (int i = 0; i < 5; ++i) if (h_flags[5 + i]) gate_mask |= 1u << i;
+    for (int i = 0; i < 5; ++i) if (nonzero(COL_Q + 5 + i)) gate_mask |= 1u << i;
     const SF w16n = root_of_unity<S>((int)lg_n + 4);
+    // only the nonzero columns are staged and transformed (compactly, in column order); the zero ones share slot nnz
+    ColMap map, list;
+    int nnz = 0;
+    memset(&map, 0, sizeof map); memset(&list, 0, sizeof list);
+    for (int c = 0; c < N_EVAL; ++c) if (nonzero(c)) { list.slot[nnz] = (unsigned char)c; map.slot[c] = (unsigned char)nnz; ++nnz; }
+    for (int c = 0; c < N_EVAL; ++c) if (!nonzero(c)) map.slot[c] = (unsigned char)nnz;
+    if (nnz < N_EVAL) HALO_CUDA(cudaMemsetAsync(ev + (size_t)nnz * n, 0, n * 32, st));
     auto numerator_on_coset = [&](unsigned c, SF* dst, unsigned slot, unsigned stride, const SF* scale) -> int {
         SF g = one;                                        // w16n^c
         for (unsigned i = 0; i < c; ++i) g = fe_mul<S>(g, w16n);
         if (c == 0) {
-            HALO_CUDA(cudaMemcpyAsync(tmp, cols, (size_t)N_EVAL * n * 32, cudaMemcpyDeviceToDevice, st));
+            for (int i = 0; i < nnz;) {                    // runs of adjacent source columns
+                int j = i + 1;
+                while (j < nnz && list.slot[j] == list.slot[j - 1] + 1) ++j;
+                HALO_CUDA(cudaMemcpyAsync(tmp + (size_t)i * n, col(list.slot[i]), (size_t)(j - i) * n * 32, cudaMemcpyDeviceToDevice, st));
+                i = j;
+            }
         } else {
             SF g1024 = g;
             for (int i = 0; i < 10; ++i) g1024 = fe_sqr<S>(g1024);
             plonk_powers_kernel<S><<<1, 128, 0, st>>>(gtab, 1024, g);
             plonk_powers_kernel<S><<<(unsigned)((n / 1024 / 16 + 128) / 128), 128, 0, st>>>(gtab + 1024, (n + 1023) / 1024, g1024);
-            plonk_coset_stage_kernel<S><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(cols, tmp, n, N_EVAL, gtab, gtab + 1024);
+            plonk_coset_stage_kernel<S><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(cols, tmp, n, nnz, gtab, gtab + 1024, list);
             R.launches += 3;
         }
-        if (int e = ntt_device<S>(tmp, ev, (int)lg_n, N_EVAL, false, nullptr)) return e;
+        if (int e = ntt_device<S>(tmp, ev, (int)lg_n, (size_t)nnz, false, nullptr)) return e;
         plonk_numerator_kernel<S><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(ev, n, ch, gate_mask, dst, slot, stride,
-                                                                              scale ? *scale : one, scale ? 1 : 0);
+                                                                              scale ? *scale : one, scale ? 1 : 0, map);
         R.launches += 1;
         HALO_CUDA(cudaGetLastError());
         return HALO_OK;
@@ -571,7 +612,12 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
         R.launches += 1;
         HALO_CUDA(cudaGetLastError());
     }
-    if (int e = msm_device<C>(R.pp[C].d_gs, tq, n, NT, o_Cts, 0)) return e;
+    {   // on the 8-coset path deg t < 8n: chunks 8..15 are zero and commit to the identity
+        const int nt_live = (!not_divisible && R.tune[5] != 1 && !dense) ? NT / 2 : NT;
+        if (int e = commit_cols(tq, nt_live, -1, o_Cts)) return e;
+        const Jac<C> id = xyzz_to_jac<C>(xyzz_identity<C>());
+        for (int i = nt_live; i < NT; ++i) memcpy(o_Cts + 12 * i, &id, 96);
+    }
     for (int i = 0; i < NT; ++i) tr.absorb_point(H::from_words(o_Cts + 12 * i));
     lap("round 4 (quotient, 16 commits)");
 

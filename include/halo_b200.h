@@ -72,6 +72,7 @@ int halo_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const
  * key 3 = log2 of the vector length below which the IPA stops folding generators (-1 never, 0 default),
  * key 4 = 1 disables the radix-4 (two-at-once) generator folds of the IPA,
  * key 5 = 1 makes the PLONK prover always take the 16-coset coefficient-division path for the quotient,
+ * key 6 = 1 makes the PLONK prover transform and commit all-zero columns like any other (no sparse-column path),
  * key 7 = 1 prints a per-round phase trace of halo_pcdl_open to stderr */
 int halo_set_tuning(int key, int value);
 /* window width override for experiments (0 = automatic) */

@@ -92,6 +92,13 @@ def test_proof_matches_oracle_and_verifies(hb, oracle, params, curve, lg_n, kind
     finally:
         lib.halo_set_tuning(5, 0)
     same_proof(O, curve, lg_n, slow.w, exp)
+    # all-zero columns are skipped (identity commitments, no transforms); treating them as dense gives the same proof
+    lib.halo_set_tuning(6, 1)
+    try:
+        dense = hb.plonk.PlonkProof.naive_prover(circuit, pub, wit)
+    finally:
+        lib.halo_set_tuning(6, 0)
+    same_proof(O, curve, lg_n, dense.w, exp)
     # the next accumulator is a valid one (protocol.rs:493-502) and chains into a second proof (IVC-style)
     hb.acc.decider(curve, pi.acc_next)
     pub2 = hb.plonk.PlonkPublicInputs(c["public_inputs"], pi.acc_next)
