@@ -26,6 +26,14 @@
 #define HD inline
 #define DEV inline
 #endif
+// Latency-bound kernels (a few warps walking a long dependent chain of point additions) want the multiplier as ONE
+// shared subroutine: fully inlined, a point addition is ~70 KB of straight-line code and the instruction cache
+// misses dominate.  Translation units built with -DHALO_NOINLINE_MUL get fe_mul / fe_sqr as real functions.
+#if defined(__CUDACC__) && defined(HALO_NOINLINE_MUL)
+#define MULDEV __host__ __device__ __noinline__
+#else
+#define MULDEV DEV
+#endif
 
 namespace halo {
 
@@ -197,7 +205,7 @@ template <int FID> DEV Fe<FID> mont_reduce(const u32 (&t)[16]) {
 
 // 8x8 limb schoolbook product into even/odd-aligned accumulators so that every 64-bit partial product lands
 // on an aligned register pair (one IMAD.WIDE.U32.X each).  ev holds columns 0..15, od holds columns 1..15.
-template <int FID> DEV Fe<FID> fe_mul(const Fe<FID>& a, const Fe<FID>& b) {
+template <int FID> MULDEV Fe<FID> fe_mul(const Fe<FID>& a, const Fe<FID>& b) {
     u32 ev[16], od[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) { ev[i] = 0; od[i] = 0; }
@@ -247,7 +255,7 @@ DEV void sqr_chain(u32 (&acc)[N], u32 x, const u32* a) {
 // Dedicated squaring: the 28 off-diagonal products a_i*a_j (i < j) once, doubled, plus the 8 diagonal squares:
 // 36 wide multiplies instead of 64 (60 instead of 88 with the reduction).  Off-diagonal products with j - i odd
 // land on odd columns (accumulator od, od[k] = column k+1), those with j - i even on even columns (ev).
-template <int FID> DEV Fe<FID> fe_sqr(const Fe<FID>& a) {
+template <int FID> MULDEV Fe<FID> fe_sqr(const Fe<FID>& a) {
     u32 ev[16], od[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) { ev[i] = 0; od[i] = 0; }

@@ -504,6 +504,185 @@ static void msm_combine_host(const XYZZ<C>* win, const MsmPlan& P, uint64_t out_
     memcpy(out_xyz, &j, 96);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Small MSMs (k <= 2^13) in ONE launch.  The general pipeline above is ~25 dependent launches, which is a
+// 0.45-0.8 ms latency floor; the IPA spends its last 15 rounds on MSM pairs of this size (crates/accumulation/src/
+// pcdl.rs:413,417 once the vectors are short) and small proofs consist of nothing else.  Here one CTA owns one
+// (MSM, 8-bit window, point range) triple end to end: signed digits -> counting sort of the point indices by bucket in
+// shared memory -> four threads per bucket accumulate its run -> (b+1)*bucket_b by double-and-add -> tree sum.
+// The host adds the range partials and runs the same Horner as for the general path.  A window whose largest
+// bucket is far above the mean (degenerate scalar distributions) raises a flag and the caller falls back to the
+// task-balanced general pipeline.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int SMALL_C = 8, SMALL_B = 128, SMALL_NWIN = 32, SMALL_T = 512;
+constexpr size_t SMALL_MAX_K = 8192;      // measured crossover against the general pipeline: between 2^13 and 2^14
+
+// signed digit (width 8) of window w of a canonical scalar s < 2^255: with A = 0x7f in every byte, the carry into
+// window w under the rule "digit > 128 -> digit - 256, carry 1" is the carry into bit 8w of s + A
+__device__ __forceinline__ int small_digit(const u32 (&s)[8], u32 w) {
+    const u32 limb = w >> 2, sh = (w & 3u) * 8u;
+    u32 carry = 0, t = 0;
+#pragma unroll
+    for (u32 i = 0; i < 8; ++i) {
+        u64 x = (u64)s[i] + 0x7f7f7f7fu + carry;
+        if (i == limb) t = (u32)x;
+        carry = (u32)(x >> 32);
+    }
+    u32 sl = 0;
+#pragma unroll
+    for (u32 i = 0; i < 8; ++i) if (i == limb) sl = s[i];
+    const u32 cin = ((t ^ sl ^ 0x7f7f7f7fu) >> sh) & 1u;
+    int d = (int)((sl >> sh) & 0xffu) + (int)cin;
+    if (d > 128) d -= 256;
+    return d;
+}
+
+template <int C>
+__global__ void __launch_bounds__(SMALL_T, 1) msm_small_kernel(const Affine<C>* __restrict__ bases,
+                                                               const Fe<CurveTraits<C>::SCALAR>* __restrict__ scalars, u32 k,
+                                                               ptrdiff_t base_stride, u32 split, u32 chunk, u32 max_bucket,
+                                                               XYZZ<C>* __restrict__ out, u32* __restrict__ flag) {
+    constexpr int SF = CurveTraits<C>::SCALAR;
+    extern __shared__ __align__(16) unsigned char small_raw[];
+    unsigned short* sorted = reinterpret_cast<unsigned short*>(small_raw);   // <= 32768 entries: index in range | sign << 15
+    XYZZ<C>* red = reinterpret_cast<XYZZ<C>*>(small_raw);                    // reused after the accumulation
+    __shared__ u32 cnt[SMALL_B], off[SMALL_B], cur[SMALL_B], wsum[4], s_bad;
+    const u32 tid = threadIdx.x;
+    const u32 h = blockIdx.x % split, w = (blockIdx.x / split) % SMALL_NWIN, j = blockIdx.x / (split * SMALL_NWIN);
+    const u32 lo = h * chunk, hi = min(k, lo + chunk);
+    const Fe<SF>* sc = scalars + (size_t)j * k;
+    bases += (ptrdiff_t)j * base_stride;
+    if (tid < SMALL_B) cnt[tid] = 0;
+    if (tid == 0) s_bad = 0;
+    __syncthreads();
+    for (u32 p = lo + tid; p < hi; p += SMALL_T) {
+        Fe<SF> s = fe_to_canonical<SF>(load_fe(sc + p));
+        int d = small_digit(s.l, w);
+        if (d != 0) atomicAdd(&cnt[abs(d) - 1], 1u);
+    }
+    __syncthreads();
+    if (tid < SMALL_B) {                                   // exclusive scan of the 128 bucket sizes (4 warps)
+        const u32 v = cnt[tid];
+        u32 x = v;
+#pragma unroll
+        for (int dlt = 1; dlt < 32; dlt <<= 1) { u32 y = __shfl_up_sync(0xffffffffu, x, dlt); if ((tid & 31) >= (u32)dlt) x += y; }
+        if ((tid & 31) == 31) wsum[tid >> 5] = x;
+        if (v > max_bucket) s_bad = 1;
+        off[tid] = x - v;
+    }
+    __syncthreads();
+    if (s_bad) { if (tid == 0) atomicOr(flag, 1u); return; }
+    if (tid < SMALL_B) {
+        u32 add = 0;
+        for (u32 i = 0; i < (tid >> 5); ++i) add += wsum[i];
+        off[tid] += add; cur[tid] = off[tid];
+    }
+    __syncthreads();
+    for (u32 p = lo + tid; p < hi; p += SMALL_T) {
+        Fe<SF> s = fe_to_canonical<SF>(load_fe(sc + p));
+        int d = small_digit(s.l, w);
+        if (d != 0) {
+            u32 pos = atomicAdd(&cur[abs(d) - 1], 1u);
+            sorted[pos] = (unsigned short)((p - lo) | (d < 0 ? 0x8000u : 0u));
+        }
+    }
+    __syncthreads();
+    // four threads per bucket, each a contiguous quarter of the bucket's run
+    const u32 b = tid >> 2, q = tid & 3u;
+    XYZZ<C> acc = xyzz_identity<C>();
+    {
+        const u32 n_b = cnt[b], o_b = off[b];
+        const u32 e0 = o_b + (n_b * q) / 4, e1 = o_b + (n_b * (q + 1)) / 4;
+        if (e0 < e1) {
+            u32 e = sorted[e0];
+            Affine<C> pt = load_affine(bases + lo + (e & 0x7fffu));
+            for (u32 i = e0; i < e1; ++i) {
+                u32 e_next = 0; Affine<C> p_next;
+                if (i + 1 < e1) { e_next = sorted[i + 1]; p_next = load_affine(bases + lo + (e_next & 0x7fffu)); }
+                xyzz_madd<C>(acc, pt, (e >> 15) != 0);
+                e = e_next; pt = p_next;
+            }
+        }
+    }
+    { XYZZ<C> o = xyzz_shfl_down<C>(acc, 2); xyzz_add<C>(acc, o); }
+    { XYZZ<C> o = xyzz_shfl_down<C>(acc, 1); xyzz_add<C>(acc, o); }
+    __syncthreads();                                       // every thread is done with `sorted`
+    // sum_b (b+1) * bucket_b = sum_i S_i with S_i = sum_{b >= i} bucket_b: a suffix scan (7 steps) and a tree sum (7)
+    if (q == 0) red[b] = acc;
+    __syncthreads();
+    if (tid < SMALL_B) acc = red[tid];
+    for (u32 st = 1; st < SMALL_B; st <<= 1) {
+        const bool on = tid < SMALL_B && tid + st < SMALL_B;
+        if (on) xyzz_add<C>(acc, red[tid + st]);
+        __syncthreads();
+        if (on) red[tid] = acc;
+        __syncthreads();
+    }
+    for (u32 st = SMALL_B / 2; st >= 1; st >>= 1) {
+        if (tid < st) { xyzz_add<C>(acc, red[tid + st]); red[tid] = acc; }
+        __syncthreads();
+    }
+    if (tid == 0) store_xyzz(out + blockIdx.x, acc);
+}
+
+// returns HALO_OK with *done = false when the caller must use the general pipeline instead
+template <int C>
+static int msm_small(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR>* d_scalars, size_t k, size_t nbatch,
+                     ptrdiff_t base_stride, uint64_t* out_xyz, bool* done) {
+    Runtime& R = rt();
+    cudaStream_t st = R.stream;
+    *done = false;
+    u32 split = (u32)std::max<size_t>(1, std::min<size_t>(4, (size_t)R.sm_count / (SMALL_NWIN * nbatch)));
+    while (split > 1 && (k + split - 1) / split < 2048) --split;
+    const u32 chunk = (u32)((k + split - 1) / split);
+    const size_t ncta = nbatch * SMALL_NWIN * split;
+    // a uniform window holds chunk/128 points per bucket (fewer when scalars are zero); tolerate 4x that
+    const u32 max_bucket = 4 * (chunk / SMALL_B) + 64;
+    static bool attr_set[2] = {false, false};
+    const size_t smem = std::max<size_t>((size_t)chunk * 2, (size_t)SMALL_B * sizeof(XYZZ<C>));
+    if (!attr_set[C]) {
+        HALO_CUDA(cudaFuncSetAttribute(msm_small_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+        attr_set[C] = true;
+    }
+    unsigned char* buf;
+    if (int e = ws_get(WS_WINSUM, 256 + ncta * sizeof(XYZZ<C>), (void**)&buf)) return e;
+    u32* d_flag = (u32*)buf;
+    XYZZ<C>* d_out = (XYZZ<C>*)(buf + 256);
+    if (int e = prof_begin()) return e;
+    HALO_CUDA(cudaMemsetAsync(d_flag, 0, 4, st));
+    msm_small_kernel<C><<<(unsigned)ncta, SMALL_T, smem, st>>>(d_bases, d_scalars, (u32)k, base_stride, split, chunk, max_bucket,
+                                                              d_out, d_flag);
+    R.launches += 1;
+    prof_mark("small");
+    HALO_CUDA(cudaGetLastError());
+    void* hbuf = nullptr;
+    if (int e = pinned_get(256 + ncta * sizeof(XYZZ<C>), &hbuf)) return e;
+    HALO_CUDA(cudaMemcpyAsync(hbuf, buf, 256 + ncta * sizeof(XYZZ<C>), cudaMemcpyDeviceToHost, st));
+    HALO_CUDA(cudaStreamSynchronize(st));
+    if (*(const u32*)hbuf != 0) return HALO_OK;            // skewed window: general pipeline
+    const XYZZ<C>* part = (const XYZZ<C>*)((const unsigned char*)hbuf + 256);
+    MsmPlan P;
+    P.c = SMALL_C; P.nwin = SMALL_NWIN;
+    auto combine = [&](size_t i) {
+        XYZZ<C> win[SMALL_NWIN];
+        for (int w = 0; w < SMALL_NWIN; ++w) {
+            const XYZZ<C>* src = part + (i * SMALL_NWIN + w) * split;
+            win[w] = src[0];
+            for (u32 hh = 1; hh < split; ++hh) xyzz_add<C>(win[w], src[hh]);
+        }
+        msm_combine_host<C>(win, P, out_xyz + 12 * i);
+    };
+    if (nbatch == 1) combine(0);
+    else {
+        std::vector<std::thread> th;
+        for (size_t i = 1; i < nbatch; ++i) th.emplace_back(combine, i);
+        combine(0);
+        for (auto& x : th) x.join();
+    }
+    *done = true;
+    return HALO_OK;
+}
+
 // nbatch MSMs of k points; MSM j uses bases + j*base_stride (0: all share one base set); scalars: nbatch x k
 // elements, out: nbatch x 12 words
 template <int C>
@@ -515,6 +694,12 @@ int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbat
         return HALO_OK;
     }
     HALO_CHECK(k < ((size_t)1 << 31), HALO_EINVAL, "msm: k must be < 2^31");
+    if (k <= SMALL_MAX_K && nbatch <= 4 && R.tune[1] != 1) {       // one-launch path (tuning key 1 = 1 disables it)
+        bool done = false;
+        if (int e = msm_small<C>((const Affine<C>*)d_bases, (const Fe<CurveTraits<C>::SCALAR>*)d_scalars, k, nbatch, base_stride,
+                                 out_xyz, &done)) return e;
+        if (done) return HALO_OK;
+    }
     MsmPlan P = make_plan(k, nbatch);
     HALO_CHECK(P.nwt * k < ((size_t)1 << 32), HALO_EINVAL, "msm: batch too large (nbatch*nwin*k must be < 2^32)");
     XYZZ<C>* d_win = nullptr;

@@ -201,6 +201,29 @@ def test_msm_degenerate_scalar_distributions(hb, oracle, kind):
 
 
 @pytest.mark.parametrize("curve", [0, 1])
+@pytest.mark.parametrize("k", [1, 5, 129, 2048, 5000, 8192])
+def test_msm_one_launch_path_and_its_fallback(hb, oracle, curve, k):
+    """MSMs up to 2^13 points take the one-launch kernel (msm_small_kernel); a window whose largest bucket is far
+    above the mean makes it hand over to the task-balanced pipeline.  Both must give the oracle's point, for uniform
+    scalars, for skewed ones (fallback) and with the path switched off (tuning key 1)."""
+    from halo_b200._lib import lib
+    O = oracle
+    sf = O.SCALAR_FIELD[curve]
+    pts = O.points_arith(curve, k)
+    uniform = O.random_scalars(sf, k, 4000 + k)
+    skewed = np.ascontiguousarray(np.tile(uniform[0], (k, 1)), dtype=np.uint64)        # every point in one bucket per window
+    half_zero = uniform.copy(); half_zero[::2] = 0
+    for sc in (uniform, skewed, half_zero):
+        exp = _aff(O, curve, O.msm(curve, pts, sc))
+        assert (_aff(O, curve, hb.group.point_dot_affine(curve, sc, pts)) == exp).all()
+        lib.halo_set_tuning(1, 1)
+        try:
+            assert (_aff(O, curve, hb.group.point_dot_affine(curve, sc, pts)) == exp).all()
+        finally:
+            lib.halo_set_tuning(1, 0)
+
+
+@pytest.mark.parametrize("curve", [0, 1])
 @pytest.mark.parametrize("log_k", [21, 22])
 def test_msm_beyond_oracle_sizes_known_discrete_logs(hb, oracle, curve, log_k):
     """BASELINE's largest sizes (2^21, 2^22) are out of the CPU oracle's reach in a test; the points are generated as
