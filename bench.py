@@ -259,6 +259,15 @@ def measure_path(lib, check, halo_b200, torch, stream, d_pts, h_sc, log_n):
             out[key] = {"ms": best * 1e3, "h2d_bytes": int(polys.nbytes + w_evals.nbytes)}
             if not dense:
                 t = time.perf_counter(); pi.verify(circuit, pub); out[f"plonk_verify_2^{lg}"] = {"ms": (time.perf_counter() - t) * 1e3}
+                # the circuit's own 41 columns resident in HBM (halo_plonk_circuit_load): a proof uploads its witness only
+                circuit.make_resident(polys)
+                best = None
+                for _ in range(2):
+                    t = time.perf_counter(); pi2 = halo_b200.plonk.PlonkProof.naive_prover(circuit, pub, wit); dt = time.perf_counter() - t
+                    best = dt if best is None else min(best, dt)
+                pi2.verify(circuit, pub)
+                out[key + "_circuit_resident"] = {"ms": best * 1e3, "h2d_bytes": int(polys[10:26].nbytes + w_evals.nbytes)}
+                circuit.release()
             del polys, w_evals, wit
     halo_b200.pp.reset(PALLAS)
     return out

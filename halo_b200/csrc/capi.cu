@@ -121,7 +121,11 @@ template <int C> int pcdl_succinct_check(const uint64_t*, uint64_t*, uint64_t*);
 template <int C> int pcdl_check(const uint64_t*);
 template <int C> int acc_prover(const uint64_t*, size_t, uint64_t*);
 size_t plonk_proof_words(unsigned lg_n);
-template <int C> int plonk_prove(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*);
+template <int C> int plonk_prove(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*);
+int plonk_circuit_load(int curve, unsigned lg_n, const uint64_t* polys, int* handle);
+int plonk_circuit_free(int handle);
+void plonk_circuits_release();
+int plonk_prove_resident(int handle, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*);
 template <int C> int plonk_verify(unsigned, const uint64_t*, const uint64_t*, size_t, size_t, const uint64_t*, const uint64_t*, int);
 template <int C> int acc_verifier(const uint64_t*, size_t, const uint64_t*);
 template <int S> int hpoly_coeffs(const uint64_t*, const uint64_t*, size_t, unsigned, uint64_t*);
@@ -364,6 +368,7 @@ int halo_shutdown(void) {
         R.up_stream[t] = nullptr;
     }
     for (int f = 0; f < 2; ++f) { if (R.ntt_tw[f]) cudaFree(R.ntt_tw[f]); R.ntt_tw[f] = nullptr; R.ntt_logmax[f] = 0; }
+    plonk_circuits_release();
     cudaStreamDestroy(R.own_stream);
     if (R.copy_stream) cudaStreamDestroy(R.copy_stream);
     if (R.copy_done) cudaEventDestroy(R.copy_done);
@@ -622,8 +627,25 @@ int halo_plonk_prove(int curve, unsigned lg_n, const uint64_t* polys, const uint
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
     HALO_CHECK(polys && w_evals && acc_prev && out_proof && (public_inputs || n_public == 0), HALO_EINVAL, "null argument");
-    return curve == 0 ? plonk_prove<0>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof)
-                      : plonk_prove<1>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof);
+    return curve == 0 ? plonk_prove<0>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof, nullptr)
+                      : plonk_prove<1>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof, nullptr);
+}
+
+int halo_plonk_circuit_load(int curve, unsigned lg_n, const uint64_t* polys, int* handle) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
+    HALO_CHECK(polys && handle, HALO_EINVAL, "null argument");
+    return plonk_circuit_load(curve, lg_n, polys, handle);
+}
+int halo_plonk_circuit_free(int handle) {
+    LOCK(); NEED_INIT();
+    return plonk_circuit_free(handle);
+}
+int halo_plonk_prove_circuit(int handle, const uint64_t* w_polys, const uint64_t* w_evals, const uint64_t* public_inputs,
+                             size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof) {
+    LOCK(); NEED_INIT();
+    HALO_CHECK(w_polys && w_evals && acc_prev && out_proof && (public_inputs || n_public == 0), HALO_EINVAL, "null argument");
+    return plonk_prove_resident(handle, w_polys, w_evals, public_inputs, n_public, acc_prev, out_proof);
 }
 
 int halo_plonk_verify(int curve, unsigned lg_n, const uint64_t* circuit_C_qs, const uint64_t* public_inputs, size_t n_public,

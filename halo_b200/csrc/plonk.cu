@@ -414,9 +414,11 @@ size_t plonk_proof_words(unsigned lg_n) { return 78 * 4 + 33 * 12 + 2 * evalproo
 
 // proof layout (u64 words): vs = ws[16] rs[15] qs[10] ts[16] ids[8] sigmas[8] z z_omega w_omegas[3] (4 each),
 // Cs = ws[16] ts[16] z (12 each), pi_r, pi_r_omega (EvalProof: Ls Rs U c hiding C_bar w_prime), acc_next (instance)
+// d_circuit == nullptr: polys holds all 57 columns.  Otherwise polys holds the 16 witness columns only and d_circuit
+// the 41 circuit columns (q r id sigma) already on the device (plonk_circuit_load).
 template <int C>
 int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, const uint64_t* pub, size_t n_pub,
-                const uint64_t* acc_prev, uint64_t* out) {
+                const uint64_t* acc_prev, uint64_t* out, const void* d_circuit) {
     typedef Host<C> H;
     typedef typename H::SF SF;
     constexpr int S = H::S;
@@ -454,7 +456,14 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     const SF omega = root_of_unity<S>((int)lg_n);
 
     // ---- round 0 (protocol.rs:74-109): resident coefficient columns
-    if (int e = upload_staged(cols, polys, (size_t)N_IN * n * 32)) return e;
+    if (d_circuit) {
+        const SF* dc = (const SF*)d_circuit;
+        HALO_CUDA(cudaMemcpyAsync(col(COL_Q), dc, (size_t)NQ * n * 32, cudaMemcpyDeviceToDevice, st));
+        HALO_CUDA(cudaMemcpyAsync(col(COL_R), dc + (size_t)NQ * n, (size_t)(NR + 2 * NS) * n * 32, cudaMemcpyDeviceToDevice, st));
+        if (int e = upload_staged(col(COL_W), polys, (size_t)NW * n * 32)) return e;
+    } else {
+        if (int e = upload_staged(cols, polys, (size_t)N_IN * n * 32)) return e;
+    }
     // staged evaluation vectors: PI (row i at omega^(i+1), negated), l1, and the three shifted witness columns
     SF* stage = tmp;                                       // [PI | l1 | wom0 wom1 wom2]
     HALO_CUDA(cudaMemsetAsync(stage, 0, 2 * n * 32, st));
@@ -469,7 +478,7 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     for (int i = 0; i < 3; ++i) {                          // shift_left of w_evals[i]
         const uint64_t* src = w_evals + (size_t)i * n * 4;
         SF* dst = stage + (size_t)(2 + i) * n;
-        HALO_CUDA(cudaMemcpyAsync(dst, src + 4, (n - 1) * 32, cudaMemcpyHostToDevice, st));
+        if (int e = upload_staged(dst, src + 4, (n - 1) * 32)) return e;
         HALO_CUDA(cudaMemcpyAsync(dst + (n - 1), src, 32, cudaMemcpyHostToDevice, st));
     }
     HALO_CUDA(cudaStreamSynchronize(st));                  // neg_pub / one are host temporaries
@@ -695,8 +704,56 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     if (trace) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); }
     return HALO_OK;
 }
-template int plonk_prove<0>(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*);
-template int plonk_prove<1>(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*);
+template int plonk_prove<0>(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*);
+template int plonk_prove<1>(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*);
+
+// ---- circuit columns kept on the device across proofs: the analogue of the reference holding `x: PlonkCircuit` /
+// the Trace's polynomials for every proof of the same circuit (an IVC chain proves one circuit over and over)
+namespace {
+struct ResidentCircuit { int curve; unsigned lg_n; void* d; };
+std::vector<ResidentCircuit>& circuits() { static std::vector<ResidentCircuit> v; return v; }
+}  // namespace
+
+int plonk_circuit_load(int curve, unsigned lg_n, const uint64_t* polys, int* handle) {
+    HALO_CHECK(lg_n >= 1 && lg_n <= 22, HALO_EINVAL, "plonk: rows must be a power of two in [2, 2^22]");
+    const size_t n = (size_t)1 << lg_n;
+    ResidentCircuit rc{curve, lg_n, nullptr};
+    HALO_CUDA(cudaMalloc(&rc.d, (size_t)(N_IN - NW) * n * 32));
+    char* d = (char*)rc.d;
+    int e = upload_staged(d, polys, (size_t)NQ * n * 32);
+    if (!e) e = upload_staged(d + (size_t)NQ * n * 32, polys + (size_t)COL_R * n * 4, (size_t)(NR + 2 * NS) * n * 32);
+    if (!e && cudaStreamSynchronize(rt().stream) != cudaSuccess) e = HALO_ECUDA;
+    if (e) { cudaFree(rc.d); return e; }
+    auto& v = circuits();
+    size_t slot = 0;
+    while (slot < v.size() && v[slot].d) ++slot;
+    if (slot == v.size()) v.push_back(rc); else v[slot] = rc;
+    *handle = (int)slot + 1;
+    return HALO_OK;
+}
+
+int plonk_circuit_free(int handle) {
+    auto& v = circuits();
+    HALO_CHECK(handle >= 1 && (size_t)handle <= v.size() && v[handle - 1].d, HALO_EINVAL, "plonk: unknown circuit handle");
+    HALO_CUDA(cudaStreamSynchronize(rt().stream));
+    HALO_CUDA(cudaFree(v[handle - 1].d));
+    v[handle - 1].d = nullptr;
+    return HALO_OK;
+}
+
+void plonk_circuits_release() {
+    for (auto& c : circuits()) if (c.d) { cudaFree(c.d); c.d = nullptr; }
+    circuits().clear();
+}
+
+int plonk_prove_resident(int handle, const uint64_t* w_polys, const uint64_t* w_evals, const uint64_t* pub, size_t n_pub,
+                         const uint64_t* acc_prev, uint64_t* out) {
+    auto& v = circuits();
+    HALO_CHECK(handle >= 1 && (size_t)handle <= v.size() && v[handle - 1].d, HALO_EINVAL, "plonk: unknown circuit handle");
+    const ResidentCircuit& rc = v[handle - 1];
+    return rc.curve == 0 ? plonk_prove<0>(rc.lg_n, w_polys, w_evals, pub, n_pub, acc_prev, out, rc.d)
+                         : plonk_prove<1>(rc.lg_n, w_polys, w_evals, pub, n_pub, acc_prev, out, rc.d);
+}
 
 namespace {
 // the proof's claimed evaluations as the value source of the gate expressions

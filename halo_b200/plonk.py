@@ -25,14 +25,42 @@ class PlonkCircuit:
     def __init__(self, curve, rows, public_input_count, C_qs):
         self.curve, self.rows, self.public_input_count = curve, rows, public_input_count
         self.C_qs = np.ascontiguousarray(C_qs, dtype=np.uint64).reshape(Q_POLYS, 12)
+        self.handle = 0
 
     @classmethod
-    def from_polys(cls, curve, polys, public_input_count):
-        """The selector commitments as Trace::new makes them (trace.rs:188): one batched MSM."""
+    def from_polys(cls, curve, polys, public_input_count, resident=False):
+        """The selector commitments as Trace::new makes them (trace.rs:188): one batched MSM.
+        resident=True also keeps the circuit's own columns (qs, rs, ids, sigmas) on the device, so that every proof
+        of this circuit uploads only its witness columns."""
         polys = np.ascontiguousarray(polys, dtype=np.uint64)
         n = polys.shape[1]
         C_qs = np.stack([pcdl.commit(curve, polys[i], n - 1) for i in range(Q_POLYS)])
-        return cls(curve, n, public_input_count, C_qs)
+        c = cls(curve, n, public_input_count, C_qs)
+        if resident:
+            c.make_resident(polys)
+        return c
+
+    def make_resident(self, polys):
+        """halo_plonk_circuit_load: the 41 circuit columns of `polys` (57, n, 4) stay in HBM until release()."""
+        _lib.ensure_init()
+        polys = np.ascontiguousarray(polys, dtype=np.uint64)
+        assert polys.shape == (N_COLUMNS, self.rows, 4)
+        self.release()
+        h = ctypes.c_int(0)
+        check(lib.halo_plonk_circuit_load(self.curve, ctypes.c_uint(self.rows.bit_length() - 1), ptr(polys.reshape(-1)),
+                                          ctypes.byref(h)))
+        self.handle = h.value
+
+    def release(self):
+        if getattr(self, "handle", 0):
+            lib.halo_plonk_circuit_free(ctypes.c_int(self.handle))
+            self.handle = 0
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
 
 
 class PlonkPublicInputs:
@@ -84,9 +112,15 @@ class PlonkProof:
             raise _lib.PreconditionError(_lib.HALO_EINVAL, "rows must be a power of two matching the columns")
         out = np.zeros(proof_words(lg_n), dtype=np.uint64)
         pub = public_inputs.public_inputs
-        check(lib.halo_plonk_prove(circuit.curve, ctypes.c_uint(lg_n), ptr(witness.polys.reshape(-1)),
-                                   ptr(witness.w_evals.reshape(-1)), ptr(pub.reshape(-1)) if pub.shape[0] else None,
-                                   ctypes.c_size_t(pub.shape[0]), ptr(public_inputs.acc_prev.q.w), ptr(out)))
+        if circuit.handle:                                  # circuit columns resident: only the witness crosses the link
+            w_polys = witness.polys[Q_POLYS:Q_POLYS + W_POLYS]
+            check(lib.halo_plonk_prove_circuit(ctypes.c_int(circuit.handle), ptr(w_polys.reshape(-1)),
+                                               ptr(witness.w_evals.reshape(-1)), ptr(pub.reshape(-1)) if pub.shape[0] else None,
+                                               ctypes.c_size_t(pub.shape[0]), ptr(public_inputs.acc_prev.q.w), ptr(out)))
+        else:
+            check(lib.halo_plonk_prove(circuit.curve, ctypes.c_uint(lg_n), ptr(witness.polys.reshape(-1)),
+                                       ptr(witness.w_evals.reshape(-1)), ptr(pub.reshape(-1)) if pub.shape[0] else None,
+                                       ctypes.c_size_t(pub.shape[0]), ptr(public_inputs.acc_prev.q.w), ptr(out)))
         return cls(circuit.curve, lg_n, out)
 
     # ---- protocol.rs:357-502 ----

@@ -145,6 +145,16 @@ int halo_construct_powers(int field, const uint64_t z[4], size_t n, uint64_t* ou
 size_t halo_plonk_proof_words(unsigned lg_n);
 int halo_plonk_prove(int curve, unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, const uint64_t* public_inputs,
                      size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof);
+/* The circuit's own columns kept on the device across proofs of the same circuit -- the analogue of the reference
+ * holding `x: PlonkCircuit` and the Trace's polynomials for every step of an IVC chain (crates/plonk/src/frontend/ivc/
+ * mod.rs:640-660 proves one circuit per curve over and over).  halo_plonk_circuit_load takes the same 57-column
+ * `polys` as halo_plonk_prove and keeps qs[10], rs[15], ids[8], sigmas[8] resident (41 x n x 32 B); *handle >= 1.
+ * halo_plonk_prove_circuit then needs only the 16 witness coefficient columns (`w_polys`, 16 x n x 4 words) and
+ * produces the identical proof.  Handles are released with halo_plonk_circuit_free or by halo_shutdown. */
+int halo_plonk_circuit_load(int curve, unsigned lg_n, const uint64_t* polys, int* handle);
+int halo_plonk_circuit_free(int handle);
+int halo_plonk_prove_circuit(int handle, const uint64_t* w_polys, const uint64_t* w_evals, const uint64_t* public_inputs,
+                             size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof);
 /* ≙ verify_succinct (protocol.rs:357-491) when succinct_only != 0, else verify (:493-502 = succinct + acc::decider).
  * circuit_C_qs = circuit.Cs.qs (10 x 12 words); public_input_count = circuit.public_input_count.
  * HALO_OK accept, HALO_EREJECT where the reference's ensure! fails. */

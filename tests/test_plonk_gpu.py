@@ -99,6 +99,13 @@ def test_proof_matches_oracle_and_verifies(hb, oracle, params, curve, lg_n, kind
     finally:
         lib.halo_set_tuning(6, 0)
     same_proof(O, curve, lg_n, dense.w, exp)
+    # circuit columns resident on the device (halo_plonk_circuit_load): only the witness is uploaded, same proof
+    circuit.make_resident(c["polys"])
+    try:
+        res = hb.plonk.PlonkProof.naive_prover(circuit, pub, wit)
+    finally:
+        circuit.release()
+    same_proof(O, curve, lg_n, res.w, exp)
     # the next accumulator is a valid one (protocol.rs:493-502) and chains into a second proof (IVC-style)
     hb.acc.decider(curve, pi.acc_next)
     pub2 = hb.plonk.PlonkPublicInputs(c["public_inputs"], pi.acc_next)

@@ -47,7 +47,12 @@ def run(lg_n, dense=False, reps=2):
     except hb.Rejected:
         ok = False
     t_verify = time.perf_counter() - t
-    print(f"n=2^{lg_n} {'all gates' if dense else 'mul circuit'}: prove {best * 1e3:.1f} ms  verify {t_verify * 1e3:.1f} ms "
+    circuit.make_resident(polys)
+    best_res = 1e9
+    for r in range(reps):
+        t = time.perf_counter(); pi = hb.plonk.PlonkProof.naive_prover(circuit, pub, wit); best_res = min(best_res, time.perf_counter() - t)
+    circuit.release()
+    print(f"n=2^{lg_n} {'all gates' if dense else 'mul circuit'}: prove {best * 1e3:.1f} ms ({best_res * 1e3:.1f} ms with the circuit resident)  verify {t_verify * 1e3:.1f} ms "
           f"(accepted={ok})  [circuit build {t_build:.1f} s, selector commits {t_setup * 1e3:.0f} ms]", flush=True)
     return best, t_verify
 
