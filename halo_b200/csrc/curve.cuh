@@ -85,6 +85,16 @@ template <int CID> HD XYZZ<CID> xyzz_dbl(const XYZZ<CID>& p) {
     return r;
 }
 
+// The doubling cases of the addition formulas (P + P) are rare; as out-of-line calls they stay out of the hot loops'
+// instruction stream (an inlined doubling is ~40 KB of code at every addition site).
+#if defined(__CUDACC__)
+#define HALO_COLD __host__ __device__ __noinline__
+#else
+#define HALO_COLD __attribute__((noinline))
+#endif
+template <int CID> HALO_COLD XYZZ<CID> xyzz_dbl_affine_cold(Affine<CID> a) { return xyzz_dbl_affine<CID>(a); }
+template <int CID> HALO_COLD XYZZ<CID> xyzz_dbl_cold(XYZZ<CID> p) { return xyzz_dbl<CID>(p); }
+
 // acc += (negate ? -a : a)   (mixed addition, 8M + 2S on the common path)
 template <int CID> HD void xyzz_madd(XYZZ<CID>& acc, const Affine<CID>& a_in, bool negate) {
     constexpr int B = HALO_BF;
@@ -97,7 +107,7 @@ template <int CID> HD void xyzz_madd(XYZZ<CID>& acc, const Affine<CID>& a_in, bo
     Fe<B> P = fe_sub<B>(U2, acc.X);
     Fe<B> R = fe_sub<B>(S2, acc.Y);
     if (fe_is_zero<B>(P)) {
-        if (fe_is_zero<B>(R)) acc = xyzz_dbl_affine<CID>(a);
+        if (fe_is_zero<B>(R)) acc = xyzz_dbl_affine_cold<CID>(a);
         else acc = xyzz_identity<CID>();
         return;
     }
@@ -123,7 +133,7 @@ template <int CID> HD void xyzz_add(XYZZ<CID>& acc, const XYZZ<CID>& o) {
     Fe<B> P = fe_sub<B>(U2, U1);
     Fe<B> R = fe_sub<B>(S2, S1);
     if (fe_is_zero<B>(P)) {
-        if (fe_is_zero<B>(R)) acc = xyzz_dbl<CID>(acc);
+        if (fe_is_zero<B>(R)) acc = xyzz_dbl_cold<CID>(acc);
         else acc = xyzz_identity<CID>();
         return;
     }

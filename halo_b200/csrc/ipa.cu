@@ -177,31 +177,45 @@ __global__ void __launch_bounds__(128, 4) ipa_fold_glv_kernel(const Affine<C>* _
 // shares its 128 doublings between the three scalars and produces n/4 instead of n/2 + n/4 points: ~40 % fewer
 // field multiplications per input generator than two radix-2 folds.  NS = 1 is the single delayed fold.
 struct JointScalars { GlvScalar s[3]; int nbits; };
+// The 3*NS operand coordinates (x, y, beta*x of each input) live in shared memory, one 16-byte lane per thread and
+// half-element, so that the ladder itself fits 128 registers and four CTAs share an SM (16 warps instead of 12).
+template <int F> __device__ __forceinline__ void s_put(uint4* sm, int slot, const Fe<F>& v) {
+    sm[(2 * slot) * 128 + threadIdx.x] = make_uint4(v.l[0], v.l[1], v.l[2], v.l[3]);
+    sm[(2 * slot + 1) * 128 + threadIdx.x] = make_uint4(v.l[4], v.l[5], v.l[6], v.l[7]);
+}
+template <int F> __device__ __forceinline__ Fe<F> s_get(const uint4* sm, int slot) {
+    const uint4 a = sm[(2 * slot) * 128 + threadIdx.x], b = sm[(2 * slot + 1) * 128 + threadIdx.x];
+    Fe<F> r;
+    r.l[0] = a.x; r.l[1] = a.y; r.l[2] = a.z; r.l[3] = a.w; r.l[4] = b.x; r.l[5] = b.y; r.l[6] = b.z; r.l[7] = b.w;
+    return r;
+}
 template <int C, int NS>
-__global__ void __launch_bounds__(128, 3) ipa_materialize_kernel(const Affine<C>* __restrict__ Bs, size_t L, JointScalars js,
+__global__ void __launch_bounds__(128, 4) ipa_materialize_kernel(const Affine<C>* __restrict__ Bs, size_t L, JointScalars js,
                                                                  Fe<CurveTraits<C>::BASE> beta, XYZZ<C>* __restrict__ out) {
     constexpr int B = CurveTraits<C>::BASE;
+    extern __shared__ uint4 joint_sm[];                  // [3*NS slots][2 halves][128 threads]
     size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= L) return;
-    Affine<C> P[NS];
-    Fe<B> x2[NS];
 #pragma unroll
     for (int t = 0; t < NS; ++t) {
-        P[t].x = g_ld(&Bs[i + (size_t)(t + 1) * L].x); P[t].y = g_ld(&Bs[i + (size_t)(t + 1) * L].y);
-        x2[t] = fe_mul<B>(P[t].x, beta);
+        const Fe<B> x = g_ld(&Bs[i + (size_t)(t + 1) * L].x), y = g_ld(&Bs[i + (size_t)(t + 1) * L].y);
+        s_put<B>(joint_sm, 3 * t, x); s_put<B>(joint_sm, 3 * t + 1, y); s_put<B>(joint_sm, 3 * t + 2, fe_mul<B>(x, beta));
     }
+    // ONE addition site in the loop body: with the six digit streams unrolled the body is ~70 inlined field
+    // multiplications (> 300 KB of code) and the ladder runs out of the instruction cache
     XYZZ<C> acc = xyzz_identity<C>();
     for (int b = js.nbits - 1; b >= 0; --b) {
         acc = xyzz_dbl<C>(acc);
         const u32 w = (u32)b >> 5, sh = (u32)b & 31;
-#pragma unroll
-        for (int t = 0; t < NS; ++t) {
-            const GlvScalar& g = js.s[t];
-            if (((g.p1[w] | g.n1[w]) >> sh) & 1u) xyzz_madd<C>(acc, P[t], (((g.n1[w] >> sh) & 1u) != 0) != (g.neg1 != 0));
-            if (((g.p2[w] | g.n2[w]) >> sh) & 1u) {
-                Affine<C> Q; Q.x = x2[t]; Q.y = P[t].y;
-                if (fe_is_zero<B>(P[t].x)) Q.y = P[t].y;            // (0,0) stays the identity: x2 = 0 too
-                xyzz_madd<C>(acc, Q, (((g.n2[w] >> sh) & 1u) != 0) != (g.neg2 != 0));
+#pragma unroll 1
+        for (int k = 0; k < 2 * NS; ++k) {
+            const GlvScalar& g = js.s[k >> 1];
+            const bool second = (k & 1) != 0;            // the phi(P) half: (beta*x, y); (0,0) stays the identity
+            const u32 pos = ((second ? g.p2[w] : g.p1[w]) >> sh) & 1u, neg = ((second ? g.n2[w] : g.n1[w]) >> sh) & 1u;
+            if (pos | neg) {
+                Affine<C> Q;
+                Q.x = s_get<B>(joint_sm, 3 * (k >> 1) + (second ? 2 : 0)); Q.y = s_get<B>(joint_sm, 3 * (k >> 1) + 1);
+                xyzz_madd<C>(acc, Q, (neg != 0) != ((second ? g.neg2 : g.neg1) != 0));
             }
         }
     }
@@ -678,7 +692,7 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
             XYZZ<C>* folded;
             if (int e = ws_get(WS_IPA_T1, m * sizeof(XYZZ<C>), (void**)&folded)) return e;
             Fe<H::B> beta; memcpy(&beta, glv_data::GLV_BETA[C], 32);
-            ipa_materialize_kernel<C, 3><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(gs, m, js, beta, folded);
+            ipa_materialize_kernel<C, 3><<<(unsigned)((m + 127) / 128), 128, 9 * 2 * 128 * sizeof(uint4), st>>>(gs, m, js, beta, folded);
             if (m >= 8192) xyzz_batch_affine_kernel<C, 8><<<(unsigned)((m / 8 + 128) / 128), 128, 0, st>>>(folded, m, gs);
             else xyzz_batch_affine_kernel<C, 1><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(folded, m, gs);
             R.launches += 3;
