@@ -154,17 +154,41 @@ __global__ void __launch_bounds__(128) ntt_twiddle_kernel(Fe<F>* __restrict__ T,
     for (size_t k = lo; k < hi; ++k) { st_fe(T + k, w); w = fe_mul<F>(w, omega); }
 }
 
-// x[i] *= c0 * g^i  (coset pre-scaling for the forward transform, post-scaling g^-i * N^-1 for the inverse)
+// Coset scaling x[j][k] *= c0 * g^k for every vector j of a batch (pre-scaling of the forward coset transform;
+// g^-k * N^-1 after the inverse).  g^k = lo[k & 1023] * hi[k >> 10] from two small tables (lo carries c0), one thread
+// per k so that every access is coalesced and the power is shared by the whole batch: 1 + 1/batch multiplications
+// per element.
 template <int F>
-__global__ void __launch_bounds__(128) ntt_geometric_scale_kernel(Fe<F>* __restrict__ data, size_t N, Fe<F> g, Fe<F> c0) {
-    size_t c = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    size_t lo = c * 16;
-    if (lo >= N) return;
-    Fe<F>* x = data + (size_t)blockIdx.y * N;
-    u32 e[8] = {(u32)lo, (u32)(lo >> 32), 0, 0, 0, 0, 0, 0};
-    Fe<F> w = fe_mul<F>(fe_pow<F>(g, e, 40), c0);
-    size_t hi = lo + 16 < N ? lo + 16 : N;
-    for (size_t k = lo; k < hi; ++k) { st_fe(x + k, fe_mul<F>(ld_fe(x + k), w)); w = fe_mul<F>(w, g); }
+__global__ void __launch_bounds__(128) ntt_power_table_kernel(Fe<F>* __restrict__ tab, size_t n, Fe<F> x, Fe<F> c0) {
+    size_t lo = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) * 16;
+    if (lo >= n) return;
+    Fe<F> cur = c0, b = x;
+    for (size_t e = lo; e; e >>= 1) { if (e & 1) cur = fe_mul<F>(cur, b); b = fe_sqr<F>(b); }
+    for (size_t k = lo; k < lo + 16 && k < n; ++k) { st_fe(tab + k, cur); cur = fe_mul<F>(cur, x); }
+}
+template <int F>
+__global__ void __launch_bounds__(256) ntt_coset_scale_kernel(Fe<F>* __restrict__ data, size_t N, size_t batch,
+                                                              const Fe<F>* __restrict__ lo, const Fe<F>* __restrict__ hi) {
+    size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (k >= N) return;
+    Fe<F> w = ld_fe(lo + (k & 1023));
+    if (k >> 10) w = fe_mul<F>(w, ld_fe(hi + (k >> 10)));
+    for (size_t j = 0; j < batch; ++j) { Fe<F>* x = data + j * N + k; st_fe(x, fe_mul<F>(ld_fe(x), w)); }
+}
+template <int F>
+static int coset_scale(Fe<F>* data, size_t N, size_t batch, const Fe<F>& g, const Fe<F>& c0) {
+    Runtime& R = rt();
+    cudaStream_t st = R.stream;
+    Fe<F>* tab;
+    const size_t nhi = (N + 1023) / 1024;
+    if (int e = ws_get(WS_NTT_TAB, (1024 + nhi) * sizeof(Fe<F>), (void**)&tab)) return e;
+    Fe<F> g1024 = g;
+    for (int i = 0; i < 10; ++i) g1024 = fe_sqr<F>(g1024);
+    ntt_power_table_kernel<F><<<1, 128, 0, st>>>(tab, 1024, g, c0);
+    ntt_power_table_kernel<F><<<(unsigned)((nhi / 16 + 128) / 128), 128, 0, st>>>(tab + 1024, nhi, g1024, fe_one<F>());
+    ntt_coset_scale_kernel<F><<<(unsigned)((N + 255) / 256), 256, 0, st>>>(data, N, batch, tab, tab + 1024);
+    R.launches += 3;
+    return HALO_OK;
 }
 
 // out[i] = sum_k coeffs[i + k*N] for i < N (zero-padded when len < N): what evaluate_over_domain_by_ref does with a
@@ -232,9 +256,7 @@ int ntt_device(Fe<F>* data, Fe<F>* out, int log_n, size_t batch, bool inverse, c
     if (int e = prof_begin()) return e;
     const Fe<F>* tw = (const Fe<F>*)R.ntt_tw[F];
     if (coset && !inverse) {
-        dim3 grid((unsigned)((N / 16 + 127) / 128 + 1), (unsigned)batch);
-        ntt_geometric_scale_kernel<F><<<grid, 128, 0, st>>>(data, N, *coset, fe_one<F>());
-        R.launches += 1;
+        if (int e = coset_scale<F>(data, N, batch, *coset, fe_one<F>())) return e;
         prof_mark("coset");
     }
     Fe<F> ninv = fe_inv<F>(fe_from_u64<F>((u64)N));
@@ -263,9 +285,7 @@ int ntt_device(Fe<F>* data, Fe<F>* out, int log_n, size_t batch, bool inverse, c
         prof_mark("last_pass");
     }
     if (coset && inverse) {
-        dim3 grid((unsigned)((N / 16 + 127) / 128 + 1), (unsigned)batch);
-        ntt_geometric_scale_kernel<F><<<grid, 128, 0, st>>>(out, N, fe_inv<F>(*coset), ninv);
-        R.launches += 1;
+        if (int e = coset_scale<F>(out, N, batch, fe_inv<F>(*coset), ninv)) return e;
         prof_mark("coset");
     }
     HALO_CUDA(cudaGetLastError());
