@@ -424,6 +424,71 @@ int halo_pp_load(int curve, const uint64_t* gs_xy, size_t n, const uint64_t s_xy
     memcpy(P.s_xy, s_xy, 64); memcpy(P.h_xy, h_xy, 64);
     return HALO_OK;
 }
+// ---- the reference's parameter blobs (crates/group/.precompute/<curve>/gs-NN.bin, sh.bin):
+// bincode 2 `standard()` = varint integers: a byte < 251 is the value, 251 / 252 / 253 introduce a u16 / u32 / u64 LE.
+// gs-NN.bin is a Vec<WrappedPoint>: a length, then per point the eight u64 limbs x[0..4], y[0..4] (Montgomery);
+// sh.bin is the tuple (S, H) without a length.
+static bool read_varint(const uint8_t* b, size_t len, size_t& pos, uint64_t& v) {
+    if (pos >= len) return false;
+    const uint8_t t = b[pos++];
+    if (t < 251) { v = t; return true; }
+    const size_t w = t == 251 ? 2 : t == 252 ? 4 : t == 253 ? 8 : 0;
+    if (!w || pos + w > len) return false;
+    v = 0;
+    for (size_t i = 0; i < w; ++i) v |= (uint64_t)b[pos + i] << (8 * i);
+    pos += w;
+    return true;
+}
+int halo_pp_decode_block(const uint8_t* bytes, size_t len, int with_length, size_t max_points, uint64_t* out_xy,
+                         size_t* n_points) {
+    HALO_CHECK(bytes && out_xy && n_points, HALO_EINVAL, "pp_decode_block: null argument");
+    size_t pos = 0;
+    uint64_t count = max_points;
+    if (with_length) HALO_CHECK(read_varint(bytes, len, pos, count), HALO_EINVAL, "pp_decode_block: truncated length");
+    const size_t take = (size_t)std::min<uint64_t>(count, max_points);           // .into_iter().take(m), pp.rs:41
+    for (size_t i = 0; i < take; ++i)
+        for (int l = 0; l < 8; ++l)
+            HALO_CHECK(read_varint(bytes, len, pos, out_xy[8 * i + l]), HALO_EINVAL, "pp_decode_block: truncated or malformed point");
+    *n_points = take;
+    return HALO_OK;
+}
+// PublicParams::new(n) (crates/group/src/pp.rs:26-61): the first n generators of the blocks, S and H from sh.bin,
+// then resident exactly as halo_pp_load makes them (on-curve check on the device, pp.rs:27-32 / wrappers.rs:603-616)
+int halo_pp_load_blobs(int curve, const uint8_t* const* blocks, const size_t* block_lens, size_t n_blocks,
+                       const uint8_t* sh, size_t sh_len, size_t n) {
+    HALO_CHECK(blocks && block_lens && sh && n_blocks > 0, HALO_EINVAL, "pp_load_blobs: null argument");
+    HALO_CHECK(n > 0 && (n & (n - 1)) == 0, HALO_EINVAL, "pp_load_blobs: n must be a power of two (pp.rs:30)");
+    // every block's length prefix first, so that the blocks decode in parallel into their final positions
+    std::vector<size_t> first(n_blocks + 1, 0), take(n_blocks, 0);
+    for (size_t i = 0; i < n_blocks && first[i] < n; ++i) {
+        size_t pos = 0; uint64_t cnt = 0;
+        HALO_CHECK(blocks[i] && read_varint(blocks[i], block_lens[i], pos, cnt), HALO_EINVAL, "pp_load_blobs: failed to decode a block");
+        take[i] = (size_t)std::min<uint64_t>(cnt, n - first[i]);
+        first[i + 1] = first[i] + take[i];
+        for (size_t j = i + 2; j <= n_blocks; ++j) first[j] = first[i + 1];
+    }
+    HALO_CHECK(first[n_blocks] == n, HALO_EPARAMS, "pp_load_blobs: the blocks hold fewer than n generators (pp.rs:31)");
+    std::vector<uint64_t> gs(n * 8);
+    std::vector<int> status(n_blocks, HALO_OK);
+    {
+        const unsigned nt = std::max(1u, std::min<unsigned>(std::thread::hardware_concurrency(), (unsigned)n_blocks));
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < nt; ++t)
+            th.emplace_back([&, t]() {
+                for (size_t i = t; i < n_blocks; i += nt) {
+                    if (!take[i]) continue;
+                    size_t got = 0;
+                    status[i] = halo_pp_decode_block(blocks[i], block_lens[i], 1, take[i], gs.data() + 8 * first[i], &got);
+                    if (status[i] == HALO_OK && got != take[i]) status[i] = HALO_EINVAL;
+                }
+            });
+        for (auto& x : th) x.join();
+    }
+    for (size_t i = 0; i < n_blocks; ++i) HALO_CHECK(status[i] == HALO_OK, HALO_EINVAL, "pp_load_blobs: failed to decode a block");
+    uint64_t shw[16]; size_t two = 0;
+    if (int e = halo_pp_decode_block(sh, sh_len, 0, 2, shw, &two)) return e;
+    return halo_pp_load(curve, gs.data(), n, shw, shw + 8);
+}
 size_t halo_pp_len(int curve) { return (curve == 0 || curve == 1) ? rt().pp[curve].n : 0; }
 int halo_pp_reset(int curve) {
     LOCK(); NEED_INIT();

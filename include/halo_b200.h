@@ -46,6 +46,17 @@ int halo_device_synchronize(void);
  * be on the curve (wrappers.rs:606); failure -> HALO_EINVAL. */
 int halo_pp_load(int curve, const uint64_t* gs_xy, size_t n, const uint64_t s_xy[8], const uint64_t h_xy[8]);
 /* number of resident generators (0 = none) */
+/* The reference's own parameter files (crates/group/.precompute/<curve>/gs-NN.bin and sh.bin, bincode 2 `standard()`
+ * varint encoding of Vec<WrappedPoint> / (WrappedPoint, WrappedPoint); crates/group/src/pp.rs:36-53).
+ * halo_pp_decode_block decodes one file on the host (with_length = 1 for gs-NN.bin, 0 for sh.bin with max_points = 2)
+ * into x,y limb octets, taking at most max_points as `.take(m)` does; no device needed.
+ * halo_pp_load_blobs ≙ PublicParams::new(n) (pp.rs:26-61): the first n generators of the blocks in order plus S, H,
+ * made resident like halo_pp_load (same on-curve check, same idempotent / monotone behaviour).
+ * HALO_EINVAL on a malformed block (the reference panics), HALO_EPARAMS when the blocks hold fewer than n points. */
+int halo_pp_decode_block(const uint8_t* bytes, size_t len, int with_length, size_t max_points, uint64_t* out_xy,
+                         size_t* n_points);
+int halo_pp_load_blobs(int curve, const uint8_t* const* blocks, const size_t* block_lens, size_t n_blocks,
+                       const uint8_t* sh, size_t sh_len, size_t n);
 size_t halo_pp_len(int curve);
 /* drop the resident set (tests only; the reference's OnceLock cannot be reset) */
 int halo_pp_reset(int curve);
