@@ -458,15 +458,23 @@ def run_halo(args, rank, world, local_rank):
         circuit = halo_b200.plonk.PlonkCircuit.from_polys(PALLAS, polys, 0)
         pub = halo_b200.plonk.PlonkPublicInputs(np.zeros((0, 4), dtype=np.uint64), acc0)
         wit = halo_b200.plonk.PlonkWitness(polys, w_evals)
-        best = None
-        for _ in range(2):
-            dist.barrier(); torch.cuda.synchronize()
-            t = time.perf_counter(); pi = halo_b200.plonk.PlonkProof.naive_prover(circuit, pub, wit); dt = time.perf_counter() - t
-            tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            best = float(tt.item()) if best is None else min(best, float(tt.item()))
-        pi.verify(circuit, pub)
-        replicas = {"ms": best * 1e3, "proofs_per_s": world / best, "note": "one independent proof per GPU, max over ranks"}
+        def timed_proofs():
+            best = None
+            for _ in range(2):
+                dist.barrier(); torch.cuda.synchronize()
+                t = time.perf_counter(); pi = halo_b200.plonk.PlonkProof.naive_prover(circuit, pub, wit); dt = time.perf_counter() - t
+                tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                best = float(tt.item()) if best is None else min(best, float(tt.item()))
+            pi.verify(circuit, pub)
+            return best
+        best = timed_proofs()
+        circuit.make_resident(polys)                        # the circuit's own columns stay in HBM; witness-only upload
+        best_res = timed_proofs()
+        circuit.release()
+        replicas = {"ms": best * 1e3, "proofs_per_s": world / best, "ms_circuit_resident": best_res * 1e3,
+                    "proofs_per_s_circuit_resident": world / best_res,
+                    "note": "one independent proof per GPU, max over ranks"}
         halo_b200.pp.reset(PALLAS)
 
     if rank != 0:
