@@ -203,8 +203,11 @@ def measure_path(lib, check, halo_b200, torch, stream, d_pts, h_sc, log_n):
         f = lambda: check(lib.halo_ntt_dev(0, ctypes.c_void_p(x.data_ptr()), ctypes.c_uint(log_n), ctypes.c_size_t(b), 0, None))
         f()
         ms = ev_ms(f)
+        passes = 1 + max(0, -(-(log_n - 11) // 9))           # ntt.cu: a last pass of <= 11 stages + passes of <= 9
         out[f"ntt_2^{log_n}_x{b}"] = {"ms": ms, "elements_per_s": b * n / (ms * 1e-3),
-                                      "gbutterfly_per_s": b * n * log_n / 2 / (ms * 1e-3) / 1e9}
+                                      "gbutterfly_per_s": b * n * log_n / 2 / (ms * 1e-3) / 1e9,
+                                      "passes": passes,
+                                      "hbm_gb_per_s": 64.0 * b * n * passes / (ms * 1e-3) / 1e9}   # 64 B per element and pass
         del x
     # the points of the MSM benchmark double as generators; S and H are two more of them
     gs = d_pts.cpu().numpy().view(np.uint64)
