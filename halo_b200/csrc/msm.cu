@@ -21,6 +21,8 @@
 //                      plain sum and a weighted sum up one level; only additions and a few doublings)
 //   8. host            Horner over the nwin window sums of each MSM (255 doublings; a single GPU thread would
 //                      take longer than the 2 KB D2H copy)
+// MSMs of at most 2^13 points skip all of this for ONE launch (msm_small_kernel, further down) unless their
+// scalars are badly skewed.
 #include "runtime.cuh"
 #include <algorithm>
 #include <thread>
@@ -649,6 +651,7 @@ static int msm_small(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR>*
     u32* d_flag = (u32*)buf;
     XYZZ<C>* d_out = (XYZZ<C>*)(buf + 256);
     if (int e = prof_begin()) return e;
+    if (R.wait_copy) { HALO_CUDA(cudaStreamWaitEvent(st, R.copy_done, 0)); R.wait_copy = false; }   // bases uploaded on copy_stream
     HALO_CUDA(cudaMemsetAsync(d_flag, 0, 4, st));
     msm_small_kernel<C><<<(unsigned)ncta, SMALL_T, smem, st>>>(d_bases, d_scalars, (u32)k, base_stride, split, chunk, max_bucket,
                                                               d_out, d_flag);
