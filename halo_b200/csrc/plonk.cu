@@ -157,7 +157,7 @@ template <int F, class V> HD Fe<F> f_gc_point(const V& v, const Fe<F>* M, unsign
 // ---------------------------------------------------------------------------------------------------------
 // kernels
 // ---------------------------------------------------------------------------------------------------------
-template <int F> struct Challenges { Fe<F> beta, gamma, alpha, alpha2, M[9]; };
+template <int F> struct Challenges { Fe<F> beta, gamma, alpha, alpha2, M[9], id_step_beta; };
 
 // Columns that are the zero polynomial (unused selectors, witness and round-constant columns of a circuit) are not
 // transformed at all: slot[c] is the position of column c among the transformed ones, and every zero column reads
@@ -186,15 +186,21 @@ __global__ void __launch_bounds__(128) plonk_numerator_kernel(const Fe<F>* __res
     ColView<F> v{ev, n, j, j + 1 == n ? 0 : j + 1, map};
     Fe<F> f = f_gc_point<F, ColView<F>>(v, ch.M, gate_mask);
     // f' and g' (protocol.rs:132-139)
+    // id_step != 0: the identity columns differ by a constant (id_i = id_0 + i * id_step, the reference's
+    // SlotId::to_scalar numbering), so only id_0 was transformed and beta * id_i is a running sum
     Fe<F> fp = fe_one<F>(), gp = fe_one<F>();
+    const bool ids_derived = !fe_is_zero<F>(ch.id_step_beta);
+    Fe<F> idb = fe_mul<F>(v.col(COL_ID), ch.beta);
     for (int i = 0; i < NS; ++i) {
         Fe<F> wg = fe_add<F>(v.w(i), ch.gamma);
-        fp = fe_mul<F>(fp, fe_add<F>(wg, fe_mul<F>(v.col(COL_ID + i), ch.beta)));
+        if (i) idb = ids_derived ? fe_add<F>(idb, ch.id_step_beta) : fe_mul<F>(v.col(COL_ID + i), ch.beta);
+        fp = fe_mul<F>(fp, fe_add<F>(wg, idb));
         gp = fe_mul<F>(gp, fe_add<F>(wg, fe_mul<F>(v.col(COL_SIG + i), ch.beta)));
     }
     Fe<F> z = v.col(COL_Z);
+    Fe<F> zw = p_ld<F>(ev + (size_t)map.slot[COL_Z] * n + v.jn);      // z_omega(x) = z(omega x): the next point of the coset
     Fe<F> cc1 = fe_mul<F>(v.col(COL_L1), fe_sub<F>(z, fe_one<F>()));
-    Fe<F> cc2 = fe_sub<F>(fe_mul<F>(z, fp), fe_mul<F>(v.col(COL_ZW), gp));
+    Fe<F> cc2 = fe_sub<F>(fe_mul<F>(z, fp), fe_mul<F>(zw, gp));
     f = fe_add<F>(f, fe_add<F>(fe_mul<F>(ch.alpha, cc1), fe_mul<F>(ch.alpha2, cc2)));
     if (scaled) f = fe_mul<F>(f, scale);                  // 1 / Z_H on this coset (quotient path)
     p_st<F>(out + coset + (size_t)stride * j, f);
@@ -376,6 +382,22 @@ __global__ void __launch_bounds__(256) plonk_nonzero_kernel(const Fe<F>* __restr
     if (__syncthreads_or(any != 0) && threadIdx.x == 0) atomicOr(flags + blockIdx.y, 1);
 }
 
+// do the identity columns differ by a constant?  flags[0] |= 1 unless id_i - id_0 == i * step (a constant polynomial)
+// for every i = 1..7 (blockIdx.y + 1)
+template <int F>
+__global__ void __launch_bounds__(256) plonk_id_affine_kernel(const Fe<F>* __restrict__ ids, size_t n, Fe<F> step,
+                                                              int* __restrict__ flags) {
+    const int i = blockIdx.y + 1;
+    Fe<F> want = fe_zero<F>();
+    for (int t = 0; t < i; ++t) want = fe_add<F>(want, step);
+    u32 bad = 0;
+    for (size_t k = (size_t)blockIdx.x * 256 + threadIdx.x; k < n; k += (size_t)gridDim.x * 256) {
+        Fe<F> d = fe_sub<F>(p_ld<F>(ids + (size_t)i * n + k), p_ld<F>(ids + k));
+        bad |= k == 0 ? !fe_eq<F>(d, want) : !fe_is_zero<F>(d);
+    }
+    if (__syncthreads_or(bad != 0) && threadIdx.x == 0) atomicOr(flags, 1);
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------
@@ -490,9 +512,18 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     HALO_CUDA(cudaMemsetAsync(d_flags, 0, N_COLS * sizeof(int), st));
     plonk_nonzero_kernel<S><<<dim3(32, N_IN), 256, 0, st>>>(cols, n, d_flags);
     R.launches += 1;
+    // the reference numbers the slots row + (column - 1) * n (SlotId::to_scalar), i.e. id_i = id_0 + i * n as polynomials;
+    // verified here on the caller's columns rather than assumed (d_flags[N_COLS - 1] is free until round 3)
+    const SF id_step = fe_from_u64<S>((u64)n);
+    plonk_id_affine_kernel<S><<<dim3(32, NS - 1), 256, 0, st>>>(col(COL_ID), n, id_step, d_flags + (N_COLS - 1));
+    R.launches += 1;
     int h_flags[N_COLS];
+    int ids_not_affine = 1;
     HALO_CUDA(cudaMemcpyAsync(h_flags, d_flags, N_IN * sizeof(int), cudaMemcpyDeviceToHost, st));
+    HALO_CUDA(cudaMemcpyAsync(&ids_not_affine, d_flags + (N_COLS - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
     HALO_CUDA(cudaStreamSynchronize(st));
+    HALO_CUDA(cudaMemsetAsync(d_flags + (N_COLS - 1), 0, sizeof(int), st));
+    const bool ids_derived = !ids_not_affine && !dense;
     auto nonzero = [&](int c) { return dense || h_flags[c] != 0; };
     // commitments of `count` adjacent columns: one batched MSM per run of nonzero columns
     auto commit_cols = [&](const SF* first, int count, int flag0, uint64_t* o) -> int {
@@ -560,8 +591,15 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     ColMap map, list;
     int nnz = 0;
     memset(&map, 0, sizeof map); memset(&list, 0, sizeof list);
-    for (int c = 0; c < N_EVAL; ++c) if (nonzero(c)) { list.slot[nnz] = (unsigned char)c; map.slot[c] = (unsigned char)nnz; ++nnz; }
-    for (int c = 0; c < N_EVAL; ++c) if (!nonzero(c)) map.slot[c] = (unsigned char)nnz;
+    // z_omega is read from z at the next point of the coset; id_1..7 come from id_0 when they differ by constants
+    auto live = [&](int c) {
+        if (c == COL_ZW) return false;
+        if (ids_derived && c > COL_ID && c < COL_ID + NS) return false;
+        return nonzero(c);
+    };
+    ch.id_step_beta = ids_derived ? fe_mul<S>(id_step, ch.beta) : fe_zero<S>();
+    for (int c = 0; c < N_EVAL; ++c) if (live(c)) { list.slot[nnz] = (unsigned char)c; map.slot[c] = (unsigned char)nnz; ++nnz; }
+    for (int c = 0; c < N_EVAL; ++c) if (!live(c)) map.slot[c] = (unsigned char)nnz;
     if (nnz < N_EVAL) HALO_CUDA(cudaMemsetAsync(ev + (size_t)nnz * n, 0, n * 32, st));
     auto numerator_on_coset = [&](unsigned c, SF* dst, unsigned slot, unsigned stride, const SF* scale) -> int {
         SF g = one;                                        // w16n^c

@@ -161,6 +161,13 @@ def test_zero_columns_and_bad_row_count(hb, oracle, params):
     pi = hb.plonk.PlonkProof.naive_prover(circuit, pub, hb.plonk.PlonkWitness(polys, w_evals))
     exp = O.plonk_prove(curve, lg_n, polys, w_evals, c["public_inputs"], acc0.q.w)
     same_proof(O, curve, lg_n, pi.w, exp)
+    # identity columns that do NOT follow id_i = id_0 + i*n (two of them swapped): the prover must notice and transform
+    # all eight instead of deriving them from id_0; the proof still equals the oracle's on the same columns
+    polys2 = c["polys"].copy()
+    polys2[[42, 43]] = polys2[[43, 42]]
+    pi2 = hb.plonk.PlonkProof.naive_prover(circuit, pub, hb.plonk.PlonkWitness(polys2, c["w_evals"]))
+    exp2 = O.plonk_prove(curve, lg_n, polys2, c["w_evals"], c["public_inputs"], acc0.q.w)
+    same_proof(O, curve, lg_n, pi2.w, exp2)
     with pytest.raises(hb.PreconditionError):
         hb.plonk.PlonkProof.naive_prover(hb.plonk.PlonkCircuit(curve, 3, 0, circuit.C_qs), pub, hb.plonk.PlonkWitness(polys, w_evals))
 
