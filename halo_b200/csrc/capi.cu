@@ -355,7 +355,11 @@ int halo_shutdown(void) {
     cudaStreamSynchronize(R.stream);
     for (auto& b : R.arena) if (b.p) cudaFree(b.p);
     R.arena.clear();
-    for (int c = 0; c < 2; ++c) { if (R.pp[c].d_gs) cudaFree(R.pp[c].d_gs); R.pp[c] = ResidentParams(); }
+    for (int c = 0; c < 2; ++c) {
+        if (R.pp[c].d_gs) cudaFree(R.pp[c].d_gs);
+        if (R.pp[c].d_fold_tab) cudaFree(R.pp[c].d_fold_tab);
+        R.pp[c] = ResidentParams();
+    }
     if (R.pinned) cudaFreeHost(R.pinned);
     R.pinned = nullptr; R.pinned_cap = 0;
     for (int t = 0; t < Runtime::UP_THREADS; ++t) {
@@ -496,6 +500,7 @@ int halo_pp_reset(int curve) {
     Runtime& R = rt();
     HALO_CUDA(cudaStreamSynchronize(R.stream));
     if (R.pp[curve].d_gs) cudaFree(R.pp[curve].d_gs);
+    if (R.pp[curve].d_fold_tab) cudaFree(R.pp[curve].d_fold_tab);
     R.pp[curve] = ResidentParams();
     return HALO_OK;
 }

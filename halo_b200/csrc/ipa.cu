@@ -226,6 +226,59 @@ __global__ void __launch_bounds__(128, 4) ipa_materialize_kernel(const Affine<C>
     g_st(&o->X, acc.X); g_st(&o->Y, acc.Y); g_st(&o->ZZ, acc.ZZ); g_st(&o->ZZZ, acc.ZZZ);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// The FIRST fold of an opening multiplies the upper half of pp.Gs -- fixed points -- by a fresh challenge.  With
+// the table  tab[k][j] = 2^k * Gs[n/2 + j]  (affine, k-major so that a warp reads 32 consecutive points) the product
+// xi * Gs[n/2 + j] = sum over the non-zero NAF digits of k1 and k2 of +-tab[k][j] (phi applied on the fly for k2)
+// needs NO doublings: ~86 mixed additions instead of 128 doublings + ~86 additions.  Because the doublings are gone
+// there is nothing to share between scalars, so this fold is taken at once (radix 2) and the radix-4 pairing starts
+// one round later.  The table (FOLD_ROWS * n/2 points, 4.6 GB at n = 2^20) is built once per parameter set.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int FOLD_ROWS = 136, FOLD_SLICE = 34;
+template <int C>
+__global__ void __launch_bounds__(128) ipa_fold_table_rows_kernel(const Affine<C>* __restrict__ hi, XYZZ<C>* __restrict__ state,
+                                                                  size_t m, int first, int rows, XYZZ<C>* __restrict__ out) {
+    size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (j >= m) return;
+    XYZZ<C> P;
+    if (first) { Affine<C> a; a.x = g_ld(&hi[j].x); a.y = g_ld(&hi[j].y); P = xyzz_from_affine<C>(a); }
+    else { P.X = g_ld(&state[j].X); P.Y = g_ld(&state[j].Y); P.ZZ = g_ld(&state[j].ZZ); P.ZZZ = g_ld(&state[j].ZZZ); }
+    for (int k = 0; k < rows; ++k) {
+        XYZZ<C>* o = out + (size_t)k * m + j;
+        g_st(&o->X, P.X); g_st(&o->Y, P.Y); g_st(&o->ZZ, P.ZZ); g_st(&o->ZZZ, P.ZZZ);
+        P = xyzz_dbl<C>(P);
+    }
+    g_st(&state[j].X, P.X); g_st(&state[j].Y, P.Y); g_st(&state[j].ZZ, P.ZZ); g_st(&state[j].ZZZ, P.ZZZ);
+}
+// out[j] = lo[j] + xi * hi[j] from the table of hi (see above); one addition site, digits scanned from the bottom
+template <int C>
+__global__ void __launch_bounds__(128, 4) ipa_fold_table_kernel(const Affine<C>* __restrict__ lo, const Affine<C>* __restrict__ tab,
+                                                                size_t m, GlvScalar g, Fe<CurveTraits<C>::BASE> beta,
+                                                                XYZZ<C>* __restrict__ out) {
+    constexpr int B = CurveTraits<C>::BASE;
+    size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (j >= m) return;
+    Affine<C> Q0;
+    Q0.x = g_ld(&lo[j].x); Q0.y = g_ld(&lo[j].y);
+    XYZZ<C> acc = xyzz_from_affine<C>(Q0);
+    for (int b = 0; b < g.nbits; ++b) {
+        const u32 w = (u32)b >> 5, sh = (u32)b & 31;
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+            const u32 pos = ((h ? g.p2[w] : g.p1[w]) >> sh) & 1u, neg = ((h ? g.n2[w] : g.n1[w]) >> sh) & 1u;
+            if (pos | neg) {
+                const Affine<C>* t = tab + (size_t)b * m + j;
+                Affine<C> Q;
+                Q.x = g_ld(&t->x); Q.y = g_ld(&t->y);
+                if (h) Q.x = fe_mul<B>(Q.x, beta);            // phi(2^b * P); (0,0) stays the identity
+                xyzz_madd<C>(acc, Q, (neg != 0) != ((h ? g.neg2 : g.neg1) != 0));
+            }
+        }
+    }
+    XYZZ<C>* o = out + j;
+    g_st(&o->X, acc.X); g_st(&o->Y, acc.Y); g_st(&o->ZZ, acc.ZZ); g_st(&o->ZZZ, acc.ZZZ);
+}
+
 // XYZZ -> affine for `m` points, BATCH consecutive points per thread sharing one inversion; identity -> (0,0)
 template <int C, int BATCH>
 __global__ void __launch_bounds__(128) xyzz_batch_affine_kernel(const XYZZ<C>* __restrict__ in, size_t m, Affine<C>* __restrict__ out) {
@@ -523,6 +576,43 @@ int pcdl_commit(const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w,
     return HALO_OK;
 }
 
+// The fold table of Gs[n/2 .. n) for openings of size n, built on first use and kept with the parameter set
+// (halo_pp_reset / halo_shutdown free it).  Rows are produced FOLD_SLICE at a time so that the XYZZ staging buffer
+// stays at a quarter of the table's size; the affine conversion is the batched one the folds use.
+template <int C>
+static int ensure_fold_table(size_t n, const Affine<C>** out) {
+    Runtime& R = rt();
+    cudaStream_t st = R.stream;
+    ResidentParams& P = R.pp[C];
+    *out = nullptr;
+    if (P.d_fold_tab && P.fold_tab_n == n) { *out = (const Affine<C>*)P.d_fold_tab; return HALO_OK; }
+    HALO_CUDA(cudaStreamSynchronize(st));
+    if (P.d_fold_tab) { cudaFree(P.d_fold_tab); P.d_fold_tab = nullptr; P.fold_tab_n = 0; }
+    const size_t m = n / 2;
+    void* tab = nullptr;
+    if (cudaMalloc(&tab, (size_t)FOLD_ROWS * m * sizeof(Affine<C>)) != cudaSuccess) { cudaGetLastError(); return HALO_OK; }   // no room: ladder
+    XYZZ<C>*tmp, *state;
+    if (int e = ws_get(WS_FOLD_TMP, (size_t)FOLD_SLICE * m * sizeof(XYZZ<C>), (void**)&tmp)) { cudaFree(tab); return e; }
+    if (int e = ws_get(WS_FOLD_STATE, m * sizeof(XYZZ<C>), (void**)&state)) { cudaFree(tab); return e; }
+    const Affine<C>* hi = (const Affine<C>*)P.d_gs + m;
+    for (int k0 = 0; k0 < FOLD_ROWS; k0 += FOLD_SLICE) {
+        const size_t cnt = (size_t)FOLD_SLICE * m;
+        ipa_fold_table_rows_kernel<C><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(hi, state, m, k0 == 0, FOLD_SLICE, tmp);
+        Affine<C>* dst = (Affine<C>*)tab + (size_t)k0 * m;
+        if (cnt >= 8192) xyzz_batch_affine_kernel<C, 8><<<(unsigned)((cnt / 8 + 128) / 128), 128, 0, st>>>(tmp, cnt, dst);
+        else xyzz_batch_affine_kernel<C, 1><<<(unsigned)((cnt + 127) / 128), 128, 0, st>>>(tmp, cnt, dst);
+        R.launches += 2;
+    }
+    if (cudaGetLastError() != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
+        cudaFree(tab);
+        last_err() = "fold table: kernel failed";
+        return HALO_ECUDA;
+    }
+    P.d_fold_tab = tab; P.fold_tab_n = n;
+    *out = (const Affine<C>*)tab;
+    return HALO_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // pcdl::open / open_without_eval (pcdl.rs:326-473)
 //   proof layout (u64 words): Ls[12 lg n] Rs[12 lg n] U[12] c[4] hiding[1] C_bar[12] w_prime[4]
@@ -619,6 +709,11 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
     const size_t tail_max = tail_lg < 0 ? 0 : (size_t)1 << tail_lg;
     // radix-4 generator folds above the tail (tuning knob 4 = 1 disables; the literal-ladder knob disables it too)
     const bool radix4 = R.tune[4] != 1 && R.tune[2] != 1;
+    // fixed-base table for the first fold (tuning knob 0: 1 = never, 2 = for every size; by default for openings
+    // over the whole parameter set of at least 2^16 generators, the size a prover keeps using)
+    const Affine<C>* fold_tab = nullptr;
+    if (R.tune[0] != 1 && R.tune[2] != 1 && n >= 4 && n / 2 > tail_max && (R.tune[0] == 2 || (n == R.pp[C].n && n >= ((size_t)1 << 16))))
+        if (int e = ensure_fold_table<C>(n, &fold_tab)) return e;
     bool pending = false;
     SF pend_xi = fe_zero<S>();
     bool tail = false;
@@ -697,6 +792,16 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
             else xyzz_batch_affine_kernel<C, 1><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(folded, m, gs);
             R.launches += 3;
             pending = false;
+        } else if (fold_tab && r == 0 && glv_decompose<C>(xi_next, &gk) && gk.nbits <= FOLD_ROWS) {
+            // the generators are still pp.Gs: xi * Gs[m + j] from the table, no doublings
+            ipa_tail_fold_kernel<S><<<(unsigned)((m + 255) / 256), 256, 0, st>>>(cs, zs, m, nullptr, 0, nullptr, xi_next, xi_inv);
+            XYZZ<C>* folded;
+            if (int e = ws_get(WS_IPA_T1, m * sizeof(XYZZ<C>), (void**)&folded)) return e;
+            Fe<H::B> beta; memcpy(&beta, glv_data::GLV_BETA[C], 32);
+            ipa_fold_table_kernel<C><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(gs, fold_tab, m, gk, beta, folded);
+            if (m >= 8192) xyzz_batch_affine_kernel<C, 8><<<(unsigned)((m / 8 + 128) / 128), 128, 0, st>>>(folded, m, gs);
+            else xyzz_batch_affine_kernel<C, 1><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(folded, m, gs);
+            R.launches += 3;
         } else if (radix4 && m > tail_max && m >= 2) {
             // delay this fold: only the scalar vectors are folded now, the generators wait for the next challenge
             ipa_tail_fold_kernel<S><<<(unsigned)((m + 255) / 256), 256, 0, st>>>(cs, zs, m, nullptr, 0, nullptr, xi_next, xi_inv);

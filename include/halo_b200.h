@@ -78,7 +78,8 @@ int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void*
 /* batched variant over device memory: b scalar vectors of k elements against the same k bases */
 int halo_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k, size_t b,
                        uint64_t* out_xyz);
-/* experiment knobs (0 = default): key 0 = bucket-reduction occupancy variant, key 1 = 1 disables the one-launch path of MSMs with k <= 2^13,
+/* experiment knobs (0 = default): key 0 = fixed-base table for the first IPA generator fold (1 = never, 2 = for every opening size; default: openings
+ * over the whole parameter set of >= 2^16 generators), key 1 = 1 disables the one-launch path of MSMs with k <= 2^13,
  * key 2 = 1 forces the literal 255-bit ladder in the IPA fold instead of the endomorphism split,
  * key 3 = log2 of the vector length below which the IPA stops folding generators (-1 never, 0 default),
  * key 4 = 1 disables the radix-4 (two-at-once) generator folds of the IPA,

@@ -183,3 +183,12 @@ def test_fold_variants_give_the_same_proof(hb, oracle, params, curve):
         finally:
             lib.halo_set_tuning(2, 0); lib.halo_set_tuning(3, 0); lib.halo_set_tuning(4, 0)
         same_instance(O, curve, q.w, exp)
+    # (d) the first fold from the fixed-base table of 2^k * Gs[n/2 + j] (no doublings), followed by ladder folds,
+    # radix-4 pairs or the tail; a second opening of another size rebuilds the table, a third reuses it
+    for tail, no_r4, size in ((-1, 0, n), (-1, 1, n), (5, 0, n), (3, 1, n), (-1, 0, n // 4), (2, 0, n // 4)):
+        lib.halo_set_tuning(0, 2); lib.halo_set_tuning(3, tail); lib.halo_set_tuning(4, no_r4)
+        try:
+            q = hb.pcdl.Instance.open(curve, p[:size], size - 1, z)
+        finally:
+            lib.halo_set_tuning(0, 0); lib.halo_set_tuning(3, 0); lib.halo_set_tuning(4, 0)
+        same_instance(O, curve, q.w, exp if size == n else O.instance_open(curve, p[:size], size - 1, z))
