@@ -232,12 +232,15 @@ __global__ void __launch_bounds__(128, 4) ipa_materialize_kernel(const Affine<C>
 // xi * Gs[n/2 + j] = sum over the non-zero NAF digits of k1 and k2 of +-tab[k][j] (phi applied on the fly for k2)
 // needs NO doublings: ~86 mixed additions instead of 128 doublings + ~86 additions.  Because the doublings are gone
 // there is nothing to share between scalars, so this fold is taken at once (radix 2) and the radix-4 pairing starts
-// one round later.  The table (FOLD_ROWS * n/2 points, 4.6 GB at n = 2^20) is built once per parameter set.
+// one round later.  Width-3 NAF digits (+-1, +-3; a quarter of the positions non-zero) take the triples 3 * 2^k * P
+// from a second set of rows: ~64 additions.  The table (2 * FOLD_ROWS * n/2 points, 9.1 GB at n = 2^20) is built
+// once per parameter set.
 // ---------------------------------------------------------------------------------------------------------
 constexpr int FOLD_ROWS = 136, FOLD_SLICE = 34;
 template <int C>
 __global__ void __launch_bounds__(128) ipa_fold_table_rows_kernel(const Affine<C>* __restrict__ hi, XYZZ<C>* __restrict__ state,
-                                                                  size_t m, int first, int rows, XYZZ<C>* __restrict__ out) {
+                                                                  size_t m, int first, int rows, XYZZ<C>* __restrict__ out,
+                                                                  XYZZ<C>* __restrict__ out3) {
     size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (j >= m) return;
     XYZZ<C> P;
@@ -246,34 +249,38 @@ __global__ void __launch_bounds__(128) ipa_fold_table_rows_kernel(const Affine<C
     for (int k = 0; k < rows; ++k) {
         XYZZ<C>* o = out + (size_t)k * m + j;
         g_st(&o->X, P.X); g_st(&o->Y, P.Y); g_st(&o->ZZ, P.ZZ); g_st(&o->ZZZ, P.ZZZ);
-        P = xyzz_dbl<C>(P);
+        XYZZ<C> D = xyzz_dbl<C>(P);
+        xyzz_add<C>(P, D);                                 // 3 * 2^k * G
+        o = out3 + (size_t)k * m + j;
+        g_st(&o->X, P.X); g_st(&o->Y, P.Y); g_st(&o->ZZ, P.ZZ); g_st(&o->ZZZ, P.ZZZ);
+        P = D;
     }
     g_st(&state[j].X, P.X); g_st(&state[j].Y, P.Y); g_st(&state[j].ZZ, P.ZZ); g_st(&state[j].ZZZ, P.ZZZ);
 }
-// out[j] = lo[j] + xi * hi[j] from the table of hi (see above); one addition site, digits scanned from the bottom
+// out[j] = lo[j] + xi * hi[j] from the table of hi.  The host turns the two half-scalars into a list of additions
+// (width-3 NAF: digits +-1 and +-3, a quarter of the positions non-zero): table row (k, or FOLD_ROWS + k for the
+// triples) | phi << 9 | negate << 10.  One addition site; the next operand is loaded while the current addition runs.
+struct FoldOps { unsigned short op[160]; int n; };
 template <int C>
 __global__ void __launch_bounds__(128, 4) ipa_fold_table_kernel(const Affine<C>* __restrict__ lo, const Affine<C>* __restrict__ tab,
-                                                                size_t m, GlvScalar g, Fe<CurveTraits<C>::BASE> beta,
-                                                                XYZZ<C>* __restrict__ out) {
+                                                                size_t m, const __grid_constant__ FoldOps ops,
+                                                                Fe<CurveTraits<C>::BASE> beta, XYZZ<C>* __restrict__ out) {
     constexpr int B = CurveTraits<C>::BASE;
     size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (j >= m) return;
     Affine<C> Q0;
     Q0.x = g_ld(&lo[j].x); Q0.y = g_ld(&lo[j].y);
     XYZZ<C> acc = xyzz_from_affine<C>(Q0);
-    for (int b = 0; b < g.nbits; ++b) {
-        const u32 w = (u32)b >> 5, sh = (u32)b & 31;
+    Affine<C> Q;
+    if (ops.n) { const Affine<C>* t = tab + (size_t)(ops.op[0] & 0x1ffu) * m + j; Q.x = g_ld(&t->x); Q.y = g_ld(&t->y); }
 #pragma unroll 1
-        for (int h = 0; h < 2; ++h) {
-            const u32 pos = ((h ? g.p2[w] : g.p1[w]) >> sh) & 1u, neg = ((h ? g.n2[w] : g.n1[w]) >> sh) & 1u;
-            if (pos | neg) {
-                const Affine<C>* t = tab + (size_t)b * m + j;
-                Affine<C> Q;
-                Q.x = g_ld(&t->x); Q.y = g_ld(&t->y);
-                if (h) Q.x = fe_mul<B>(Q.x, beta);            // phi(2^b * P); (0,0) stays the identity
-                xyzz_madd<C>(acc, Q, (neg != 0) != ((h ? g.neg2 : g.neg1) != 0));
-            }
-        }
+    for (int i = 0; i < ops.n; ++i) {
+        const u32 op = ops.op[i];
+        Affine<C> Qn;
+        if (i + 1 < ops.n) { const Affine<C>* t = tab + (size_t)(ops.op[i + 1] & 0x1ffu) * m + j; Qn.x = g_ld(&t->x); Qn.y = g_ld(&t->y); }
+        if (op & 0x200u) Q.x = fe_mul<B>(Q.x, beta);          // phi; (0,0) stays the identity
+        xyzz_madd<C>(acc, Q, (op & 0x400u) != 0);
+        Q = Qn;
     }
     XYZZ<C>* o = out + j;
     g_st(&o->X, acc.X); g_st(&o->Y, acc.Y); g_st(&o->ZZ, acc.ZZ); g_st(&o->ZZZ, acc.ZZZ);
@@ -576,6 +583,31 @@ int pcdl_commit(const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w,
     return HALO_OK;
 }
 
+// width-3 NAF of the two half-scalars as a list of table additions; false if a digit falls outside the table
+static void wnaf3_ops(const u32 mag[5], int negative, u32 phi_bit, FoldOps* ops, bool* ok) {
+    u64 k[3] = {(u64)mag[0] | ((u64)mag[1] << 32), (u64)mag[2] | ((u64)mag[3] << 32), (u64)mag[4]};
+    for (int pos = 0; k[0] | k[1] | k[2]; ++pos) {
+        if (k[0] & 1) {
+            int d = (int)(k[0] & 7);                        // odd: 1, 3, 5, 7  ->  1, 3, -3, -1
+            if (d > 4) d -= 8;
+            if (d > 0) { u64 b0 = k[0]; k[0] -= (u64)d; if (k[0] > b0) { if (k[1]-- == 0) --k[2]; } }
+            else { u64 b0 = k[0]; k[0] += (u64)(-d); if (k[0] < b0) { if (++k[1] == 0) ++k[2]; } }
+            if (pos >= FOLD_ROWS || ops->n >= 160) { *ok = false; return; }
+            const u32 row = (u32)pos + ((d == 3 || d == -3) ? (u32)FOLD_ROWS : 0u);
+            const bool neg = (d < 0) != (negative != 0);
+            ops->op[ops->n++] = (unsigned short)(row | phi_bit | (neg ? 0x400u : 0u));
+        }
+        k[0] = (k[0] >> 1) | (k[1] << 63); k[1] = (k[1] >> 1) | (k[2] << 63); k[2] >>= 1;
+    }
+}
+static bool fold_ops_from(const GlvScalar& g, FoldOps* ops) {
+    bool ok = true;
+    ops->n = 0;
+    wnaf3_ops(g.k1, g.neg1, 0u, ops, &ok);
+    if (ok) wnaf3_ops(g.k2, g.neg2, 0x200u, ops, &ok);
+    return ok;
+}
+
 // The fold table of Gs[n/2 .. n) for openings of size n, built on first use and kept with the parameter set
 // (halo_pp_reset / halo_shutdown free it).  Rows are produced FOLD_SLICE at a time so that the XYZZ staging buffer
 // stays at a quarter of the table's size; the affine conversion is the batched one the folds use.
@@ -590,18 +622,21 @@ static int ensure_fold_table(size_t n, const Affine<C>** out) {
     if (P.d_fold_tab) { cudaFree(P.d_fold_tab); P.d_fold_tab = nullptr; P.fold_tab_n = 0; }
     const size_t m = n / 2;
     void* tab = nullptr;
-    if (cudaMalloc(&tab, (size_t)FOLD_ROWS * m * sizeof(Affine<C>)) != cudaSuccess) { cudaGetLastError(); return HALO_OK; }   // no room: ladder
+    if (cudaMalloc(&tab, (size_t)2 * FOLD_ROWS * m * sizeof(Affine<C>)) != cudaSuccess) { cudaGetLastError(); return HALO_OK; }   // no room: ladder
     XYZZ<C>*tmp, *state;
-    if (int e = ws_get(WS_FOLD_TMP, (size_t)FOLD_SLICE * m * sizeof(XYZZ<C>), (void**)&tmp)) { cudaFree(tab); return e; }
+    if (int e = ws_get(WS_FOLD_TMP, (size_t)2 * FOLD_SLICE * m * sizeof(XYZZ<C>), (void**)&tmp)) { cudaFree(tab); return e; }
     if (int e = ws_get(WS_FOLD_STATE, m * sizeof(XYZZ<C>), (void**)&state)) { cudaFree(tab); return e; }
     const Affine<C>* hi = (const Affine<C>*)P.d_gs + m;
     for (int k0 = 0; k0 < FOLD_ROWS; k0 += FOLD_SLICE) {
         const size_t cnt = (size_t)FOLD_SLICE * m;
-        ipa_fold_table_rows_kernel<C><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(hi, state, m, k0 == 0, FOLD_SLICE, tmp);
-        Affine<C>* dst = (Affine<C>*)tab + (size_t)k0 * m;
-        if (cnt >= 8192) xyzz_batch_affine_kernel<C, 8><<<(unsigned)((cnt / 8 + 128) / 128), 128, 0, st>>>(tmp, cnt, dst);
-        else xyzz_batch_affine_kernel<C, 1><<<(unsigned)((cnt + 127) / 128), 128, 0, st>>>(tmp, cnt, dst);
-        R.launches += 2;
+        ipa_fold_table_rows_kernel<C><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(hi, state, m, k0 == 0, FOLD_SLICE, tmp, tmp + cnt);
+        for (int t3 = 0; t3 < 2; ++t3) {                   // rows of 2^k * G, then rows of 3 * 2^k * G
+            Affine<C>* dst = (Affine<C>*)tab + ((size_t)t3 * FOLD_ROWS + k0) * m;
+            const XYZZ<C>* src = tmp + (size_t)t3 * cnt;
+            if (cnt >= 8192) xyzz_batch_affine_kernel<C, 8><<<(unsigned)((cnt / 8 + 128) / 128), 128, 0, st>>>(src, cnt, dst);
+            else xyzz_batch_affine_kernel<C, 1><<<(unsigned)((cnt + 127) / 128), 128, 0, st>>>(src, cnt, dst);
+        }
+        R.launches += 3;
     }
     if (cudaGetLastError() != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
         cudaFree(tab);
@@ -769,6 +804,7 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
         xi = xi_next;
         double t3 = trace ? now() : 0;
         GlvScalar gk;
+        FoldOps fops;
         if (tail) {
             const size_t th = std::max(m, nu);
             ipa_tail_fold_kernel<S><<<(unsigned)((th + 255) / 256), 256, 0, st>>>(cs, zs, m, tail_w + w_cur * T, nu,
@@ -792,13 +828,13 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
             else xyzz_batch_affine_kernel<C, 1><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(folded, m, gs);
             R.launches += 3;
             pending = false;
-        } else if (fold_tab && r == 0 && glv_decompose<C>(xi_next, &gk) && gk.nbits <= FOLD_ROWS) {
+        } else if (fold_tab && r == 0 && glv_decompose<C>(xi_next, &gk) && fold_ops_from(gk, &fops)) {
             // the generators are still pp.Gs: xi * Gs[m + j] from the table, no doublings
             ipa_tail_fold_kernel<S><<<(unsigned)((m + 255) / 256), 256, 0, st>>>(cs, zs, m, nullptr, 0, nullptr, xi_next, xi_inv);
             XYZZ<C>* folded;
             if (int e = ws_get(WS_IPA_T1, m * sizeof(XYZZ<C>), (void**)&folded)) return e;
             Fe<H::B> beta; memcpy(&beta, glv_data::GLV_BETA[C], 32);
-            ipa_fold_table_kernel<C><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(gs, fold_tab, m, gk, beta, folded);
+            ipa_fold_table_kernel<C><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(gs, fold_tab, m, fops, beta, folded);
             if (m >= 8192) xyzz_batch_affine_kernel<C, 8><<<(unsigned)((m / 8 + 128) / 128), 128, 0, st>>>(folded, m, gs);
             else xyzz_batch_affine_kernel<C, 1><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(folded, m, gs);
             R.launches += 3;
