@@ -207,17 +207,23 @@ __global__ void __launch_bounds__(128) plonk_numerator_kernel(const Fe<F>* __res
 }
 
 // numerators and denominators of the grand product on H (protocol.rs:140-141): ev holds w_0..7, id_0..7, sigma_0..7
+// map.slot[i], [NS + i], [2 NS + i]: where w_i, id_i, sigma_i sit among the transformed columns (zero columns share a
+// column of zeros); id_step_beta != 0: only id_0 was transformed, beta * id_i = beta * id_0 + i * id_step_beta
 template <int F>
 __global__ void __launch_bounds__(128) plonk_perm_kernel(const Fe<F>* __restrict__ ev, size_t n, Fe<F> beta, Fe<F> gamma,
-                                                         Fe<F>* __restrict__ num, Fe<F>* __restrict__ den) {
+                                                         Fe<F>* __restrict__ num, Fe<F>* __restrict__ den,
+                                                         Fe<F> id_step_beta, const __grid_constant__ ColMap map) {
     size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (j >= n) return;
     Fe<F> fp = fe_one<F>(), gp = fe_one<F>();
     if (j) {                                              // index 0 is not part of the running product
+        const bool ids_derived = !fe_is_zero<F>(id_step_beta);
+        Fe<F> idb = fe_mul<F>(p_ld<F>(ev + (size_t)map.slot[NS] * n + j), beta);
         for (int i = 0; i < NS; ++i) {
-            Fe<F> wg = fe_add<F>(p_ld<F>(ev + (size_t)i * n + j), gamma);
-            fp = fe_mul<F>(fp, fe_add<F>(wg, fe_mul<F>(p_ld<F>(ev + (size_t)(NS + i) * n + j), beta)));
-            gp = fe_mul<F>(gp, fe_add<F>(wg, fe_mul<F>(p_ld<F>(ev + (size_t)(2 * NS + i) * n + j), beta)));
+            Fe<F> wg = fe_add<F>(p_ld<F>(ev + (size_t)map.slot[i] * n + j), gamma);
+            if (i) idb = ids_derived ? fe_add<F>(idb, id_step_beta) : fe_mul<F>(p_ld<F>(ev + (size_t)map.slot[NS + i] * n + j), beta);
+            fp = fe_mul<F>(fp, fe_add<F>(wg, idb));
+            gp = fe_mul<F>(gp, fe_add<F>(wg, fe_mul<F>(p_ld<F>(ev + (size_t)map.slot[2 * NS + i] * n + j), beta)));
         }
     }
     p_st<F>(num + j, fp);
@@ -526,12 +532,12 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     const bool ids_derived = !ids_not_affine && !dense;
     auto nonzero = [&](int c) { return dense || h_flags[c] != 0; };
     // commitments of `count` adjacent columns: one batched MSM per run of nonzero columns
-    auto commit_cols = [&](const SF* first, int count, int flag0, uint64_t* o) -> int {
+    auto commit_cols = [&](const SF* first, int count, auto&& live, uint64_t* o) -> int {
         const Jac<C> id = xyzz_to_jac<C>(xyzz_identity<C>());
         for (int i = 0; i < count;) {
-            if (flag0 >= 0 && !nonzero(flag0 + i)) { memcpy(o + 12 * i, &id, 96); ++i; continue; }
+            if (!live(i)) { memcpy(o + 12 * i, &id, 96); ++i; continue; }
             int j = i + 1;
-            while (j < count && (flag0 < 0 || nonzero(flag0 + j))) ++j;
+            while (j < count && live(j)) ++j;
             if (int e = msm_device<C>(R.pp[C].d_gs, first + (size_t)i * n, n, (size_t)(j - i), o + 12 * i, 0)) return e;
             i = j;
         }
@@ -549,7 +555,7 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     uint64_t* o_acc = o_piro + evalproof_words(lg_n);
 
     // ---- round 1 (:114-115): the 16 witness commitments as one batched MSM over the resident generators
-    if (int e = commit_cols(col(COL_W), NW, COL_W, o_Cws)) return e;
+    if (int e = commit_cols(col(COL_W), NW, [&](int i) { return nonzero(COL_W + i); }, o_Cws)) return e;
     for (int i = 0; i < NW; ++i) tr.absorb_point(H::from_words(o_Cws + 12 * i));
     lap("round 1 (16 commits)");
 
@@ -557,11 +563,27 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     Challenges<S> ch;
     ch.beta = tr.challenge();
     ch.gamma = tr.challenge();
-    HALO_CUDA(cudaMemcpyAsync(tmp, col(COL_W), (size_t)NS * n * 32, cudaMemcpyDeviceToDevice, st));
-    HALO_CUDA(cudaMemcpyAsync(tmp + (size_t)NS * n, col(COL_ID), (size_t)2 * NS * n * 32, cudaMemcpyDeviceToDevice, st));
-    if (int e = ntt_device<S>(tmp, ev, (int)lg_n, 3 * NS, false, nullptr)) return e;
+    {   // values on H of the live columns among w_0..7, id_0..7, sigma_0..7 (zero columns and derived ids are not transformed)
+        ColMap pm;
+        memset(&pm, 0, sizeof pm);
+        int live3 = 0;
+        const int src_col[3] = {COL_W, COL_ID, COL_SIG};
+        for (int g3 = 0; g3 < 3; ++g3)
+            for (int i = 0; i < NS; ++i) {
+                const int c = src_col[g3] + i;
+                const bool skip = !nonzero(c) || (ids_derived && g3 == 1 && i > 0);
+                if (skip) { pm.slot[g3 * NS + i] = 255; continue; }
+                HALO_CUDA(cudaMemcpyAsync(tmp + (size_t)live3 * n, col(c), n * 32, cudaMemcpyDeviceToDevice, st));
+                pm.slot[g3 * NS + i] = (unsigned char)live3++;
+            }
+        for (int i = 0; i < 3 * NS; ++i) if (pm.slot[i] == 255) pm.slot[i] = (unsigned char)live3;      // the shared zero column
+        if (int e = ntt_device<S>(tmp, ev, (int)lg_n, (size_t)live3, false, nullptr)) return e;
+        if (live3 < 3 * NS) HALO_CUDA(cudaMemsetAsync(ev + (size_t)live3 * n, 0, n * 32, st));
+        SF* num = f0; SF* den = f0 + n;
+        plonk_perm_kernel<S><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(ev, n, ch.beta, ch.gamma, num, den,
+                                                                        ids_derived ? fe_mul<S>(id_step, ch.beta) : fe_zero<S>(), pm);
+    }
     SF* num = f0; SF* den = f0 + n;
-    plonk_perm_kernel<S><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(ev, n, ch.beta, ch.gamma, num, den);
     R.launches += 1;
     if (int e = scan_mul_device<S>(num, n, misc, false)) return e;
     if (int e = scan_mul_device<S>(den, n, misc, true)) return e;
@@ -660,8 +682,15 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
         HALO_CUDA(cudaGetLastError());
     }
     {   // on the 8-coset path deg t < 8n: chunks 8..15 are zero and commit to the identity
+        // and a quotient of low degree (few gates in use) leaves more of them zero: flag the chunks like the columns
         const int nt_live = (!not_divisible && R.tune[5] != 1 && !dense) ? NT / 2 : NT;
-        if (int e = commit_cols(tq, nt_live, -1, o_Cts)) return e;
+        int t_flags[NT];
+        HALO_CUDA(cudaMemsetAsync(d_flags, 0, NT * sizeof(int), st));
+        plonk_nonzero_kernel<S><<<dim3(32, nt_live), 256, 0, st>>>(tq, n, d_flags);
+        R.launches += 1;
+        HALO_CUDA(cudaMemcpyAsync(t_flags, d_flags, nt_live * sizeof(int), cudaMemcpyDeviceToHost, st));
+        HALO_CUDA(cudaStreamSynchronize(st));
+        if (int e = commit_cols(tq, nt_live, [&](int i) { return dense || t_flags[i] != 0; }, o_Cts)) return e;
         const Jac<C> id = xyzz_to_jac<C>(xyzz_identity<C>());
         for (int i = nt_live; i < NT; ++i) memcpy(o_Cts + 12 * i, &id, 96);
     }
