@@ -712,13 +712,14 @@ int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbat
     HALO_CUDA(cudaMemcpyAsync(h, d_win, P.nwt * sizeof(XYZZ<C>), cudaMemcpyDeviceToHost, R.stream));
     HALO_CUDA(cudaStreamSynchronize(R.stream));
     const XYZZ<C>* win = (const XYZZ<C>*)h;
-    if (nbatch < 4) {
-        for (size_t i = 0; i < nbatch; ++i) msm_combine_host<C>(win + i * P.nwin, P, out_xyz + 12 * i);
-    } else {
+    if (nbatch == 1) {
+        msm_combine_host<C>(win, P, out_xyz);
+    } else {                                              // one Horner (255 doublings, ~55 us) per MSM: the calling thread takes a share
         unsigned nt = std::min<size_t>(nbatch, std::max(1u, std::thread::hardware_concurrency()));
+        auto share = [&](unsigned t) { for (size_t i = t; i < nbatch; i += nt) msm_combine_host<C>(win + i * P.nwin, P, out_xyz + 12 * i); };
         std::vector<std::thread> th;
-        for (unsigned t = 0; t < nt; ++t)
-            th.emplace_back([&, t]() { for (size_t i = t; i < nbatch; i += nt) msm_combine_host<C>(win + i * P.nwin, P, out_xyz + 12 * i); });
+        for (unsigned t = 1; t < nt; ++t) th.emplace_back(share, t);
+        share(0);
         for (auto& x : th) x.join();
     }
     return HALO_OK;
