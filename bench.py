@@ -416,7 +416,7 @@ def run_halo(args, rank, world, local_rank):
     result_dev = total.copy()
 
     # ---- end-to-end arm (host buffers) ----
-    for _ in range(2):
+    for _ in range(max(args.warmup, 3)):
         step_e2e()
     e2e_ms, _ = timed(step_e2e, args.steps)
     clocks = sampler.stop() if sampler else None
