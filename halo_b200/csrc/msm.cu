@@ -202,20 +202,37 @@ __global__ void __launch_bounds__(256) msm_task_hist(const u32* __restrict__ cou
     __syncthreads();
     for (int i = threadIdx.x; i <= (int)L; i += blockDim.x) if (sh[i]) atomicAdd(&hist[i], sh[i]);
 }
-// bincur: exclusive scan of hist (in place), used as cursors
+// bincur: exclusive scan of hist (in place), used as cursors.  The L + 1 cursors are hit by every bucket, so the
+// atomics are aggregated per warp: lanes with the same bin elect a leader (match.any), full-length tasks go through a
+// warp prefix sum -- one atomic per (warp, bin) instead of one per bucket.
 __global__ void __launch_bounds__(256) msm_task_emit(const u32* __restrict__ counts, size_t nb, u32 L,
                                                      u32* __restrict__ bincur, uint2* __restrict__ tasks) {
-    for (size_t b = blockIdx.x * (size_t)blockDim.x + threadIdx.x; b < nb; b += (size_t)gridDim.x * blockDim.x) {
-        const u32 cnt = counts[b];
+    const u32 lane = threadIdx.x & 31;
+    for (size_t base = blockIdx.x * (size_t)blockDim.x; base < nb; base += (size_t)gridDim.x * blockDim.x) {
+        const size_t b = base + threadIdx.x;
+        const bool valid = b < nb;
+        const u32 cnt = valid ? counts[b] : 0u;
         const u32 full = cnt / L, rem = cnt - full * L;
-        if (full) {
-            u32 pos = atomicAdd(&bincur[0], full);
-            for (u32 s = 0; s < full; ++s) tasks[pos + s] = make_uint2((u32)b, s);
+        // full-length tasks: bin 0
+        u32 incl = full;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { u32 y = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= (u32)d) incl += y; }
+        const u32 warp_full = __shfl_sync(0xffffffffu, incl, 31);
+        u32 pos0 = 0;
+        if (warp_full) {
+            if (lane == 31) pos0 = atomicAdd(&bincur[0], warp_full);
+            pos0 = __shfl_sync(0xffffffffu, pos0, 31) + incl - full;
+            for (u32 s = 0; s < full; ++s) tasks[pos0 + s] = make_uint2((u32)b, s);
         }
-        if (rem || cnt == 0) {
-            u32 pos = atomicAdd(&bincur[L - rem], 1u);
-            tasks[pos] = make_uint2((u32)b, full);
-        }
+        // the remainder task (or the single empty task of an empty bucket): bin L - rem
+        const bool has = valid && (rem || cnt == 0);
+        const u32 key = has ? L - rem : 0xffffffffu;
+        const u32 peers = __match_any_sync(0xffffffffu, key);
+        const u32 leader = (u32)__ffs((int)peers) - 1u;
+        u32 pos = 0;
+        if (has && lane == leader) pos = atomicAdd(&bincur[key], (u32)__popc(peers));
+        pos = __shfl_sync(0xffffffffu, pos, leader);
+        if (has) tasks[pos + (u32)__popc(peers & ((1u << lane) - 1u))] = make_uint2((u32)b, full);
     }
 }
 
