@@ -4,6 +4,8 @@
 #include <cstring>
 #include <algorithm>
 #include <thread>
+#include <new>
+#include <stdexcept>
 
 namespace halo {
 
@@ -59,10 +61,10 @@ int upload_staged(void* d_dst, const void* h_src, size_t bytes) {
     HALO_CUDA(cudaGetDevice(&dev));
     const size_t nchunks = (bytes + CH - 1) / CH;
     int status[T];
-    std::thread th[T];
-    for (int t = 0; t < T; ++t) {
-        status[t] = 0;
-        th[t] = std::thread([&, t]() {
+    for (int t = 0; t < T; ++t) status[t] = 0;
+    Workers wk;
+    wk.spawn_indexed(0, (unsigned)T, [&](unsigned t) {
+        {
             if (cudaSetDevice(dev) != cudaSuccess || cudaStreamWaitEvent(R.up_stream[t], go, 0) != cudaSuccess) { status[t] = 1; return; }
             int slot = 0;
             for (size_t c = t; c < nchunks; c += T, slot ^= 1) {
@@ -88,9 +90,9 @@ int upload_staged(void* d_dst, const void* h_src, size_t bytes) {
                 if (cudaMemcpyAsync((char*)d_dst + off, R.up_buf[t][slot], len, cudaMemcpyHostToDevice, R.up_stream[t]) != cudaSuccess ||
                     cudaEventRecord(R.up_ev[t][slot], R.up_stream[t]) != cudaSuccess) { status[t] = 1; return; }
             }
-        });
-    }
-    for (int t = 0; t < T; ++t) th[t].join();
+        }
+    });
+    wk.join();
     cudaEventDestroy(go);
     for (int t = 0; t < T; ++t) {
         HALO_CHECK(status[t] == 0, HALO_ECUDA, "staged upload failed");
@@ -120,6 +122,8 @@ template <int C> int msm_device(const void* d_bases, const void* d_scalars, size
 template <int F> int ntt_device(Fe<F>* data, Fe<F>* out, int log_n, size_t batch, bool inverse, const Fe<F>* coset);
 template <int F> int ntt_fold_device(const Fe<F>* coeffs, size_t len, int log_n, Fe<F>* out);
 template <int C> int pcdl_commit(const uint64_t*, size_t, size_t, const uint64_t*, uint64_t*);
+template <int C> int pcdl_chunked_commit(const uint64_t*, size_t, size_t, const uint64_t*, size_t, uint64_t*, size_t*);
+template <int C> int fold_table_build(size_t);
 template <int C> int pcdl_open(const uint64_t*, size_t, const uint64_t*, size_t, const uint64_t*, const uint64_t*, const uint64_t*,
                                const uint64_t*, const uint64_t*, uint64_t*, uint64_t*, bool);
 template <int C> int pcdl_succinct_check(const uint64_t*, uint64_t*, uint64_t*);
@@ -291,6 +295,12 @@ __global__ void bench_pipe_kernel(int mode, int iters, unsigned long long* out) 
 using namespace halo;
 
 #define LOCK() std::lock_guard<std::recursive_mutex> lock__(rt().mu)
+// Nothing may unwind through the C ABI: std::bad_alloc from a host vector or std::system_error from a thread or mutex
+// becomes an error code (the header promises that no entry point aborts the host process).
+#define HALO_API_BEGIN try {
+#define HALO_API_END } catch (const std::bad_alloc&) { halo::last_err() = "out of host memory"; return HALO_EINVAL; } \
+    catch (const std::exception& e__) { halo::last_err() = std::string("exception: ") + e__.what(); return HALO_ECUDA; } \
+    catch (...) { halo::last_err() = "unknown exception"; return HALO_ECUDA; }
 #define NEED_INIT() HALO_CHECK(rt().inited, HALO_ENOINIT, "halo_init has not been called")
 
 extern "C" int halo_msm(int, const uint64_t*, size_t, const uint64_t*, size_t, uint64_t*);
@@ -334,7 +344,7 @@ extern "C" {
 
 const char* halo_last_error(void) { return last_err().c_str(); }
 
-int halo_init(int device) {
+int halo_init(int device) { HALO_API_BEGIN
     LOCK();
     Runtime& R = rt();
     if (R.inited) return HALO_OK;
@@ -351,9 +361,10 @@ int halo_init(int device) {
     R.arena.resize(WS_COUNT);
     R.inited = true;
     return HALO_OK;
+HALO_API_END
 }
 
-int halo_shutdown(void) {
+int halo_shutdown(void) { HALO_API_BEGIN
     LOCK();
     Runtime& R = rt();
     if (!R.inited) return HALO_OK;
@@ -386,22 +397,25 @@ int halo_shutdown(void) {
     R.own_stream = R.stream = nullptr;
     R.inited = false;
     return HALO_OK;
+HALO_API_END
 }
 
-int halo_set_stream(void* s) {
+int halo_set_stream(void* s) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     Runtime& R = rt();
     HALO_CUDA(cudaStreamSynchronize(R.stream));
     R.stream = s ? (cudaStream_t)s : R.own_stream;
     return HALO_OK;
+HALO_API_END
 }
-int halo_device_synchronize(void) {
+int halo_device_synchronize(void) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CUDA(cudaStreamSynchronize(rt().stream));
     return HALO_OK;
+HALO_API_END
 }
 
-int halo_pp_load(int curve, const uint64_t* gs_xy, size_t n, const uint64_t s_xy[8], const uint64_t h_xy[8]) {
+int halo_pp_load(int curve, const uint64_t* gs_xy, size_t n, const uint64_t s_xy[8], const uint64_t h_xy[8]) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
     HALO_CHECK(gs_xy && s_xy && h_xy && n > 0, HALO_EINVAL, "pp_load: null or empty parameters");
@@ -432,6 +446,7 @@ int halo_pp_load(int curve, const uint64_t* gs_xy, size_t n, const uint64_t s_xy
     P.d_gs = d; P.n = n;
     memcpy(P.s_xy, s_xy, 64); memcpy(P.h_xy, h_xy, 64);
     return HALO_OK;
+HALO_API_END
 }
 // ---- the reference's parameter blobs (crates/group/.precompute/<curve>/gs-NN.bin, sh.bin):
 // bincode 2 `standard()` = varint integers: a byte < 251 is the value, 251 / 252 / 253 introduce a u16 / u32 / u64 LE.
@@ -449,7 +464,7 @@ static bool read_varint(const uint8_t* b, size_t len, size_t& pos, uint64_t& v) 
     return true;
 }
 int halo_pp_decode_block(const uint8_t* bytes, size_t len, int with_length, size_t max_points, uint64_t* out_xy,
-                         size_t* n_points) {
+                         size_t* n_points) { HALO_API_BEGIN
     HALO_CHECK(bytes && out_xy && n_points, HALO_EINVAL, "pp_decode_block: null argument");
     size_t pos = 0;
     uint64_t count = max_points;
@@ -460,11 +475,12 @@ int halo_pp_decode_block(const uint8_t* bytes, size_t len, int with_length, size
             HALO_CHECK(read_varint(bytes, len, pos, out_xy[8 * i + l]), HALO_EINVAL, "pp_decode_block: truncated or malformed point");
     *n_points = take;
     return HALO_OK;
+HALO_API_END
 }
 // PublicParams::new(n) (crates/group/src/pp.rs:26-61): the first n generators of the blocks, S and H from sh.bin,
 // then resident exactly as halo_pp_load makes them (on-curve check on the device, pp.rs:27-32 / wrappers.rs:603-616)
 int halo_pp_load_blobs(int curve, const uint8_t* const* blocks, const size_t* block_lens, size_t n_blocks,
-                       const uint8_t* sh, size_t sh_len, size_t n) {
+                       const uint8_t* sh, size_t sh_len, size_t n) { HALO_API_BEGIN
     HALO_CHECK(blocks && block_lens && sh && n_blocks > 0, HALO_EINVAL, "pp_load_blobs: null argument");
     HALO_CHECK(n > 0 && (n & (n - 1)) == 0, HALO_EINVAL, "pp_load_blobs: n must be a power of two (pp.rs:30)");
     // every block's length prefix first, so that the blocks decode in parallel into their final positions
@@ -481,25 +497,27 @@ int halo_pp_load_blobs(int curve, const uint8_t* const* blocks, const size_t* bl
     std::vector<int> status(n_blocks, HALO_OK);
     {
         const unsigned nt = std::max(1u, std::min<unsigned>(std::thread::hardware_concurrency(), (unsigned)n_blocks));
-        std::vector<std::thread> th;
-        for (unsigned t = 0; t < nt; ++t)
-            th.emplace_back([&, t]() {
-                for (size_t i = t; i < n_blocks; i += nt) {
-                    if (!take[i]) continue;
-                    size_t got = 0;
-                    status[i] = halo_pp_decode_block(blocks[i], block_lens[i], 1, take[i], gs.data() + 8 * first[i], &got);
-                    if (status[i] == HALO_OK && got != take[i]) status[i] = HALO_EINVAL;
-                }
-            });
-        for (auto& x : th) x.join();
+        Workers wk;
+        wk.spawn_indexed(0, nt, [&](unsigned t) {
+            for (size_t i = t; i < n_blocks; i += nt) {
+                if (!take[i]) continue;
+                size_t got = 0;
+                status[i] = halo_pp_decode_block(blocks[i], block_lens[i], 1, take[i], gs.data() + 8 * first[i], &got);
+                if (status[i] == HALO_OK && got != take[i]) status[i] = HALO_EINVAL;
+            }
+        });
+        wk.join();
     }
     for (size_t i = 0; i < n_blocks; ++i) HALO_CHECK(status[i] == HALO_OK, HALO_EINVAL, "pp_load_blobs: failed to decode a block");
     uint64_t shw[16]; size_t two = 0;
     if (int e = halo_pp_decode_block(sh, sh_len, 0, 2, shw, &two)) return e;
     return halo_pp_load(curve, gs.data(), n, shw, shw + 8);
+HALO_API_END
 }
-size_t halo_pp_len(int curve) { return (curve == 0 || curve == 1) ? rt().pp[curve].n : 0; }
-int halo_pp_reset(int curve) {
+size_t halo_pp_len(int curve) {
+    try { LOCK(); return (curve == 0 || curve == 1) ? rt().pp[curve].n : 0; } catch (...) { return 0; }
+}
+int halo_pp_reset(int curve) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
     Runtime& R = rt();
@@ -508,10 +526,11 @@ int halo_pp_reset(int curve) {
     if (R.pp[curve].d_fold_tab) cudaFree(R.pp[curve].d_fold_tab);
     R.pp[curve] = ResidentParams();
     return HALO_OK;
+HALO_API_END
 }
 
-int halo_profile_enable(int on) { LOCK(); rt().prof_on = on != 0; rt().prof_n = 0; return HALO_OK; }
-int halo_profile_read(float* ms, const char** names, int max_stages) {
+int halo_profile_enable(int on) { HALO_API_BEGIN LOCK(); rt().prof_on = on != 0; rt().prof_n = 0; return HALO_OK; HALO_API_END }
+int halo_profile_read(float* ms, const char** names, int max_stages) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     Runtime& R = rt();
     int n = R.prof_n < max_stages ? R.prof_n : max_stages;
@@ -521,11 +540,12 @@ int halo_profile_read(float* ms, const char** names, int max_stages) {
         if (names) names[i] = R.prof_name[i];
     }
     return n;
+HALO_API_END
 }
 unsigned long long halo_launch_count(void) { return rt().launches; }
 
 uint64_t halo_gen_point_multiplier(uint64_t seed, uint64_t i) { return splitmix64(seed + i * 0x2545F4914F6CDD1DULL) | 1ULL; }
-int halo_gen_points_dev(int curve, uint64_t seed, size_t first, size_t n, void* d_out_xy) {
+int halo_gen_points_dev(int curve, uint64_t seed, size_t first, size_t n, void* d_out_xy) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK((curve == 0 || curve == 1) && (d_out_xy || n == 0), HALO_EINVAL, "gen_points: bad argument");
     if (n == 0) return HALO_OK;
@@ -535,8 +555,9 @@ int halo_gen_points_dev(int curve, uint64_t seed, size_t first, size_t n, void* 
     else gen_points_kernel<1><<<grid, 128, 0, R.stream>>>(seed, first, n, (Affine<1>*)d_out_xy);
     HALO_CUDA(cudaGetLastError());
     return HALO_OK;
+HALO_API_END
 }
-int halo_gen_points(int curve, uint64_t seed, size_t first, size_t n, uint64_t* out_xy) {
+int halo_gen_points(int curve, uint64_t seed, size_t first, size_t n, uint64_t* out_xy) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(out_xy || n == 0, HALO_EINVAL, "gen_points: null output");
     if (n == 0) return HALO_OK;
@@ -546,12 +567,13 @@ int halo_gen_points(int curve, uint64_t seed, size_t first, size_t n, uint64_t* 
     HALO_CUDA(cudaMemcpyAsync(out_xy, d, n * 64, cudaMemcpyDeviceToHost, rt().stream));
     HALO_CUDA(cudaStreamSynchronize(rt().stream));
     return HALO_OK;
+HALO_API_END
 }
 
-int halo_set_tuning(int key, int value) { if (key < 0 || key >= 8) return HALO_EINVAL; rt().tune[key] = value; return HALO_OK; }
-int halo_msm_set_window(int c) { rt().msm_window_override = c; return HALO_OK; }
+int halo_set_tuning(int key, int value) { HALO_API_BEGIN LOCK(); if (key < 0 || key >= 8) return HALO_EINVAL; rt().tune[key] = value; return HALO_OK; HALO_API_END }
+int halo_msm_set_window(int c) { HALO_API_BEGIN LOCK(); rt().msm_window_override = c; return HALO_OK; HALO_API_END }
 
-int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k, uint64_t out_xyz[12]) {
+int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k, uint64_t out_xyz[12]) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
     HALO_CHECK(out_xyz && (d_scalars || k == 0), HALO_EINVAL, "msm: null pointer");
@@ -563,10 +585,11 @@ int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void*
     }
     bases += base_off * 64;
     return curve == 0 ? msm_device<0>(bases, d_scalars, k, 1, out_xyz, 0) : msm_device<1>(bases, d_scalars, k, 1, out_xyz, 0);
+HALO_API_END
 }
 
 int halo_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k, size_t b,
-                       uint64_t* out_xyz) {
+                       uint64_t* out_xyz) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
     HALO_CHECK(out_xyz && (d_scalars || k == 0 || b == 0), HALO_EINVAL, "msm_batch: null pointer");
@@ -578,9 +601,10 @@ int halo_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const
     }
     bases += base_off * 64;
     return curve == 0 ? msm_device<0>(bases, d_scalars, k, b, out_xyz, 0) : msm_device<1>(bases, d_scalars, k, b, out_xyz, 0);
+HALO_API_END
 }
 
-int halo_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_t* scalars, size_t k, uint64_t out_xyz[12]) {
+int halo_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_t* scalars, size_t k, uint64_t out_xyz[12]) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
     HALO_CHECK(out_xyz && (scalars || k == 0), HALO_EINVAL, "msm: null pointer");
@@ -605,9 +629,10 @@ int halo_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_
     int rc = halo_msm_dev(curve, d_b, base_off, d_s, k, out_xyz);
     if (R.wait_copy) { cudaStreamSynchronize(R.copy_stream); R.wait_copy = false; }   // error paths: never leave a copy in flight
     return rc;
+HALO_API_END
 }
 
-int halo_msm_batch(int curve, size_t base_off, const uint64_t* scalars, size_t k, size_t b, uint64_t* out_xyz) {
+int halo_msm_batch(int curve, size_t base_off, const uint64_t* scalars, size_t k, size_t b, uint64_t* out_xyz) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
     HALO_CHECK(out_xyz && (scalars || k == 0 || b == 0), HALO_EINVAL, "msm_batch: null pointer");
@@ -617,22 +642,25 @@ int halo_msm_batch(int curve, size_t base_off, const uint64_t* scalars, size_t k
         HALO_CUDA(cudaMemcpyAsync(d_s, scalars, b * k * 32, cudaMemcpyHostToDevice, rt().stream));
     }
     return halo_msm_batch_dev(curve, nullptr, base_off, d_s, k, b, out_xyz);
+HALO_API_END
 }
 
-int halo_msm_proj(int curve, const uint64_t* bases_xyz, const uint64_t* scalars, size_t k, uint64_t out_xyz[12]) {
+int halo_msm_proj(int curve, const uint64_t* bases_xyz, const uint64_t* scalars, size_t k, uint64_t out_xyz[12]) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
     HALO_CHECK(out_xyz && ((bases_xyz && scalars) || k == 0), HALO_EINVAL, "msm_proj: null pointer");
     return curve == 0 ? msm_proj_impl<0>(bases_xyz, scalars, k, out_xyz) : msm_proj_impl<1>(bases_xyz, scalars, k, out_xyz);
+HALO_API_END
 }
 
-int halo_point_sum(int curve, const uint64_t* pts_xyz, size_t n, uint64_t out_xyz[12]) {
+int halo_point_sum(int curve, const uint64_t* pts_xyz, size_t n, uint64_t out_xyz[12]) { HALO_API_BEGIN
     HALO_CHECK((curve == 0 || curve == 1) && out_xyz && (pts_xyz || n == 0), HALO_EINVAL, "point_sum: bad argument");
     if (curve == 0) point_sum_impl<0>(pts_xyz, n, out_xyz); else point_sum_impl<1>(pts_xyz, n, out_xyz);
     return HALO_OK;
+HALO_API_END
 }
 
-int halo_field_op(int field, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {
+int halo_field_op(int field, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK((field == 0 || field == 1) && a && out && op >= 0 && op <= 5, HALO_EINVAL, "field_op: bad argument");
     if (n == 0) return HALO_OK;
@@ -652,9 +680,10 @@ int halo_field_op(int field, int op, const uint64_t* a, const uint64_t* b, uint6
     HALO_CUDA(cudaMemcpyAsync(out, dout, n * 32, cudaMemcpyDeviceToHost, R.stream));
     HALO_CUDA(cudaStreamSynchronize(R.stream));
     return HALO_OK;
+HALO_API_END
 }
 
-int halo_bench_modmul(int field, int blocks, int threads, int iters, float* ms, uint64_t out[4]) {
+int halo_bench_modmul(int field, int blocks, int threads, int iters, float* ms, uint64_t out[4]) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     Runtime& R = rt();
     void* d;
@@ -673,8 +702,9 @@ int halo_bench_modmul(int field, int blocks, int threads, int iters, float* ms, 
     HALO_CUDA(cudaMemcpy(out, d, 32, cudaMemcpyDeviceToHost));
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     return HALO_OK;
+HALO_API_END
 }
-int halo_bench_imad(int blocks, int threads, int iters, float* ms, uint64_t* out) {
+int halo_bench_imad(int blocks, int threads, int iters, float* ms, uint64_t* out) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     Runtime& R = rt();
     void* d;
@@ -692,47 +722,53 @@ int halo_bench_imad(int blocks, int threads, int iters, float* ms, uint64_t* out
     HALO_CUDA(cudaMemcpy(out, d, 8, cudaMemcpyDeviceToHost));
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     return HALO_OK;
+HALO_API_END
 }
 
 // ---- PLONK prover / verifier (plonk.cu) ----
 size_t halo_plonk_proof_words(unsigned lg_n) { return plonk_proof_words(lg_n); }
 
 int halo_plonk_prove(int curve, unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, const uint64_t* public_inputs,
-                     size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof) {
+                     size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
     HALO_CHECK(polys && w_evals && acc_prev && out_proof && (public_inputs || n_public == 0), HALO_EINVAL, "null argument");
     return curve == 0 ? plonk_prove<0>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof, nullptr)
                       : plonk_prove<1>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof, nullptr);
+HALO_API_END
 }
 
-int halo_plonk_circuit_load(int curve, unsigned lg_n, const uint64_t* polys, int* handle) {
+int halo_plonk_circuit_load(int curve, unsigned lg_n, const uint64_t* polys, int* handle) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
     HALO_CHECK(polys && handle, HALO_EINVAL, "null argument");
     return plonk_circuit_load(curve, lg_n, polys, handle);
+HALO_API_END
 }
-int halo_plonk_circuit_free(int handle) {
+int halo_plonk_circuit_free(int handle) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     return plonk_circuit_free(handle);
+HALO_API_END
 }
 int halo_plonk_prove_circuit(int handle, const uint64_t* w_polys, const uint64_t* w_evals, const uint64_t* public_inputs,
-                             size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof) {
+                             size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(w_polys && w_evals && acc_prev && out_proof && (public_inputs || n_public == 0), HALO_EINVAL, "null argument");
     return plonk_prove_resident(handle, w_polys, w_evals, public_inputs, n_public, acc_prev, out_proof);
+HALO_API_END
 }
 
 int halo_plonk_verify(int curve, unsigned lg_n, const uint64_t* circuit_C_qs, const uint64_t* public_inputs, size_t n_public,
-                      size_t public_input_count, const uint64_t* acc_prev, const uint64_t* proof, int succinct_only) {
+                      size_t public_input_count, const uint64_t* acc_prev, const uint64_t* proof, int succinct_only) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
     HALO_CHECK(circuit_C_qs && acc_prev && proof && (public_inputs || n_public == 0), HALO_EINVAL, "null argument");
     return curve == 0 ? plonk_verify<0>(lg_n, circuit_C_qs, public_inputs, n_public, public_input_count, acc_prev, proof, succinct_only)
                       : plonk_verify<1>(lg_n, circuit_C_qs, public_inputs, n_public, public_input_count, acc_prev, proof, succinct_only);
+HALO_API_END
 }
 
-int halo_bench_pipe(int mode, int blocks, int threads, int iters, float* ms, uint64_t* out) {
+int halo_bench_pipe(int mode, int blocks, int threads, int iters, float* ms, uint64_t* out) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     Runtime& R = rt();
     void* d;
@@ -750,6 +786,7 @@ int halo_bench_pipe(int mode, int blocks, int threads, int iters, float* ms, uin
     HALO_CUDA(cudaMemcpy(out, d, 8, cudaMemcpyDeviceToHost));
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     return HALO_OK;
+HALO_API_END
 }
 
 }  // extern "C"
@@ -803,24 +840,27 @@ static int poly_evaluate_impl(const uint64_t* coeffs, size_t len, unsigned log_n
 }
 
 extern "C" {
-int halo_ntt_dev(int field, void* d_data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null) {
+int halo_ntt_dev(int field, void* d_data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK((field == 0 || field == 1) && (d_data || b == 0) && log_n <= 30, HALO_EINVAL, "ntt: bad argument");
     if (b == 0) return HALO_OK;
     return field == 0 ? ntt_dev_impl<0>(d_data, log_n, b, inverse, coset_offset_or_null)
                       : ntt_dev_impl<1>(d_data, log_n, b, inverse, coset_offset_or_null);
+HALO_API_END
 }
-int halo_ntt(int field, uint64_t* data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null) {
+int halo_ntt(int field, uint64_t* data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK((field == 0 || field == 1) && (data || b == 0) && log_n <= 30, HALO_EINVAL, "ntt: bad argument");
     if (b == 0) return HALO_OK;
     return field == 0 ? ntt_host_impl<0>(data, log_n, b, inverse, coset_offset_or_null)
                       : ntt_host_impl<1>(data, log_n, b, inverse, coset_offset_or_null);
+HALO_API_END
 }
-int halo_poly_evaluate(int field, const uint64_t* coeffs, size_t len, unsigned log_n, uint64_t* out_evals) {
+int halo_poly_evaluate(int field, const uint64_t* coeffs, size_t len, unsigned log_n, uint64_t* out_evals) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK((field == 0 || field == 1) && (coeffs || len == 0) && out_evals && log_n <= 30, HALO_EINVAL, "poly_evaluate: bad argument");
     return field == 0 ? poly_evaluate_impl<0>(coeffs, len, log_n, out_evals) : poly_evaluate_impl<1>(coeffs, len, log_n, out_evals);
+HALO_API_END
 }
 }  // extern "C"
 
@@ -830,74 +870,99 @@ extern "C" {
 size_t halo_instance_words(unsigned lg_n) { return 24 * (size_t)lg_n + 54; }
 size_t halo_proof_words(unsigned lg_n) { return 24 * (size_t)lg_n + 33; }
 
-int halo_pcdl_commit(int curve, const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w_or_null, uint64_t out_xyz[12]) {
+int halo_pcdl_commit(int curve, const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w_or_null, uint64_t out_xyz[12]) { HALO_API_BEGIN
     LOCK(); NEED_INIT(); NEED_CURVE();
     HALO_CHECK(out_xyz && (coeffs || len == 0), HALO_EINVAL, "pcdl_commit: null pointer");
     return curve == 0 ? pcdl_commit<0>(coeffs, len, d, w_or_null, out_xyz) : pcdl_commit<1>(coeffs, len, d, w_or_null, out_xyz);
+HALO_API_END
+}
+int halo_pcdl_chunked_commit(int curve, const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w_or_null, size_t chunk_size,
+                              uint64_t* out_xyz, size_t* out_count) { HALO_API_BEGIN
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    HALO_CHECK((out_xyz || len == 0) && (coeffs || len == 0), HALO_EINVAL, "chunked_commit: null pointer");
+    return curve == 0 ? pcdl_chunked_commit<0>(coeffs, len, d, w_or_null, chunk_size, out_xyz, out_count)
+                      : pcdl_chunked_commit<1>(coeffs, len, d, w_or_null, chunk_size, out_xyz, out_count);
+HALO_API_END
+}
+int halo_ipa_fold_table_build(int curve, size_t n) { HALO_API_BEGIN
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    return curve == 0 ? fold_table_build<0>(n) : fold_table_build<1>(n);
+HALO_API_END
 }
 int halo_pcdl_open(int curve, const uint64_t* coeffs, size_t len, const uint64_t C_xyz[12], size_t d, const uint64_t z[4],
                    const uint64_t* v_or_null, const uint64_t* w_or_null, const uint64_t* hide_q, const uint64_t* hide_wbar,
-                   uint64_t* out_proof, uint64_t* out_v_or_null) {
+                   uint64_t* out_proof, uint64_t* out_v_or_null) { HALO_API_BEGIN
     LOCK(); NEED_INIT(); NEED_CURVE();
     HALO_CHECK(C_xyz && z && out_proof && (coeffs || len == 0), HALO_EINVAL, "pcdl_open: null pointer");
     return curve == 0 ? pcdl_open<0>(coeffs, len, C_xyz, d, z, v_or_null, w_or_null, hide_q, hide_wbar, out_proof, out_v_or_null, false)
                       : pcdl_open<1>(coeffs, len, C_xyz, d, z, v_or_null, w_or_null, hide_q, hide_wbar, out_proof, out_v_or_null, false);
+HALO_API_END
 }
-int halo_pcdl_succinct_check(int curve, const uint64_t* instance, uint64_t* out_xis_or_null, uint64_t* out_U_or_null) {
+int halo_pcdl_succinct_check(int curve, const uint64_t* instance, uint64_t* out_xis_or_null, uint64_t* out_U_or_null) { HALO_API_BEGIN
     LOCK(); NEED_INIT(); NEED_CURVE();
     HALO_CHECK(instance, HALO_EINVAL, "succinct_check: null pointer");
     return curve == 0 ? pcdl_succinct_check<0>(instance, out_xis_or_null, out_U_or_null)
                       : pcdl_succinct_check<1>(instance, out_xis_or_null, out_U_or_null);
+HALO_API_END
 }
-int halo_pcdl_check(int curve, const uint64_t* instance) {
+int halo_pcdl_check(int curve, const uint64_t* instance) { HALO_API_BEGIN
     LOCK(); NEED_INIT(); NEED_CURVE();
     HALO_CHECK(instance, HALO_EINVAL, "check: null pointer");
     return curve == 0 ? pcdl_check<0>(instance) : pcdl_check<1>(instance);
+HALO_API_END
 }
-int halo_acc_prover(int curve, const uint64_t* instances, size_t m, uint64_t* out_acc) {
+int halo_acc_prover(int curve, const uint64_t* instances, size_t m, uint64_t* out_acc) { HALO_API_BEGIN
     LOCK(); NEED_INIT(); NEED_CURVE();
     HALO_CHECK(out_acc, HALO_EINVAL, "acc_prover: null pointer");
     return curve == 0 ? acc_prover<0>(instances, m, out_acc) : acc_prover<1>(instances, m, out_acc);
+HALO_API_END
 }
-int halo_acc_verifier(int curve, const uint64_t* instances, size_t m, const uint64_t* acc) {
+int halo_acc_verifier(int curve, const uint64_t* instances, size_t m, const uint64_t* acc) { HALO_API_BEGIN
     LOCK(); NEED_INIT(); NEED_CURVE();
     HALO_CHECK(acc, HALO_EINVAL, "acc_verifier: null pointer");
     return curve == 0 ? acc_verifier<0>(instances, m, acc) : acc_verifier<1>(instances, m, acc);
+HALO_API_END
 }
-int halo_acc_decider(int curve, const uint64_t* acc) { return halo_pcdl_check(curve, acc); }
-int halo_hpoly_commit(int curve, const uint64_t* xis, size_t lg_n, uint64_t out_xyz[12]) {
+int halo_acc_decider(int curve, const uint64_t* acc) { HALO_API_BEGIN return halo_pcdl_check(curve, acc); HALO_API_END }
+int halo_hpoly_commit(int curve, const uint64_t* xis, size_t lg_n, uint64_t out_xyz[12]) { HALO_API_BEGIN
     LOCK(); NEED_INIT(); NEED_CURVE();
     HALO_CHECK(xis && out_xyz && lg_n <= 30, HALO_EINVAL, "hpoly_commit: bad argument");
     HALO_CHECK(rt().pp[curve].n >= ((size_t)1 << lg_n), HALO_EPARAMS, "hpoly_commit: resident generators missing or too few");
     return curve == 0 ? hpoly_commit_words<0>(xis, (unsigned)lg_n, out_xyz) : hpoly_commit_words<1>(xis, (unsigned)lg_n, out_xyz);
+HALO_API_END
 }
-int halo_acc_hpoly(int field, const uint64_t* xis, const uint64_t* alphas, size_t m, size_t lg_n, uint64_t* out_coeffs) {
+int halo_acc_hpoly(int field, const uint64_t* xis, const uint64_t* alphas, size_t m, size_t lg_n, uint64_t* out_coeffs) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK((field == 0 || field == 1) && xis && alphas && out_coeffs && lg_n <= 30, HALO_EINVAL, "acc_hpoly: bad argument");
     return field == 0 ? hpoly_coeffs<0>(xis, alphas, m, (unsigned)lg_n, out_coeffs) : hpoly_coeffs<1>(xis, alphas, m, (unsigned)lg_n, out_coeffs);
+HALO_API_END
 }
-int halo_hpoly_eval(int field, const uint64_t* xis, size_t lg_n, const uint64_t z[4], uint64_t out[4]) {
+int halo_hpoly_eval(int field, const uint64_t* xis, size_t lg_n, const uint64_t z[4], uint64_t out[4]) { HALO_API_BEGIN
     HALO_CHECK((field == 0 || field == 1) && xis && z && out, HALO_EINVAL, "hpoly_eval: bad argument");
     if (field == 0) hpoly_eval_words<0>(xis, (unsigned)lg_n, z, out); else hpoly_eval_words<1>(xis, (unsigned)lg_n, z, out);
     return HALO_OK;
+HALO_API_END
 }
 }  // extern "C"
 
 extern "C" {
-int halo_scalar_dot(int field, const uint64_t* xs, const uint64_t* ys, size_t n, uint64_t out[4]) {
+int halo_scalar_dot(int field, const uint64_t* xs, const uint64_t* ys, size_t n, uint64_t out[4]) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK((field == 0 || field == 1) && out && ((xs && ys) || n == 0), HALO_EINVAL, "scalar_dot: bad argument");
     return field == 0 ? scalar_dot_host<0>(xs, ys, n, out) : scalar_dot_host<1>(xs, ys, n, out);
+HALO_API_END
 }
-int halo_construct_powers(int field, const uint64_t z[4], size_t n, uint64_t* out) {
+int halo_construct_powers(int field, const uint64_t z[4], size_t n, uint64_t* out) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK((field == 0 || field == 1) && z && (out || n == 0), HALO_EINVAL, "construct_powers: bad argument");
     return field == 0 ? construct_powers_host<0>(z, n, out) : construct_powers_host<1>(z, n, out);
+HALO_API_END
 }
-int halo_poly_mul(int field, const uint64_t* a, size_t la, const uint64_t* b, size_t lb, uint64_t* out) {
+int halo_poly_mul(int field, const uint64_t* a, size_t la, const uint64_t* b, size_t lb, uint64_t* out) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK((field == 0 || field == 1) && ((a && b && out) || la == 0 || lb == 0), HALO_EINVAL, "poly_mul: bad argument");
     HALO_CHECK(la + lb <= ((size_t)1 << 30), HALO_EINVAL, "poly_mul: product too long");
     return field == 0 ? poly_mul_host<0>(a, la, b, lb, out) : poly_mul_host<1>(a, la, b, lb, out);
+HALO_API_END
 }
 }  // extern "C"

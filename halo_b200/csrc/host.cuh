@@ -28,8 +28,23 @@ struct Host {
         for (int i = 7; i >= 0; --i) { u32 p = modulus_limb<S>(i); if (s.l[i] != p) return s.l[i] < p; }
         return false;
     }
+    static bool scalar_words_valid(const uint64_t* w) { return scalar_is_valid(scalar(w)); }
+    static bool base_is_valid(const Fe<B>& s) {
+        for (int i = 7; i >= 0; --i) { u32 p = modulus_limb<B>(i); if (s.l[i] != p) return s.l[i] < p; }
+        return false;
+    }
+    // What arkworks' validated deserialisation guarantees for a Projective<P> and the C ABI has to check itself:
+    // every coordinate below the modulus and Y^2 = X^3 + 5 Z^6 (Z = 0 is the identity).  Both Pasta curves have prime
+    // order, so on-curve implies in-subgroup.
+    static bool point_words_valid(const uint64_t* w) {
+        Jac<C> j; memcpy(&j, w, 96);
+        if (!base_is_valid(j.X) || !base_is_valid(j.Y) || !base_is_valid(j.Z)) return false;
+        if (fe_is_zero<B>(j.Z)) return true;
+        const Fe<B> z2 = fe_sqr<B>(j.Z), z6 = fe_mul<B>(fe_sqr<B>(z2), z2);
+        const Fe<B> rhs = fe_add<B>(fe_mul<B>(fe_sqr<B>(j.X), j.X), fe_mul<B>(fe_from_u64<B>(5), z6));
+        return fe_eq<B>(fe_sqr<B>(j.Y), rhs);
+    }
 };
-
 
 // msm.cu / ntt.cu / ipa.cu
 template <int C> int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, uint64_t* out_xyz,

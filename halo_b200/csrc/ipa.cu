@@ -583,6 +583,43 @@ int pcdl_commit(const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w,
     return HALO_OK;
 }
 
+// pcdl::chunked_commit (pcdl.rs:294-314): one pedersen::commit(w, Gs[0..n], chunk) per chunk of the (stripped)
+// coefficient vector.  The full-length chunks are consecutive scalar vectors over the same bases, i.e. exactly the
+// layout of the batched MSM; a ragged last chunk is one more MSM.  *out_count = number of chunks = ceil(len / chunk).
+template <int C>
+int pcdl_chunked_commit(const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w, size_t chunk, uint64_t* out_xyz,
+                        size_t* out_count) {
+    typedef Host<C> H;
+    Runtime& R = rt();
+    const size_t n = d + 1;
+    len = strip_len(coeffs, len);
+    HALO_CHECK(n != 0 && (n & (n - 1)) == 0, HALO_EINVAL, "chunked_commit: n is not a power of two");
+    HALO_CHECK(R.pp[C].n > 0, HALO_EPARAMS, "chunked_commit: public parameters not loaded");
+    HALO_CHECK(d <= R.pp[C].n - 1, HALO_EINVAL, "chunked_commit: d <= D violated");
+    HALO_CHECK(chunk > 0, HALO_EINVAL, "chunked_commit: chunk size must be non-zero (slice::chunks panics)");
+    HALO_CHECK(len == 0 || std::min(chunk, len) <= n, HALO_EINVAL, "chunked_commit: a chunk is longer than Gs[0..n] (pedersen.rs:14-19)");
+    const size_t full = len / chunk, rem = len - full * chunk, count = full + (rem ? 1 : 0);
+    if (out_count) *out_count = count;
+    if (!count) return HALO_OK;
+    void* d_c;
+    if (int e = ws_get(WS_SCALARS, len * 32, &d_c)) return e;
+    HALO_CUDA(cudaMemcpyAsync(d_c, coeffs, len * 32, cudaMemcpyHostToDevice, R.stream));
+    // batches bounded by the pipeline's 2^32 (window, point) pairs and a 1 GiB index buffer
+    const size_t per = std::max<size_t>(1, std::min<size_t>(64, ((size_t)1 << 28) / (chunk * 17)));
+    for (size_t i = 0; i < full; i += per) {
+        const size_t b = std::min(per, full - i);
+        if (int e = msm_device<C>(R.pp[C].d_gs, (const char*)d_c + i * chunk * 32, chunk, b, out_xyz + 12 * i, 0)) return e;
+    }
+    if (rem) if (int e = msm_device<C>(R.pp[C].d_gs, (const char*)d_c + full * chunk * 32, rem, 1, out_xyz + 12 * full, 0)) return e;
+    if (w) {
+        const typename H::Pt wS = H::mul(H::from_affine_words(R.pp[C].s_xy), H::scalar(w));
+        for (size_t i = 0; i < count; ++i) H::to_words(H::add(wS, H::from_words(out_xyz + 12 * i)), out_xyz + 12 * i);
+    }
+    return HALO_OK;
+}
+template int pcdl_chunked_commit<0>(const uint64_t*, size_t, size_t, const uint64_t*, size_t, uint64_t*, size_t*);
+template int pcdl_chunked_commit<1>(const uint64_t*, size_t, size_t, const uint64_t*, size_t, uint64_t*, size_t*);
+
 // width-3 NAF of the two half-scalars as a list of table additions; false if a digit falls outside the table
 static void wnaf3_ops(const u32 mag[5], int negative, u32 phi_bit, FoldOps* ops, bool* ok) {
     u64 k[3] = {(u64)mag[0] | ((u64)mag[1] << 32), (u64)mag[2] | ((u64)mag[3] << 32), (u64)mag[4]};
@@ -647,6 +684,21 @@ static int ensure_fold_table(size_t n, const Affine<C>** out) {
     *out = (const Affine<C>*)tab;
     return HALO_OK;
 }
+
+// explicit set-up step (halo_ipa_fold_table_build): build the table for openings of size n now instead of inside the
+// first opening
+template <int C>
+int fold_table_build(size_t n) {
+    Runtime& R = rt();
+    HALO_CHECK(n >= 4 && (n & (n - 1)) == 0, HALO_EINVAL, "fold table: n must be a power of two >= 4");
+    HALO_CHECK(R.pp[C].n >= n, HALO_EPARAMS, "fold table: public parameters missing or shorter than n");
+    const Affine<C>* tab = nullptr;
+    if (int e = ensure_fold_table<C>(n, &tab)) return e;
+    HALO_CHECK(tab != nullptr, HALO_ECUDA, "fold table: not enough device memory (openings fall back to the ladder fold)");
+    return HALO_OK;
+}
+template int fold_table_build<0>(size_t);
+template int fold_table_build<1>(size_t);
 
 // ---------------------------------------------------------------------------------------------------------
 // pcdl::open / open_without_eval (pcdl.rs:326-473)
@@ -887,10 +939,12 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
 // ---------------------------------------------------------------------------------------------------------
 template <int S>
 static Fe<S> hpoly_eval(const Fe<S>* xis, unsigned lg_n, const Fe<S>& z) {
-    Fe<S> one = fe_one<S>(), v = one, zi = z;
-    for (unsigned i = 0; i < lg_n; ++i) {
-        v = fe_mul<S>(v, fe_add<S>(one, fe_mul<S>(xis[lg_n - i], zi)));
+    // literally as the reference: the first factor is taken before the loop, so lg n = 0 yields 1 + xi_0 z
+    Fe<S> one = fe_one<S>(), zi = z;
+    Fe<S> v = fe_add<S>(one, fe_mul<S>(xis[lg_n], z));
+    for (unsigned i = 1; i < lg_n; ++i) {
         zi = fe_sqr<S>(zi);
+        v = fe_mul<S>(v, fe_add<S>(one, fe_mul<S>(xis[lg_n - i], zi)));
     }
     return v;
 }
@@ -915,6 +969,35 @@ struct InstanceView {
     typename H::Pt Cbar() const { return H::from_words(proof() + 24 * lg_n + 17); }
     typename H::SF wprime() const { return H::scalar(proof() + 24 * lg_n + 29); }
 };
+
+// What the reference gets from its types -- arkworks field elements are always below the modulus and deserialised
+// points are checked to be on the curve -- has to be checked at the C ABI: a flat instance is raw words.  `d` is
+// validated FIRST, because every other offset is derived from it.  HALO_EINVAL for a malformed d (n not a power of
+// two, as the assert in the reference), HALO_EREJECT for d > D, a non-canonical scalar or an off-curve point.
+template <int C>
+static int instance_validate(const uint64_t* inst) {
+    typedef Host<C> H;
+    Runtime& R = rt();
+    const uint64_t d = inst[12];
+    HALO_CHECK(d != ~(uint64_t)0 && ((d + 1) & d) == 0, HALO_EINVAL, "instance: n = d + 1 is not a power of two");
+    HALO_CHECK(R.pp[C].n > 0, HALO_EPARAMS, "instance: public parameters not loaded");
+    HALO_CHECK(d <= R.pp[C].n - 1, HALO_EREJECT, "d was larger than D!");
+    InstanceView<C> q(inst);
+    const unsigned L = q.lg_n;
+    HALO_CHECK(H::point_words_valid(inst), HALO_EREJECT, "instance: C is not a point of the curve");
+    HALO_CHECK(H::scalar_words_valid(inst + 13) && H::scalar_words_valid(inst + 17), HALO_EREJECT, "instance: z or v not below the modulus");
+    const uint64_t* pr = q.proof();
+    for (unsigned i = 0; i < 2 * L + 1; ++i)               // Ls, Rs, U
+        HALO_CHECK(H::point_words_valid(pr + 12 * i), HALO_EREJECT, "instance: L_i, R_i or U is not a point of the curve");
+    HALO_CHECK(H::scalar_words_valid(pr + 24 * L + 12), HALO_EREJECT, "instance: c not below the modulus");
+    const uint64_t hiding = pr[24 * L + 16];
+    HALO_CHECK(hiding <= 1, HALO_EREJECT, "instance: malformed Option tag");
+    if (hiding) {
+        HALO_CHECK(H::point_words_valid(pr + 24 * L + 17), HALO_EREJECT, "instance: C_bar is not a point of the curve");
+        HALO_CHECK(H::scalar_words_valid(pr + 24 * L + 29), HALO_EREJECT, "instance: w' not below the modulus");
+    }
+    return HALO_OK;
+}
 
 // sum_i ks[i] * pts[i] on the host for a few dozen points: 4-bit fixed windows with the doublings shared by all
 // points (Straus), 252 doublings + ~74 additions per point instead of a 255-step ladder per point
@@ -950,11 +1033,8 @@ int pcdl_succinct_check(const uint64_t* inst, uint64_t* xis_out, uint64_t* U_out
     typedef typename H::Pt Pt;
     constexpr int S = H::S;
     Runtime& R = rt();
+    if (int e = instance_validate<C>(inst)) return e;
     InstanceView<C> q(inst);
-    const size_t n = q.d + 1;
-    HALO_CHECK((n & (n - 1)) == 0, HALO_EINVAL, "succinct_check: n is not a power of two");
-    HALO_CHECK(R.pp[C].n > 0, HALO_EPARAMS, "succinct_check: public parameters not loaded");
-    HALO_CHECK(q.d <= R.pp[C].n - 1, HALO_EREJECT, "d was larger than D!");
     const unsigned lg_n = q.lg_n;
     const SF z = q.z(), v = q.v();
     Transcript<C> tr(LABEL_PCDL);
@@ -1030,6 +1110,7 @@ static int hpoly_commit(const typename Host<C>::SF* xis, unsigned lg_n, typename
 template <int C>
 int pcdl_check(const uint64_t* inst) {
     typedef Host<C> H;
+    if (int e = instance_validate<C>(inst)) return e;
     InstanceView<C> q(inst);
     std::vector<typename H::SF> xis(q.lg_n + 1);
     uint64_t U[12];
@@ -1068,6 +1149,14 @@ static int acc_common(const uint64_t* insts, size_t m, AccCommon<C>* out) {
     typedef typename H::SF SF;
     constexpr int S = H::S;
     HALO_CHECK(m > 0 && insts, HALO_EREJECT, "No instances given");
+    // the per-instance stride comes from the first instance's d: it must be a sane size BEFORE anything is read at
+    // offsets derived from it (every instance is then validated in full by its succinct check)
+    {
+        const uint64_t d0 = insts[12];
+        HALO_CHECK(d0 != ~(uint64_t)0 && ((d0 + 1) & d0) == 0, HALO_EREJECT, "acc: d + 1 of the first instance is not a power of two");
+        HALO_CHECK(rt().pp[C].n > 0, HALO_EPARAMS, "acc: public parameters not loaded");
+        HALO_CHECK(d0 <= rt().pp[C].n - 1, HALO_EREJECT, "d was larger than D!");
+    }
     InstanceView<C> first(insts);
     const size_t d = first.d;
     const unsigned lg_n = first.lg_n;
@@ -1106,9 +1195,9 @@ static int acc_common(const uint64_t* insts, size_t m, AccCommon<C>* out) {
     };
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
     const unsigned nt = (unsigned)std::min<size_t>(m, hw > 1 ? hw - 1 : 1);
-    std::vector<std::thread> th;
-    if (m > 1) for (unsigned t = 0; t < nt; ++t) th.emplace_back(work);
-    else work();
+    Workers th;
+    if (m > 1) th.spawn(nt, work);
+    if (th.size() == 0) work();
     // 6. alpha = rho1([h_i, U_i])
     Transcript<C> tr(LABEL_ASDL);
     int first_bad = -1;
@@ -1117,7 +1206,7 @@ static int acc_common(const uint64_t* insts, size_t m, AccCommon<C>* out) {
         if (rc[i]) { first_bad = (int)i; break; }
         for (unsigned k = 0; k <= lg_n; ++k) tr.absorb_scalar(out->xis[i * (lg_n + 1) + k]);
     }
-    for (auto& x : th) x.join();
+    th.join();
     if (first_bad < 0) for (size_t i = 0; i < m; ++i) if (rc[i]) { first_bad = (int)i; break; }
     if (first_bad >= 0) { last_err() = why[first_bad]; return rc[first_bad]; }
     lap("succinct checks + sponge");
@@ -1169,6 +1258,10 @@ int acc_verifier(const uint64_t* insts, size_t m, const uint64_t* acc) {
     constexpr int S = H::S;
     AccCommon<C> cs;
     if (int e = acc_common<C>(insts, m, &cs)) return e;
+    {
+        const int e = instance_validate<C>(acc);
+        if (e) return e == HALO_EINVAL ? HALO_EREJECT : e;
+    }
     InstanceView<C> a(acc);
     HALO_CHECK(xyzz_eq<C>(cs.Cbar, a.Cm()), HALO_EREJECT, "C_bar' != C_bar");
     HALO_CHECK(fe_eq<S>(cs.z, a.z()), HALO_EREJECT, "z' = z");

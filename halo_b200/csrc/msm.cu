@@ -694,10 +694,10 @@ static int msm_small(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR>*
     };
     if (nbatch == 1) combine(0);
     else {
-        std::vector<std::thread> th;
-        for (size_t i = 1; i < nbatch; ++i) th.emplace_back(combine, i);
+        Workers wk;
+        wk.spawn_indexed(1, (unsigned)nbatch, [&](unsigned i) { combine(i); });
         combine(0);
-        for (auto& x : th) x.join();
+        wk.join();
     }
     *done = true;
     return HALO_OK;
@@ -734,10 +734,10 @@ int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbat
     } else {                                              // one Horner (255 doublings, ~55 us) per MSM: the calling thread takes a share
         unsigned nt = std::min<size_t>(nbatch, std::max(1u, std::thread::hardware_concurrency()));
         auto share = [&](unsigned t) { for (size_t i = t; i < nbatch; i += nt) msm_combine_host<C>(win + i * P.nwin, P, out_xyz + 12 * i); };
-        std::vector<std::thread> th;
-        for (unsigned t = 1; t < nt; ++t) th.emplace_back(share, t);
+        Workers wk;
+        wk.spawn_indexed(1, nt, share);
         share(0);
-        for (auto& x : th) x.join();
+        wk.join();
     }
     return HALO_OK;
 }

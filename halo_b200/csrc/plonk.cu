@@ -858,6 +858,14 @@ int plonk_verify(unsigned lg_n, const uint64_t* C_qs, const uint64_t* pub, size_
     const uint64_t* o_pir = o_Cz + 12;
     const uint64_t* o_piro = o_pir + evalproof_words(lg_n);
     const uint64_t* o_acc = o_piro + evalproof_words(lg_n);
+    // the reference's types guarantee canonical field elements and on-curve points; raw words have to be checked
+    // (the two opening proofs and both accumulators are validated as instances inside acc_verifier)
+    for (int i = 0; i < NW + NT + 1; ++i)
+        HALO_CHECK(H::point_words_valid(o_Cws + 12 * i), HALO_EREJECT, "plonk: a commitment of the proof is not a point of the curve");
+    for (int i = 0; i < NQ; ++i)
+        HALO_CHECK(H::point_words_valid(C_qs + 12 * i), HALO_EINVAL, "plonk: a circuit commitment is not a point of the curve");
+    for (size_t j = 0; j < n_pub; ++j)
+        HALO_CHECK(H::scalar_words_valid(pub + 4 * j), HALO_EINVAL, "plonk: public input not below the modulus");
 
     Transcript<C> tr(LABEL_PLONK);
     Pt Cws[NW], Cts[NT], Cz = H::from_words(o_Cz);

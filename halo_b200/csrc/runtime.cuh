@@ -6,6 +6,7 @@
 #include <mutex>
 #include <string>
 #include <vector>
+#include <thread>
 #include <cstdio>
 #include "curve.cuh"
 #include "../../include/halo_b200.h"
@@ -81,6 +82,26 @@ inline std::string& last_err() { static thread_local std::string e; return e; }
             return (code);                          \
         }                                           \
     } while (0)
+
+// Worker threads that are always joined: thread creation failing half way (std::system_error) or an exception in the
+// spawning thread must not destroy a joinable std::thread, which would terminate the host process.
+struct Workers {
+    std::vector<std::thread> th;
+    template <class F> void spawn(unsigned n, F f) {
+        for (unsigned i = 0; i < n; ++i) {
+            try { th.emplace_back(f); } catch (...) { break; }
+        }
+    }
+    template <class F> void spawn_indexed(unsigned first, unsigned last, F f) {   // f(t) for t in [first, last)
+        for (unsigned t = first; t < last; ++t) {
+            try { th.emplace_back(f, t); } catch (...) { for (; t < last; ++t) f(t); break; }
+        }
+    }
+    size_t size() const { return th.size(); }
+    void join() { for (auto& t : th) if (t.joinable()) t.join(); th.clear(); }
+    ~Workers() { join(); }
+};
+
 
 // stage timing: prof_begin() at the start of a pipeline, prof_mark("name") after each stage's launches
 int prof_begin();

@@ -33,6 +33,27 @@ def commit(curve, coeffs, d, w=None):
     return out
 
 
+def chunked_commit(curve, coeffs, d, w=None, chunk_size=1):
+    """≙ pcdl::chunked_commit (pcdl.rs:294-314): one commit per `chunk_size` coefficients; returns (count, 12)."""
+    _lib.ensure_init()
+    c = as_u64(coeffs, 4)
+    if chunk_size <= 0:
+        raise _lib.PreconditionError(_lib.HALO_EINVAL, "chunk size must be non-zero (slice::chunks panics)")
+    cap = -(-c.shape[0] // chunk_size)
+    out = np.zeros((max(cap, 1), 12), dtype=np.uint64)
+    cnt = ctypes.c_size_t(0)
+    wv = as_u64(w, 4).reshape(4) if w is not None else None
+    check(lib.halo_pcdl_chunked_commit(curve, ptr(c) if c.shape[0] else None, ctypes.c_size_t(c.shape[0]), ctypes.c_size_t(d),
+                                       ptr(wv), ctypes.c_size_t(chunk_size), ptr(out), ctypes.byref(cnt)))
+    return out[:cnt.value]
+
+
+def fold_table_build(curve, n):
+    """Explicit set-up of the fixed-base table of the first generator fold for openings of size n (API addition)."""
+    _lib.ensure_init()
+    check(lib.halo_ipa_fold_table_build(curve, ctypes.c_size_t(n)))
+
+
 class HPoly:
     """h(X) = prod_{i<lg n} (1 + xi_{lg n - i} X^{2^i}) kept as its challenges (pcdl.rs:191-233)."""
 

@@ -100,6 +100,17 @@ size_t halo_instance_words(unsigned lg_n);
 size_t halo_proof_words(unsigned lg_n);
 /* ≙ pcdl::commit(p, d, w) (pcdl.rs:275-287) against the resident generators; asserts -> HALO_EINVAL */
 int halo_pcdl_commit(int curve, const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w_or_null, uint64_t out_xyz[12]);
+/* ≙ pcdl::chunked_commit(p, d, w, chunk_size) (pcdl.rs:294-314): one commit per chunk of p's coefficients (trailing zeros
+ * stripped as DensePolynomial does), each against Gs[0..chunk) with the same optional w.  out_xyz must hold
+ * ceil(len / chunk_size) points; *out_count (may be NULL) receives the number written.  chunk_size == 0 or a chunk
+ * longer than n -> HALO_EINVAL (slice::chunks / pedersen.rs:14-19 panic). */
+int halo_pcdl_chunked_commit(int curve, const uint64_t* coeffs, size_t len, size_t d, const uint64_t* w_or_null, size_t chunk_size,
+                              uint64_t* out_xyz, size_t* out_count);
+/* Explicit set-up of the fixed-base table the first generator fold of an opening of size n uses (2 x 136 x n/2 affine
+ * points: 9.1 GB at n = 2^20, ~0.25 s).  halo_pcdl_open builds it lazily for openings over the whole parameter set of
+ * >= 2^16 generators; a one-shot caller can pay for it here, outside its timed path.  Freed by halo_pp_reset /
+ * halo_shutdown.  HALO_ECUDA when the device has no room (openings then use the ladder fold). */
+int halo_ipa_fold_table_build(int curve, size_t n);
 /* ≙ pcdl::open / open_without_eval (pcdl.rs:326-473).  v_or_null == NULL: v = p(z) is computed (open) and written to
  * out_v_or_null.  Hiding (w_or_null != NULL) consumes the caller's randomness: hide_q = the d coefficients of the
  * uniform polynomial q (pcdl.rs:348), hide_wbar = w_bar (pcdl.rs:352). */
