@@ -136,7 +136,13 @@ int plonk_circuit_free(int handle);
 void plonk_circuits_release();
 int plonk_prove_resident(int handle, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*);
 template <int C> int plonk_verify(unsigned, const uint64_t*, const uint64_t*, size_t, size_t, const uint64_t*, const uint64_t*, int);
-template <int C> int acc_verifier(const uint64_t*, size_t, const uint64_t*);
+template <int C> int acc_verifier(const uint64_t*, size_t, const uint64_t*, bool sharded = false);
+template <int C> int acc_prover_dist(const uint64_t*, size_t, uint64_t*);
+template <int C> int pcdl_check_dist(const uint64_t*);
+bool dist_on();
+int dist_rank();
+int dist_world();
+int dist_allgather_dev(const void* d_send, void* d_recv, size_t bytes);
 template <int S> int hpoly_coeffs(const uint64_t*, const uint64_t*, size_t, unsigned, uint64_t*);
 template <int C> int hpoly_commit_words(const uint64_t*, unsigned, uint64_t*);
 template <int S> void hpoly_eval_words(const uint64_t*, unsigned, const uint64_t*, uint64_t*);
@@ -839,7 +845,42 @@ static int poly_evaluate_impl(const uint64_t* coeffs, size_t len, unsigned log_n
     return HALO_OK;
 }
 
+// NTT / iNTT batches across the communicator, by polynomial: rank r transforms the polynomials [r*per, (r+1)*per) of the
+// batch (per = ceil(b / world)); the blocks are all-gathered between device buffers and every rank returns the whole
+// result.  A single transform never leaves its GPU.
+template <int F>
+static int ntt_dist_impl(uint64_t* data, unsigned log_n, size_t b, int inverse, const uint64_t* coset) {
+    Runtime& R = rt();
+    const size_t W = (size_t)dist_world(), me = (size_t)dist_rank();
+    const size_t per = (b + W - 1) / W, N = (size_t)1 << log_n, blk = per * N * 32;
+    const size_t lo = std::min(b, me * per), hi = std::min(b, lo + per), cnt = hi - lo;
+    void *d_in, *d_out, *d_all;
+    if (int e = ws_get(WS_NTT0, blk, &d_in)) return e;
+    if (int e = ws_get(WS_NTT1, blk, &d_out)) return e;
+    if (int e = ws_get(WS_PLONK_TMP, blk * W, &d_all)) return e;
+    if (cnt) {
+        if (int e = upload_staged(d_in, data + lo * N * 4, cnt * N * 32)) return e;
+        Fe<F> g;
+        if (coset) memcpy(&g, coset, 32);
+        if (int e = ntt_device<F>((Fe<F>*)d_in, (Fe<F>*)d_out, (int)log_n, cnt, inverse != 0, coset ? &g : nullptr)) return e;
+    }
+    if (cnt < per) HALO_CUDA(cudaMemsetAsync((char*)d_out + cnt * N * 32, 0, (per - cnt) * N * 32, R.stream));
+    if (int e = dist_allgather_dev(d_out, d_all, blk)) return e;
+    HALO_CUDA(cudaMemcpyAsync(data, d_all, b * N * 32, cudaMemcpyDeviceToHost, R.stream));
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
+    return HALO_OK;
+}
+
 extern "C" {
+int halo_dist_ntt(int field, uint64_t* data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null) { HALO_API_BEGIN
+    LOCK(); NEED_INIT();
+    HALO_CHECK((field == 0 || field == 1) && (data || b == 0) && log_n <= 30, HALO_EINVAL, "ntt: bad argument");
+    HALO_CHECK(dist_on(), HALO_ENOINIT, "halo_dist_init has not been called");
+    if (b == 0) return HALO_OK;
+    return field == 0 ? ntt_dist_impl<0>(data, log_n, b, inverse, coset_offset_or_null)
+                      : ntt_dist_impl<1>(data, log_n, b, inverse, coset_offset_or_null);
+HALO_API_END
+}
 int halo_ntt_dev(int field, void* d_data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK((field == 0 || field == 1) && (d_data || b == 0) && log_n <= 30, HALO_EINVAL, "ntt: bad argument");
@@ -924,6 +965,26 @@ int halo_acc_verifier(int curve, const uint64_t* instances, size_t m, const uint
 HALO_API_END
 }
 int halo_acc_decider(int curve, const uint64_t* acc) { HALO_API_BEGIN return halo_pcdl_check(curve, acc); HALO_API_END }
+/* ---- the same three across the GPUs of the library's communicator (dist.cu) ---- */
+int halo_dist_acc_prover(int curve, const uint64_t* instances, size_t m, uint64_t* out_acc) { HALO_API_BEGIN
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    HALO_CHECK(out_acc, HALO_EINVAL, "acc_prover: null pointer");
+    return curve == 0 ? acc_prover_dist<0>(instances, m, out_acc) : acc_prover_dist<1>(instances, m, out_acc);
+HALO_API_END
+}
+int halo_dist_acc_verifier(int curve, const uint64_t* instances, size_t m, const uint64_t* acc) { HALO_API_BEGIN
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    HALO_CHECK(acc, HALO_EINVAL, "acc_verifier: null pointer");
+    HALO_CHECK(dist_on(), HALO_ENOINIT, "halo_dist_init has not been called");
+    return curve == 0 ? acc_verifier<0>(instances, m, acc, true) : acc_verifier<1>(instances, m, acc, true);
+HALO_API_END
+}
+int halo_dist_acc_decider(int curve, const uint64_t* acc) { HALO_API_BEGIN
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    HALO_CHECK(acc, HALO_EINVAL, "acc_decider: null pointer");
+    return curve == 0 ? pcdl_check_dist<0>(acc) : pcdl_check_dist<1>(acc);
+HALO_API_END
+}
 int halo_hpoly_commit(int curve, const uint64_t* xis, size_t lg_n, uint64_t out_xyz[12]) { HALO_API_BEGIN
     LOCK(); NEED_INIT(); NEED_CURVE();
     HALO_CHECK(xis && out_xyz && lg_n <= 30, HALO_EINVAL, "hpoly_commit: bad argument");

@@ -27,6 +27,15 @@ extern "C" int halo_msm_proj(int, const uint64_t*, const uint64_t*, size_t, uint
 
 namespace halo {
 
+// dist.cu: the library's NCCL layer (one process per GPU)
+bool dist_on();
+int dist_rank();
+int dist_world();
+int dist_allgather_dev(const void* d_send, void* d_recv, size_t bytes);
+int dist_allgather_host(const void* h_send, void* h_recv_all, size_t bytes);
+void dist_range(size_t total, size_t* lo, size_t* hi);
+template <int C> int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, size_t nbatch, uint64_t* out_xyz);
+
 template <int F> __device__ __forceinline__ Fe<F> g_ld(const Fe<F>* p) {
     Fe<F> r;
     const uint4* q = reinterpret_cast<const uint4*>(p);
@@ -1144,7 +1153,7 @@ struct AccCommon {
 
 // acc::common_subroutine (acc.rs:128-176).  insts: m flat instances of the same d.
 template <int C>
-static int acc_common(const uint64_t* insts, size_t m, AccCommon<C>* out) {
+static int acc_common(const uint64_t* insts, size_t m, AccCommon<C>* out, bool sharded = false) {
     typedef Host<C> H;
     typedef typename H::SF SF;
     constexpr int S = H::S;
@@ -1172,6 +1181,55 @@ static int acc_common(const uint64_t* insts, size_t m, AccCommon<C>* out) {
         fprintf(stderr, "[halo trace] acc_common m=%zu %-24s %9.3f ms\n", m, what, std::chrono::duration<double, std::milli>(t1 - t0).count());
         t0 = t1;
     };
+    // Multi-GPU (one process per GPU, SURVEY section 8(e) "ASDL over m instances: by instance"): rank r runs the succinct
+    // checks of instances r, r + N, r + 2N, ... on its share of the host's cores; challenge vectors, U's and verdicts
+    // are all-gathered (a few hundred KB), after which every rank runs the same serial sponge below.
+    if (sharded && dist_on() && dist_world() > 1) {
+        const size_t W = (size_t)dist_world(), me = (size_t)dist_rank();
+        const size_t per = (m + W - 1) / W, rec = (size_t)(lg_n + 1) * 4 + 12 + 1;      // words per instance record
+        std::vector<uint64_t> mine(per * rec, 0), all(per * rec * W, 0);
+        std::atomic<size_t> nxt{0};
+        auto share = [&]() {
+            for (;;) {
+                const size_t j = nxt.fetch_add(1, std::memory_order_relaxed);
+                const size_t i = j * W + me;
+                if (j >= per || i >= m) return;
+                const uint64_t* qi = insts + i * iw;
+                uint64_t* r = mine.data() + j * rec;
+                int code = HALO_EREJECT;
+                if ((size_t)qi[12] == d) code = pcdl_succinct_check<C>(qi, r, r + (size_t)(lg_n + 1) * 4);
+                r[rec - 1] = (uint64_t)(int64_t)code;
+            }
+        };
+        {
+            const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+            Workers wk;
+            wk.spawn((unsigned)std::min<size_t>(per, std::max<size_t>(1, hw / W)) - 1, share);
+            share();
+            wk.join();
+        }
+        if (int e = dist_allgather_host(mine.data(), all.data(), per * rec * 8)) return e;
+        Transcript<C> trs(LABEL_ASDL);
+        for (size_t i = 0; i < m; ++i) {
+            const uint64_t* r = all.data() + ((i % W) * per + i / W) * rec;
+            const int code = (int)(int64_t)r[rec - 1];
+            if (code) { last_err() = "acc: an instance failed its succinct check (sharded)"; return code; }
+            memcpy(out->xis.data() + i * (lg_n + 1), r, (size_t)(lg_n + 1) * 32);
+            memcpy(Us.data() + 12 * i, r + (size_t)(lg_n + 1) * 4, 96);
+            for (unsigned k = 0; k <= lg_n; ++k) trs.absorb_scalar(out->xis[i * (lg_n + 1) + k]);
+        }
+        lap("sharded succinct checks + gather + sponge");
+        for (size_t i = 0; i < m; ++i) trs.absorb_point(H::from_words(Us.data() + 12 * i));
+        const SF alpha = trs.challenge();
+        out->alphas.resize(m);
+        SF cur = fe_one<S>();
+        for (size_t i = 0; i < m; ++i) { out->alphas[i] = cur; cur = fe_mul<S>(cur, alpha); }
+        uint64_t Cw[12];
+        if (int e = halo_msm_proj(C, Us.data(), (const uint64_t*)out->alphas.data(), m, Cw)) return e;
+        out->Cbar = H::from_words(Cw);
+        out->z = trs.challenge();
+        return HALO_OK;
+    }
     // 4. m independent succinct checks (each sequential inside) on worker threads that take the instances in
     // order, while this thread already feeds finished challenge vectors to the AS_DL sponge (step 6 is one serial
     // chain of ~m lg n permutations - as long as all the checks together at m = 1024)
@@ -1251,13 +1309,89 @@ int acc_prover(const uint64_t* insts, size_t m, uint64_t* out_acc) {
                         nullptr, true);
 }
 
+// sum of `parts` vectors of n elements: out[i] = sum_p in[p * n + i]  (modular addition is not an NCCL operator)
+template <int F>
+__global__ void __launch_bounds__(256) vec_sum_kernel(const Fe<F>* __restrict__ in, size_t n, int parts, Fe<F>* __restrict__ out) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fe<F> s = g_ld(in + i);
+    for (int p = 1; p < parts; ++p) s = fe_add<F>(s, g_ld(in + (size_t)p * n + i));
+    g_st(out + i, s);
+}
+
+// acc::prover across the GPUs of the communicator: succinct checks by instance (acc_common), h(X) = sum alpha^i h_i(X)
+// as per-rank partial coefficient vectors over an instance range, all-gathered and added on every rank; the opening
+// itself is sequential in its challenges and runs replicated, so every rank returns the same accumulator.
+template <int C>
+int acc_prover_dist(const uint64_t* insts, size_t m, uint64_t* out_acc) {
+    typedef Host<C> H;
+    typedef typename H::SF SF;
+    constexpr int S = H::S;
+    HALO_CHECK(dist_on(), HALO_ENOINIT, "halo_dist_init has not been called");
+    AccCommon<C> cs;
+    if (int e = acc_common<C>(insts, m, &cs, true)) return e;
+    const SF v = cs.eval(cs.z);
+    const size_t n = cs.d + 1;
+    const int W = dist_world();
+    SF *d_h, *d_part;
+    if (int e = ws_get(WS_IPA_C, n * 32, (void**)&d_h)) return e;
+    if (int e = ws_get(WS_IPA_T1, (size_t)(W + 1) * n * 32, (void**)&d_part)) return e;
+    size_t lo, hi;
+    dist_range(m, &lo, &hi);
+    if (hi > lo) {
+        if (int e = hpoly_expand_dev<S>(cs.xis.data() + lo * (cs.lg_n + 1), cs.alphas.data() + lo, hi - lo, cs.lg_n, d_part)) return e;
+    } else {
+        HALO_CUDA(cudaMemsetAsync(d_part, 0, n * 32, rt().stream));
+    }
+    if (int e = dist_allgather_dev(d_part, d_part + n, n * 32)) return e;
+    vec_sum_kernel<S><<<(unsigned)((n + 255) / 256), 256, 0, rt().stream>>>(d_part + n, n, W, d_h);
+    rt().launches += 1;
+    HALO_CUDA(cudaGetLastError());
+    H::to_words(cs.Cbar, out_acc);
+    out_acc[12] = cs.d;
+    H::put_scalar(cs.z, out_acc + 13);
+    H::put_scalar(v, out_acc + 17);
+    uint64_t Cw[12];
+    H::to_words(cs.Cbar, Cw);
+    return pcdl_open<C>(nullptr, n, Cw, cs.d, (const uint64_t*)&cs.z, nullptr, nullptr, nullptr, nullptr, out_acc + 21,
+                        nullptr, true);
+}
+template int acc_prover_dist<0>(const uint64_t*, size_t, uint64_t*);
+template int acc_prover_dist<1>(const uint64_t*, size_t, uint64_t*);
+
+// acc::decider / pcdl::check with commit(h) as a point-range-sharded MSM over the resident generators
+template <int C>
+int pcdl_check_dist(const uint64_t* inst) {
+    typedef Host<C> H;
+    constexpr int S = H::S;
+    HALO_CHECK(dist_on(), HALO_ENOINIT, "halo_dist_init has not been called");
+    if (int e = instance_validate<C>(inst)) return e;
+    InstanceView<C> q(inst);
+    std::vector<typename H::SF> xis(q.lg_n + 1);
+    uint64_t U[12];
+    if (int e = pcdl_succinct_check<C>(inst, (uint64_t*)xis.data(), U)) return e;
+    const size_t n = (size_t)1 << q.lg_n;
+    typename H::SF* d_h;
+    if (int e = ws_get(WS_IPA_C, n * 32, (void**)&d_h)) return e;
+    typename H::SF one = fe_one<S>();
+    if (int e = hpoly_expand_dev<S>(xis.data(), &one, 1, q.lg_n, d_h)) return e;
+    size_t lo, hi;
+    dist_range(n, &lo, &hi);
+    uint64_t cw[12];
+    if (int e = dist_msm_device<C>((const Affine<C>*)rt().pp[C].d_gs + lo, d_h + lo, hi - lo, 1, cw)) return e;
+    HALO_CHECK(xyzz_eq<C>(H::from_words(U), H::from_words(cw)), HALO_EREJECT, "U != CM.Commit(ck, h_vec)");
+    return HALO_OK;
+}
+template int pcdl_check_dist<0>(const uint64_t*);
+template int pcdl_check_dist<1>(const uint64_t*);
+
 // acc::verifier (acc.rs:200-213)
 template <int C>
-int acc_verifier(const uint64_t* insts, size_t m, const uint64_t* acc) {
+int acc_verifier(const uint64_t* insts, size_t m, const uint64_t* acc, bool sharded) {
     typedef Host<C> H;
     constexpr int S = H::S;
     AccCommon<C> cs;
-    if (int e = acc_common<C>(insts, m, &cs)) return e;
+    if (int e = acc_common<C>(insts, m, &cs, sharded)) return e;
     {
         const int e = instance_validate<C>(acc);
         if (e) return e == HALO_EINVAL ? HALO_EREJECT : e;
@@ -1282,8 +1416,8 @@ template int pcdl_check<0>(const uint64_t*);
 template int pcdl_check<1>(const uint64_t*);
 template int acc_prover<0>(const uint64_t*, size_t, uint64_t*);
 template int acc_prover<1>(const uint64_t*, size_t, uint64_t*);
-template int acc_verifier<0>(const uint64_t*, size_t, const uint64_t*);
-template int acc_verifier<1>(const uint64_t*, size_t, const uint64_t*);
+template int acc_verifier<0>(const uint64_t*, size_t, const uint64_t*, bool);
+template int acc_verifier<1>(const uint64_t*, size_t, const uint64_t*, bool);
 
 // h(X) coefficient vector for m accumulated instances, returned to the host (≙ AccumulatedHPolys::get_poly)
 template <int S>

@@ -741,6 +741,30 @@ int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbat
     }
     return HALO_OK;
 }
+// The device half only, for the multi-GPU exchange (dist.cu): runs the general pipeline and leaves the nbatch * nwin
+// window sums in device memory; *c_out / *nwin_out tell the receiver how to combine them.  k > 0.
+template <int C>
+int msm_windows_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, ptrdiff_t base_stride,
+                       void** d_winsum, int* c_out, int* nwin_out) {
+    HALO_CHECK(k > 0 && k < ((size_t)1 << 31), HALO_EINVAL, "msm: k must be in [1, 2^31)");
+    MsmPlan P = make_plan(k, nbatch);
+    HALO_CHECK(P.nwt * k < ((size_t)1 << 32), HALO_EINVAL, "msm: batch too large (nbatch*nwin*k must be < 2^32)");
+    XYZZ<C>* d_win = nullptr;
+    if (int e = msm_enqueue<C>((const Affine<C>*)d_bases, (const Fe<CurveTraits<C>::SCALAR>*)d_scalars, k, P, base_stride, &d_win)) return e;
+    *d_winsum = d_win; *c_out = P.c; *nwin_out = P.nwin;
+    return HALO_OK;
+}
+template int msm_windows_device<0>(const void*, const void*, size_t, size_t, ptrdiff_t, void**, int*, int*);
+template int msm_windows_device<1>(const void*, const void*, size_t, size_t, ptrdiff_t, void**, int*, int*);
+// Horner over nwin window sums of width c (host)
+template <int C>
+void msm_horner_host(const void* win, int c, int nwin, uint64_t out_xyz[12]) {
+    MsmPlan P; P.c = c; P.nwin = nwin;
+    msm_combine_host<C>((const XYZZ<C>*)win, P, out_xyz);
+}
+template void msm_horner_host<0>(const void*, int, int, uint64_t*);
+template void msm_horner_host<1>(const void*, int, int, uint64_t*);
+
 template int msm_device<0>(const void*, const void*, size_t, size_t, uint64_t*, ptrdiff_t);
 template int msm_device<1>(const void*, const void*, size_t, size_t, uint64_t*, ptrdiff_t);
 

@@ -11,7 +11,8 @@
  *   - curve: 0 = Pallas, 1 = Vesta.   field: 0 = halo Fp (Pallas scalars), 1 = halo Fq (Vesta scalars)
  *                      (crates/group/src/lib.rs:8-9).  A curve's scalars live in field == curve.
  * Every function returns 0 on success or a negative HALO_E* code; nothing aborts.  Pointers are HOST pointers
- * unless the name ends in _dev.  The library keeps no caller pointer after returning.  One process drives one GPU.
+ * unless the name ends in _dev.  The library keeps no caller pointer after returning.  One process drives one GPU;
+ * N GPUs are N such processes joined by the halo_dist_* calls below.
  */
 #ifndef HALO_B200_H
 #define HALO_B200_H
@@ -131,6 +132,42 @@ int halo_hpoly_commit(int curve, const uint64_t* xis, size_t lg_n, uint64_t out_
 int halo_acc_hpoly(int field, const uint64_t* xis, const uint64_t* alphas, size_t m, size_t lg_n, uint64_t* out_coeffs);
 /* ≙ HPoly::eval (pcdl.rs:221-233), host */
 int halo_hpoly_eval(int field, const uint64_t* xis, size_t lg_n, const uint64_t z[4], uint64_t out[4]);
+
+/* ---- multi-GPU: one process per GPU, the library owns an NCCL communicator ------------------
+ * The reference is a single process with rayon; a host that wants N GPUs runs N ranks (threads of a launcher, MPI
+ * ranks, torchrun workers), each of which calls halo_init(device) and then halo_dist_init.  Rank 0 obtains the 128-byte
+ * NCCL id with halo_dist_unique_id and ships it to the others over any channel it has (a file, a socket, MPI_Bcast).
+ * NCCL is bound with dlopen("libnccl.so.2") on first use, so single-GPU callers never need it.
+ * Every halo_dist_* call is COLLECTIVE: all ranks call it, in the same order, and all receive the same result.
+ *   MSM        ≙ point_dot_affine / commit sharded by POINT RANGE: a rank runs the whole Pippenger pipeline over its
+ *              range down to its window sums, which are all-gathered from device memory and combined on every rank.
+ *              halo_dist_msm takes the rank's own slice (k_local may differ between ranks and may be 0);
+ *              halo_dist_msm_global takes the WHOLE problem on every rank (the SPMD drop-in for group.rs:48-50) and
+ *              slices it internally; bases_xy == NULL uses the resident generators Gs[base_off ..].
+ *   AS_DL      ≙ acc::prover / verifier / decider sharded by INSTANCE: succinct checks of instances rank, rank + N, ...
+ *              on each rank's host cores, h(X) = sum alpha^i h_i(X) as per-rank partial coefficient vectors all-gathered
+ *              and added on the device, the decider's commit(h) as a point-range-sharded MSM.  The transcript and the
+ *              opening are sequential and run replicated.  Every rank passes all m instances.
+ *   NTT        batches sharded by POLYNOMIAL; a single transform stays on one GPU.  Every rank passes the whole batch
+ *              and receives the whole result. */
+int halo_dist_unique_id(uint8_t out[128]);
+int halo_dist_init(int rank, int world, const uint8_t nccl_unique_id[128]);
+int halo_dist_shutdown(void);
+/* HALO_ENOINIT when no communicator exists; rank / world may be NULL */
+int halo_dist_info(int* rank, int* world);
+int halo_dist_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_t* scalars, size_t k_local,
+                  uint64_t out_xyz[12]);
+int halo_dist_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k_local,
+                      uint64_t out_xyz[12]);
+int halo_dist_msm_global(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_t* scalars, size_t k,
+                         uint64_t out_xyz[12]);
+/* b <= 64 MSMs over the same local base range, device-resident scalars (b x k_local x 4 words) */
+int halo_dist_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k_local, size_t b,
+                            uint64_t* out_xyz);
+int halo_dist_acc_prover(int curve, const uint64_t* instances, size_t m, uint64_t* out_acc);
+int halo_dist_acc_verifier(int curve, const uint64_t* instances, size_t m, const uint64_t* acc);
+int halo_dist_acc_decider(int curve, const uint64_t* acc);
+int halo_dist_ntt(int field, uint64_t* data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null);
 
 /* ---- NTT / iNTT  ≙ Evals::from_poly* / Evals::interpolate*  (crates/group/src/poly.rs:56-64,133-139) and the direct
  * evaluate_over_domain_by_ref / interpolate calls at crates/plonk/src/plonk/protocol.rs:82-106,140-141,158-159,195.
