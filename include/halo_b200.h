@@ -187,6 +187,19 @@ int halo_poly_mul(int field, const uint64_t* a, size_t la, const uint64_t* b, si
 /* ≙ scalar_dot (group.rs:43-45) and construct_powers (group.rs:58-66): out[i] = z^i, i < n */
 int halo_scalar_dot(int field, const uint64_t* xs, const uint64_t* ys, size_t n, uint64_t out[4]);
 int halo_construct_powers(int field, const uint64_t z[4], size_t n, uint64_t* out);
+/* No counterpart in the reference: added for callers that cannot allocate (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same result as halo_scalar_dot --
+ * out = sum_{i<n} xs[i] * ys[i] in `field` -- with every pointer a DEVICE pointer (d_out: one element, 32 bytes) and
+ * nothing allocated: the per-block partial sums live in a fixed 128 KiB file-scope device array of the library (4096
+ * slots, one per 4096 elements) and the sum is finished on the device.  Two kernel launches on the library's stream
+ * (halo_set_stream); the call returns without synchronising -- order later work on that stream or call
+ * halo_device_synchronize.  The first call on a device looks the array's address up (cudaGetSymbolAddress), so make
+ * it before starting a graph capture.
+ * Limit: n <= 2^24 elements per call; larger n -> HALO_EINVAL (use halo_scalar_dot).
+ * Every call shares the one scratch array, which keeps the previous call's contents (a call reads only the slots it
+ * has written itself, so nothing needs clearing): calls on one stream are ordered, calls that OVERLAP on the GPU
+ * (several streams, concurrent graph launches) race. */
+int halo_scalar_dot_noalloc_dev(int field, const void* d_xs, const void* d_ys, size_t n, void* d_out);
 
 /* ---- PLONK prover / verifier -------------------------------------------------------------------------------
  * ≙ PlonkProof::naive_prover (crates/plonk/src/plonk/protocol.rs:64-355) on what Trace::consume produces
