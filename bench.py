@@ -32,9 +32,14 @@ PALLAS = 0
 P_BASE = 0x40000000000000000000000000000000224698fc094cf91b992d30ed00000001
 Q_SCALAR = 0x40000000000000000000000000000000224698fc0994a8dd8c46eb2100000001
 # XYZZ mixed addition = 8M + 2S (halo_b200/csrc/curve.cuh xyzz_madd); one per (point, window)
-MODMUL_PER_MADD = 10
-# dram__bytes_read.sum + dram__bytes_write.sum of one msm_accumulate launch at 2^20 (profiles/r1b_msm_accumulate_ncu_full.csv)
-TRAFFIC_BYTES_ACCUMULATE_2P20 = 563.4e6
+MADD_MUL, MADD_SQR = 8, 2
+MODMUL_PER_MADD = MADD_MUL + MADD_SQR
+# wide multiplies (IMAD.WIDE.U32) a multiplication / a squaring executes (halo_b200/csrc/field.cuh: 64 + 24, 36 + 24;
+# profiles/r2_sass_histogram.txt counts them in the SASS)
+IMAD_PER_MUL, IMAD_PER_SQR = 88, 60
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel at 2^20, from the ncu --set full
+# capture of the CURRENT kernel named here; None until that capture exists (never a number from older code)
+TRAFFIC_CAPTURE = {"file": None, "bytes_per_launch": None}
 
 
 def parse_args():
@@ -316,6 +321,8 @@ def run_halo(args, rank, world, local_rank):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     halo_b200.init(local_rank)
+    if world > 1:
+        halo_b200.dist.init_torch(dist)      # the library's own NCCL communicator (halo_dist_init); id over torch.distributed
     stream = torch.cuda.Stream()      # torch's default stream has handle 0, which halo_set_stream reads as 'library stream'
     torch.cuda.set_stream(stream)
     check(lib.halo_set_stream(ctypes.c_void_p(stream.cuda_stream)))
@@ -335,40 +342,40 @@ def run_halo(args, rank, world, local_rank):
     h_pts = d_pts.cpu().pin_memory()
     h_sc = d_sc.cpu().pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # 256 MiB > 126 MB L2
-    out = np.zeros(12, dtype=np.uint64)
-    d_part = torch.zeros(12, dtype=torch.int64, device="cuda")
-    gathered = torch.zeros((world, 12), dtype=torch.int64, device="cuda") if world > 1 else None
-
     total = np.zeros(12, dtype=np.uint64)
 
     prof = {"on": False, "ms": {}}
     ms_buf = (ctypes.c_float * 24)()
     nm_buf = (ctypes.c_char_p * 24)()
 
-    def step_dev():
-        check(lib.halo_msm_dev(PALLAS, ctypes.c_void_p(d_pts.data_ptr()), ctypes.c_size_t(0),
-                               ctypes.c_void_p(d_sc.data_ptr()), ctypes.c_size_t(k), out.ctypes.data_as(u64p)))
-        if prof["on"]:                       # per-stage CUDA-event times of THIS MSM (before the combine runs another)
+    def read_stage_profile():
+        if prof["on"]:                       # per-stage CUDA-event times of THIS MSM
             nst = lib.halo_profile_read(ms_buf, nm_buf, 24)
             for j in range(max(nst, 0)):
                 nm = nm_buf[j].decode()
                 prof["ms"][nm] = prof["ms"].get(nm, 0.0) + ms_buf[j]
-        combine()
 
-    def step_e2e():
-        check(lib.halo_msm(PALLAS, ctypes.cast(h_pts.data_ptr(), u64p), ctypes.c_size_t(0),
-                           ctypes.cast(h_sc.data_ptr(), u64p), ctypes.c_size_t(k), out.ctypes.data_as(u64p)))
-        combine()
-
-    def combine():
-        # the real exchange step of a point-range-sharded MSM: one Jacobian point per rank over NCCL, then N adds
+    # N > 1: one call per rank does the whole point-range-sharded MSM inside the library: local Pippenger down to the
+    # window sums, ncclAllGather of them straight from device memory, combine on every rank (halo_dist_msm[_dev])
+    def step_dev():
         if world == 1:
-            total[:] = out
-            return
-        d_part.copy_(torch.from_numpy(out.view(np.int64)))
-        dist.all_gather_into_tensor(gathered, d_part)
-        parts = gathered.cpu().numpy().view(np.uint64).copy()
-        check(lib.halo_point_sum(PALLAS, parts.ctypes.data_as(u64p), ctypes.c_size_t(world), total.ctypes.data_as(u64p)))
+            check(lib.halo_msm_dev(PALLAS, ctypes.c_void_p(d_pts.data_ptr()), ctypes.c_size_t(0),
+                                   ctypes.c_void_p(d_sc.data_ptr()), ctypes.c_size_t(k), total.ctypes.data_as(u64p)))
+        else:
+            check(lib.halo_dist_msm_dev(PALLAS, ctypes.c_void_p(d_pts.data_ptr()), ctypes.c_size_t(0),
+                                        ctypes.c_void_p(d_sc.data_ptr()), ctypes.c_size_t(k), total.ctypes.data_as(u64p)))
+        read_stage_profile()
+
+    def make_step_host(pts_arr_ptr, sc_arr_ptr):
+        def f():
+            fn = lib.halo_msm if world == 1 else lib.halo_dist_msm
+            check(fn(PALLAS, pts_arr_ptr, ctypes.c_size_t(0), sc_arr_ptr, ctypes.c_size_t(k), total.ctypes.data_as(u64p)))
+        return f
+
+    step_e2e = make_step_host(ctypes.cast(h_pts.data_ptr(), u64p), ctypes.cast(h_sc.data_ptr(), u64p))
+    # the same through PAGEABLE host buffers (what a Rust Vec is): the library stages them through pinned chunks
+    pg_pts, pg_sc = h_pts.numpy().copy(), h_sc.numpy().copy()
+    step_e2e_pageable = make_step_host(ctypes.cast(pg_pts.ctypes.data, u64p), ctypes.cast(pg_sc.ctypes.data, u64p))
 
     def barrier():
         if dist is not None:
@@ -404,6 +411,12 @@ def run_halo(args, rank, world, local_rank):
         check(lib.halo_bench_modmul(1, 148 * bps, threads, 400, ctypes.byref(ms), chk))
         peak_modmul = max(peak_modmul, 148 * bps * threads * 400 * 4 / (ms.value * 1e-3))
 
+    peak_imad = 0.0
+    chk1 = (ctypes.c_uint64 * 1)()
+    for threads, bps in ((256, 4), (512, 2)):
+        check(lib.halo_bench_imad(148 * bps, threads, 4000, ctypes.byref(ms), chk1))
+        peak_imad = max(peak_imad, 148 * bps * threads * 4000 * 8 / (ms.value * 1e-3))
+
     # ---- device-resident arm ----
     for _ in range(max(args.warmup, 3)):
         step_dev()
@@ -419,32 +432,116 @@ def run_halo(args, rank, world, local_rank):
     for _ in range(max(args.warmup, 3)):
         step_e2e()
     e2e_ms, _ = timed(step_e2e, args.steps)
-    clocks = sampler.stop() if sampler else None
     result_e2e = total.copy()
+    for _ in range(3):
+        step_e2e_pageable()
+    e2e_pg_ms, _ = timed(step_e2e_pageable, args.steps)
+    clocks = sampler.stop() if sampler else None
+    result_pg = total.copy()
 
-    # ---- verification against the known discrete logs (outside the timed regions) ----
-    t_loc = expected_scalar(d_sc.cpu().numpy().view(np.uint64), seed, first)
-    if dist is not None:
+    # ---- self-consistency check against the known discrete logs (outside the timed regions).  The points are m_i * G, so
+    # the MSM must equal (sum s_i m_i) * G; the right-hand side is a k = 1 MSM of THIS library, hence "self_check": the
+    # independent bit-exact check of a 2^20-point MSM against the oracle is tests/test_msm_gpu.py::test_msm_large_bit_exact
+    # (and the cpu_baseline leg below compares this very result with the oracle's scalar multiplication at N = 1).
+    def all_sum(t_loc):
+        if dist is None:
+            return t_loc
         parts = [None] * world
         dist.all_gather_object(parts, t_loc)
-        t_all = sum(parts) % Q_SCALAR
-    else:
-        t_all = t_loc
-    verified = None
-    if rank == 0:
+        return sum(parts) % Q_SCALAR
+
+    def point_of_scalar(t):
+        """t * G through a k = 1 MSM of the library (gen[0] = m0 * G  =>  t*G = (t / m0) * gen[0])."""
         exp = np.zeros(12, dtype=np.uint64)
         gen = np.zeros((1, 8), dtype=np.uint64)
-        check(lib.halo_gen_points(PALLAS, ctypes.c_uint64(0), ctypes.c_size_t(0), ctypes.c_size_t(1),
-                                  gen.ctypes.data_as(u64p)))
+        check(lib.halo_gen_points(PALLAS, ctypes.c_uint64(0), ctypes.c_size_t(0), ctypes.c_size_t(1), gen.ctypes.data_as(u64p)))
         m0 = int(gen_multipliers(0, 0, 1)[0])
-        # gen[0] = m0 * G  =>  t*G = (t / m0) * gen[0]
-        t_adj = t_all * pow(m0, -1, Q_SCALAR) % Q_SCALAR
+        t_adj = t * pow(m0, -1, Q_SCALAR) % Q_SCALAR
         sc1 = int_to_limbs(t_adj * (1 << 256) % Q_SCALAR).reshape(1, 4)
         check(lib.halo_msm(PALLAS, gen.ctypes.data_as(u64p), ctypes.c_size_t(0), sc1.ctypes.data_as(u64p),
                            ctypes.c_size_t(1), exp.ctypes.data_as(u64p)))
-        verified = bool(jac_equal(result_dev, exp) and jac_equal(result_e2e, exp))
-        if not verified:
+        return exp
+
+    t_all = all_sum(expected_scalar(d_sc.cpu().numpy().view(np.uint64), seed, first))
+    self_check = None
+    if rank == 0:
+        exp = point_of_scalar(t_all)
+        self_check = bool(jac_equal(result_dev, exp) and jac_equal(result_e2e, exp) and jac_equal(result_pg, exp))
+        if not self_check:
             raise SystemExit("bench.py: MSM result does not match the known discrete-log check")
+
+    # ---- STRONG scaling of the headline: ONE MSM of a fixed total size (2^20 and 2^22 points) split by point range over
+    # the N GPUs, device-resident, exchange inside the timed region, CUDA events, max over ranks ----
+    strong = {}
+    if not args.no_path:
+        for lgT in (20, 22):
+            kT = 1 << lgT
+            lo, hi = kT * rank // world, kT * (rank + 1) // world
+            kl = hi - lo
+            s_pts = torch.empty((kl, 8), dtype=torch.int64, device="cuda")
+            check(lib.halo_gen_points_dev(PALLAS, ctypes.c_uint64(seed + 1), ctypes.c_size_t(lo), ctypes.c_size_t(kl),
+                                          ctypes.c_void_p(s_pts.data_ptr())))
+            gs_ = torch.Generator(device="cuda"); gs_.manual_seed(999 + 31 * lgT + rank)
+            s_sc = torch.randint(-(1 << 63), (1 << 63) - 1, (kl, 4), dtype=torch.int64, device="cuda", generator=gs_)
+            s_sc[:, 3] &= (1 << 62) - 1
+            res = np.zeros(12, dtype=np.uint64)
+
+            def step_strong():
+                fn = lib.halo_msm_dev if world == 1 else lib.halo_dist_msm_dev
+                check(fn(PALLAS, ctypes.c_void_p(s_pts.data_ptr()), ctypes.c_size_t(0), ctypes.c_void_p(s_sc.data_ptr()),
+                         ctypes.c_size_t(kl), res.ctypes.data_as(u64p)))
+            for _ in range(3):
+                step_strong()
+            reps = max(5, args.steps // 2)
+            ms_tot, _ = timed(step_strong, reps)
+            t_s = all_sum(expected_scalar(s_sc.cpu().numpy().view(np.uint64), seed + 1, lo))
+            ok = bool(jac_equal(res, point_of_scalar(t_s))) if rank == 0 else None
+            if rank == 0 and not ok:
+                raise SystemExit(f"bench.py: strong-scaling MSM 2^{lgT} fails the discrete-log check")
+            strong[f"msm_2^{lgT}_total"] = {"ms_per_step": ms_tot / reps, "points_per_s": kT * reps / (ms_tot * 1e-3),
+                                            "points_per_gpu": kl, "self_check": ok}
+            del s_pts, s_sc
+
+    # ---- config 5 (BASELINE.json): AS_DL prove + verify + decide over m = 1024 instances of n = 2^16, sharded by instance
+    # at N > 1 (halo_dist_acc_*); wall clock, max over ranks.  The transcript absorbs every challenge of every
+    # instance in ONE serial sponge (acc.rs:157-160), which bounds what sharding can give.
+    acc5 = None
+    if not args.no_path:
+        lg5, m5 = 16, 1024
+        n5 = 1 << lg5
+        g5 = np.zeros((n5 + 2, 8), dtype=np.uint64)
+        check(lib.halo_gen_points(PALLAS, ctypes.c_uint64(99), ctypes.c_size_t(0), ctypes.c_size_t(n5 + 2), g5.ctypes.data_as(u64p)))
+        halo_b200.pp.reset(PALLAS)
+        halo_b200.pp.set_pp(PALLAS, g5[:n5], g5[n5], g5[n5 + 1])
+        rng5 = np.random.default_rng(5)                    # same seed on every rank: identical instances
+
+        def rand_elems(cnt):
+            t = rng5.integers(0, 1 << 63, size=(cnt, 4), dtype=np.uint64)
+            t[:, 3] &= np.uint64((1 << 62) - 1)
+            return t
+        base5 = [halo_b200.pcdl.Instance.open(PALLAS, rand_elems(n5), n5 - 1, rand_elems(1)[0]) for _ in range(32)]
+        qs5 = [base5[i % 32] for i in range(m5)]
+        P5 = (halo_b200.acc.prover, halo_b200.acc.verifier, halo_b200.acc.decider) if world == 1 else \
+             (halo_b200.dist.acc_prover, halo_b200.dist.acc_verifier, halo_b200.dist.acc_decider)
+        best = {}
+
+        def wall(name, fn):
+            barrier()
+            t0 = time.perf_counter(); r = fn(); dt = time.perf_counter() - t0
+            if dist is not None:
+                tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                dt = float(tt.item())
+            best[name] = min(best.get(name, 1e9), dt)
+            return r
+        for _ in range(2):
+            acc_ = wall("prover", lambda: P5[0](PALLAS, qs5))
+            wall("verifier", lambda: P5[1](PALLAS, qs5, acc_))
+            wall("decider", lambda: P5[2](PALLAS, acc_))
+        acc5 = {"m": m5, "log_n": lg5, "prover_ms": best["prover"] * 1e3, "verifier_ms": best["verifier"] * 1e3,
+                "decider_ms": best["decider"] * 1e3, "sharding": "by instance (halo_dist_acc_*)" if world > 1 else "single GPU",
+                "note": "dominated by the protocol's serial Poseidon sponge over all m*(lg n + 1) challenges (host)"}
+        halo_b200.pp.reset(PALLAS)
 
     # whole proofs do not shard (DESIGN.md section 5: replicas only): at N > 1 every rank proves its own 2^log_n-gate
     # circuit at the same time; the time is the max over ranks
@@ -500,11 +597,26 @@ def run_halo(args, rank, world, local_rank):
         ach = modmul / (acc_ms * 1e-3)
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        step_s = tot_ms / args.steps * 1e-3
+        # SURVEY section 8(d)'s canonical model of the WHOLE step (signed 16-bit windows, 11-modmul mixed additions, full
+        # bucket reduction): W_msm(n) = 176 n + 1.68e7 modmul; work per rank
+        model_modmul = 176.0 * k + 1.68e7
+        # executed wide multiplies of the dominant kernel: squarings are 60, not 88
+        imads = (MADD_MUL * IMAD_PER_MUL + MADD_SQR * IMAD_PER_SQR) * k * nw
         roof = {"kernel": "msm_accumulate", "bound": "int32-pipe", "achieved": ach / 1e9, "peak": peak_modmul / 1e9,
-                "unit": "Gmodmul/s", "frac": ach / peak_modmul, "traffic": TRAFFIC_BYTES_ACCUMULATE_2P20 if args.log_n == 20 else None,
-                "traffic_source": "ncu --set full, profiles/r1b_msm_accumulate_ncu_full.csv (dram read + write per launch)",
-                "peak_source": "measured live: halo_bench_modmul (dependent 255-bit Montgomery multiplications)",
+                "unit": "Gmodmul/s", "frac": ach / peak_modmul,
+                "traffic": TRAFFIC_CAPTURE["bytes_per_launch"] if args.log_n == 20 else None,
+                "traffic_source": TRAFFIC_CAPTURE["file"],
+                "peak_source": "measured live: halo_bench_modmul (dependent 255-bit Montgomery multiplications of THIS library, "
+                               "i.e. a ceiling for code built on fe_mul, not the raw pipe: see `pipe`)",
                 "ms_per_launch": acc_ms, "share_of_step": acc_ms / (tot_ms / args.steps),
+                "pipe": {"what": "executed IMAD.WIDE.U32 of the kernel (8 x 88 + 2 x 60 per mixed addition) / raw issue rate",
+                         "achieved": imads / (acc_ms * 1e-3) / 1e12, "peak": peak_imad / 1e12, "unit": "T IMAD.WIDE/s",
+                         "frac": imads / (acc_ms * 1e-3) / peak_imad,
+                         "peak_source": "measured live: halo_bench_imad (8 independent wide multiply-adds per thread)"},
+                "step_frac": {"what": "SURVEY 8(d) model 176 n + 1.68e7 modmul over the whole step / live modmul peak",
+                              "achieved": model_modmul / step_s / 1e9, "peak": peak_modmul / 1e9, "unit": "Gmodmul/s",
+                              "frac": model_modmul / step_s / peak_modmul},
                 "hbm": {"bound": "hbm", "achieved": abytes / (acc_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": abytes / (acc_ms * 1e-3) / 1e9 / hbm_peak,
                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
@@ -515,12 +627,25 @@ def run_halo(args, rank, world, local_rank):
         path = measure_path(lib, check, halo_b200, torch, stream, d_pts, h_sc, args.log_n)
     elif replicas is not None:
         path = {f"plonk_prove_2^{min(args.log_n, 20)}_replicas": replicas}
+    if path is not None:
+        path["strong_scaling"] = strong
+        path[f"asdl_m1024_2^16"] = acc5
+        path["parity_note"] = ("PLONK figures: parity unpinned (the reference stores no proof; GPU == CPU restatement field by "
+                               "field up to 2^16 rows, tests/test_config_sizes_gpu.py); MSM / IPA / AS_DL / NTT: pinned")
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         kk, cores, times = cpu_msm_leg(min(args.log_n, 20), 2)
+        # the checker, in its own leg: t * G by the oracle's scalar multiplication must be the point the timed GPU runs returned
+        import oracle_lib as O_
+        gen_aff = O_.generator(PALLAS)
+        exp_o = O_.point_mul(PALLAS, gen_aff, int_to_limbs(t_all * (1 << 256) % Q_SCALAR))
+        oracle_check = bool(jac_equal(result_dev, np.asarray(exp_o, dtype=np.uint64).reshape(-1)[:12]))
+        if not oracle_check:
+            raise SystemExit("bench.py: the timed MSM result differs from the oracle's t * G")
         cpu = {"value": kk / min(times), "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"best of 2 x MSM of 2^{min(args.log_n, 20)} points, CPU restatement (oracle/msm.hpp), all host threads"}
+        cpu["timed_result_equals_oracle"] = oracle_check
         if not args.no_path:
             cpu["path"] = cpu_path_leg()
 
@@ -529,11 +654,13 @@ def run_halo(args, rank, world, local_rank):
         "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u32x8-montgomery", "data": "synthetic",
         "config": {"workload": f"pallas_msm_2^{args.log_n}_random_points", "log_n": args.log_n, "points_per_gpu": k,
-                   "sharding": "point-range, NCCL all-gather of partial sums" if world > 1 else "single GPU",
+                   "sharding": "point range; window sums all-gathered by the library (halo_dist_msm_dev)" if world > 1 else "single GPU",
                    "l2": "flushed between timed iterations (256 MiB memset outside the event pair)"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(k * 96), "d2h_bytes_per_step": int(nw * 128),
-                "ms_per_step": e2e_ms / args.steps},
-        "gpu_launches": int(launches), "verified": verified, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu, "path": path,
+                "ms_per_step": e2e_ms / args.steps, "host_buffers": "pinned",
+                "pageable": {"value": n_pts * args.steps / (e2e_pg_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_pg_ms / args.steps,
+                             "note": "plain malloc'd buffers (a Rust Vec): staged through pinned chunks by 8 host threads"}},
+        "gpu_launches": int(launches), "self_check": self_check, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu, "path": path,
     }))
     if dist is not None:
         dist.destroy_process_group()

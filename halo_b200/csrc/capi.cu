@@ -36,10 +36,17 @@ int pinned_get(size_t bytes, void** out) {
     return HALO_OK;
 }
 
-int upload_staged(void* d_dst, const void* h_src, size_t bytes) {
+bool host_ptr_is_pageable(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+
+int upload_staged(void* d_dst, const void* h_src, size_t bytes, cudaStream_t order_stream) {
     Runtime& R = rt();
+    if (!order_stream) order_stream = R.stream;
     if (bytes < 4 * Runtime::UP_CHUNK) {
-        HALO_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, R.stream));
+        HALO_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, order_stream));
         return HALO_OK;
     }
     constexpr int T = Runtime::UP_THREADS, SL = Runtime::UP_SLOTS;
@@ -96,7 +103,61 @@ int upload_staged(void* d_dst, const void* h_src, size_t bytes) {
     cudaEventDestroy(go);
     for (int t = 0; t < T; ++t) {
         HALO_CHECK(status[t] == 0, HALO_ECUDA, "staged upload failed");
-        for (int k = 0; k < SL; ++k) HALO_CUDA(cudaStreamWaitEvent(R.stream, R.up_ev[t][k], 0));
+        for (int k = 0; k < SL; ++k) HALO_CUDA(cudaStreamWaitEvent(order_stream, R.up_ev[t][k], 0));
+    }
+    return HALO_OK;
+}
+
+int msm_wait_bases(cudaStream_t st) {
+    Runtime& R = rt();
+    if (R.upload_thread.joinable()) {
+        R.upload_thread.join();
+        HALO_CHECK(R.upload_rc == HALO_OK, HALO_ECUDA, "msm: staged upload of the base points failed");
+    }
+    if (R.wait_copy) { HALO_CUDA(cudaStreamWaitEvent(st, R.copy_done, 0)); R.wait_copy = false; }
+    return HALO_OK;
+}
+void msm_upload_finish() {
+    Runtime& R = rt();
+    if (R.upload_thread.joinable()) R.upload_thread.join();
+    if (R.wait_copy) { cudaStreamSynchronize(R.copy_stream); R.wait_copy = false; }   // error paths: never leave a copy in flight
+}
+int msm_upload_inputs(const uint64_t* bases_xy, size_t base_off, const uint64_t* scalars, size_t k, void** d_s, void** d_b) {
+    Runtime& R = rt();
+    *d_s = nullptr; *d_b = nullptr;
+    if (!k) return HALO_OK;
+    if (int e = ws_get(WS_SCALARS, k * 32, d_s)) return e;
+    const bool staged = k * 32 >= 4 * Runtime::UP_CHUNK && host_ptr_is_pageable(scalars);
+    if (staged) { if (int e = upload_staged(*d_s, scalars, k * 32)) return e; }
+    else HALO_CUDA(cudaMemcpyAsync(*d_s, scalars, k * 32, cudaMemcpyHostToDevice, R.stream));
+    if (!bases_xy) return HALO_OK;
+    // the bases go up on a second stream while the scalar half of the pipeline (digits, scan, scatter, task list)
+    // runs; only the accumulation waits for them.  The previous call has finished (MSM calls are synchronous), so
+    // the workspace is free to overwrite.
+    if (int e = ws_get(WS_BASES, k * 64, d_b)) return e;
+    HALO_CUDA(cudaEventRecord(R.copy_go, R.stream));                 // scalars first: they gate the pipeline
+    HALO_CUDA(cudaStreamWaitEvent(R.copy_stream, R.copy_go, 0));
+    const uint64_t* src = bases_xy + 8 * base_off;
+    if (k * 64 >= 4 * Runtime::UP_CHUNK && host_ptr_is_pageable(src)) {
+        void* dst = *d_b;
+        R.upload_rc = HALO_OK;
+        R.wait_copy = true;
+        try {
+            R.upload_thread = std::thread([dst, src, k]() {
+                Runtime& Q = rt();
+                int rc = cudaSetDevice(Q.device) == cudaSuccess ? HALO_OK : HALO_ECUDA;
+                if (!rc) rc = upload_staged(dst, src, k * 64, Q.copy_stream);
+                if (!rc && cudaEventRecord(Q.copy_done, Q.copy_stream) != cudaSuccess) rc = HALO_ECUDA;
+                Q.upload_rc = rc;
+            });
+        } catch (...) {                                              // no thread to be had: do it inline
+            if (int e = upload_staged(dst, src, k * 64, R.copy_stream)) return e;
+            HALO_CUDA(cudaEventRecord(R.copy_done, R.copy_stream));
+        }
+    } else {
+        HALO_CUDA(cudaMemcpyAsync(*d_b, src, k * 64, cudaMemcpyHostToDevice, R.copy_stream));
+        HALO_CUDA(cudaEventRecord(R.copy_done, R.copy_stream));
+        R.wait_copy = true;
     }
     return HALO_OK;
 }
@@ -614,26 +675,11 @@ int halo_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
     HALO_CHECK(out_xyz && (scalars || k == 0), HALO_EINVAL, "msm: null pointer");
-    Runtime& R = rt();
     void *d_s = nullptr, *d_b = nullptr;
-    if (k) {
-        if (int e = ws_get(WS_SCALARS, k * 32, &d_s)) return e;
-        HALO_CUDA(cudaMemcpyAsync(d_s, scalars, k * 32, cudaMemcpyHostToDevice, R.stream));
-        if (bases_xy) {
-            // the bases go up on a second stream while the scalar half of the pipeline (digits, scan, scatter, task
-            // list) runs; only the accumulation waits for them.  The previous call has finished (MSM calls are
-            // synchronous), so the workspace is free to overwrite.
-            if (int e = ws_get(WS_BASES, k * 64, &d_b)) return e;
-            HALO_CUDA(cudaEventRecord(R.copy_go, R.stream));                 // scalars first: they gate the pipeline
-            HALO_CUDA(cudaStreamWaitEvent(R.copy_stream, R.copy_go, 0));
-            HALO_CUDA(cudaMemcpyAsync(d_b, bases_xy + 8 * base_off, k * 64, cudaMemcpyHostToDevice, R.copy_stream));
-            HALO_CUDA(cudaEventRecord(R.copy_done, R.copy_stream));
-            R.wait_copy = true;
-            base_off = 0;
-        }
-    }
+    if (int e = msm_upload_inputs(bases_xy, base_off, scalars, k, &d_s, &d_b)) { msm_upload_finish(); return e; }
+    if (d_b) base_off = 0;
     int rc = halo_msm_dev(curve, d_b, base_off, d_s, k, out_xyz);
-    if (R.wait_copy) { cudaStreamSynchronize(R.copy_stream); R.wait_copy = false; }   // error paths: never leave a copy in flight
+    msm_upload_finish();
     return rc;
 HALO_API_END
 }

@@ -261,23 +261,11 @@ int halo_dist_msm(int curve, const uint64_t* bases_xy, size_t base_off, const ui
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
     HALO_CHECK(out_xyz && (scalars || k_local == 0), HALO_EINVAL, "dist msm: null pointer");
-    Runtime& R = rt();
     void *d_s = nullptr, *d_b = nullptr;
-    if (k_local) {
-        if (int e = ws_get(WS_SCALARS, k_local * 32, &d_s)) return e;
-        HALO_CUDA(cudaMemcpyAsync(d_s, scalars, k_local * 32, cudaMemcpyHostToDevice, R.stream));
-        if (bases_xy) {
-            if (int e = ws_get(WS_BASES, k_local * 64, &d_b)) return e;
-            HALO_CUDA(cudaEventRecord(R.copy_go, R.stream));
-            HALO_CUDA(cudaStreamWaitEvent(R.copy_stream, R.copy_go, 0));
-            HALO_CUDA(cudaMemcpyAsync(d_b, bases_xy + 8 * base_off, k_local * 64, cudaMemcpyHostToDevice, R.copy_stream));
-            HALO_CUDA(cudaEventRecord(R.copy_done, R.copy_stream));
-            R.wait_copy = true;
-            base_off = 0;
-        }
-    }
+    if (int e = msm_upload_inputs(bases_xy, base_off, scalars, k_local, &d_s, &d_b)) { msm_upload_finish(); return e; }
+    if (d_b) base_off = 0;
     int rc = halo_dist_msm_dev(curve, d_b, base_off, d_s, k_local, out_xyz);
-    if (R.wait_copy) { cudaStreamSynchronize(R.copy_stream); R.wait_copy = false; }
+    msm_upload_finish();
     return rc;
 HALO_API_END
 }

@@ -481,7 +481,7 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     scan_partials<<<1, 256, 0, st>>>(hist, P.L + 1, &meta->ntasks);
     msm_task_emit<<<grid_b, 256, 0, st>>>(counts, P.nb, P.L, hist, tasks);
     prof_mark("tasks");
-    if (R.wait_copy) { HALO_CUDA(cudaStreamWaitEvent(st, R.copy_done, 0)); R.wait_copy = false; }   // bases uploaded on copy_stream
+    if (int e = msm_wait_bases(st)) return e;                                                         // bases uploaded on copy_stream
     msm_accumulate<C><<<(unsigned)((P.max_tasks + 127) / 128), 128, 0, st>>>(d_bases, idx, offsets, counts, tasks, meta,
                                                                            P.L, pslot, buckets, partial,
                                                                            (u32)(P.B * P.nwin), base_stride);
@@ -668,7 +668,7 @@ static int msm_small(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR>*
     u32* d_flag = (u32*)buf;
     XYZZ<C>* d_out = (XYZZ<C>*)(buf + 256);
     if (int e = prof_begin()) return e;
-    if (R.wait_copy) { HALO_CUDA(cudaStreamWaitEvent(st, R.copy_done, 0)); R.wait_copy = false; }   // bases uploaded on copy_stream
+    if (int e = msm_wait_bases(st)) return e;                                                         // bases uploaded on copy_stream
     HALO_CUDA(cudaMemsetAsync(d_flag, 0, 4, st));
     msm_small_kernel<C><<<(unsigned)ncta, SMALL_T, smem, st>>>(d_bases, d_scalars, (u32)k, base_stride, split, chunk, max_bucket,
                                                               d_out, d_flag);

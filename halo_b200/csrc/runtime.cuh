@@ -35,6 +35,11 @@ struct Runtime {
     cudaStream_t copy_stream = nullptr;   // second stream: the base-point upload of halo_msm overlaps the scalar pipeline
     cudaEvent_t copy_done = nullptr, copy_go = nullptr;
     bool wait_copy = false;               // the next MSM must wait for copy_done before touching its bases
+    // pageable caller buffers: the base points are staged to the device by a helper thread while the calling thread
+    // already enqueues the scalar half of the pipeline; joined (all chunks ISSUED, copy_done recorded) right before the
+    // first kernel that reads the bases
+    std::thread upload_thread;
+    int upload_rc = 0;
     ResidentParams pp[2];
     std::vector<DeviceBuf> arena;   // indexed slots
     void* pinned = nullptr;         // pinned host staging
@@ -113,7 +118,15 @@ int pinned_get(size_t bytes, void** out);
 // host -> device copy of a (pageable) caller buffer, ordered after everything already queued on the library stream
 // and complete on that stream when it returns: worker threads stage chunks through pinned memory so the CPU copy
 // and the DMA overlap and several cores feed the link
-int upload_staged(void* d_dst, const void* h_src, size_t bytes);
+int upload_staged(void* d_dst, const void* h_src, size_t bytes, cudaStream_t order_stream = nullptr);
+// true when p is ordinary (pageable, unregistered) host memory, i.e. what a Rust Vec or a numpy array is
+bool host_ptr_is_pageable(const void* p);
+// host scalars (and optionally bases) of an MSM -> the WS_SCALARS / WS_BASES workspaces, bases overlapping the scalar
+// half of the pipeline (see wait_copy / upload_thread); msm_upload_finish joins and clears after the MSM returned
+int msm_upload_inputs(const uint64_t* bases_xy, size_t base_off, const uint64_t* scalars, size_t k, void** d_s, void** d_b);
+void msm_upload_finish();
+// called by the MSM pipelines right before the first kernel that reads the bases
+int msm_wait_bases(cudaStream_t st);
 
 enum WsSlot {
     WS_SCALARS = 0, WS_BASES, WS_COUNTS, WS_OFFSETS, WS_CURSOR, WS_IDX, WS_ORDER, WS_SIZEHIST, WS_BUCKETS,
