@@ -1183,51 +1183,98 @@ static int acc_common(const uint64_t* insts, size_t m, AccCommon<C>* out, bool s
     };
     // Multi-GPU (one process per GPU, SURVEY section 8(e) "ASDL over m instances: by instance"): rank r runs the succinct
     // checks of instances r, r + N, r + 2N, ... on its share of the host's cores; challenge vectors, U's and verdicts
-    // are all-gathered (a few hundred KB), after which every rank runs the same serial sponge below.
+    // are all-gathered block by block (a few hundred KB in all) while rank 0 feeds them to the serial sponge.
     if (sharded && dist_on() && dist_world() > 1) {
+        // Pipelined in blocks of BS instances per rank: the ranks check block b + 1 while the all-gather of block b is
+        // in flight and rank 0's sponge thread is absorbing the blocks before it -- the sponge is one serial chain of
+        // m (lg n + 1) permutations and stays the critical path, as on one GPU; the other ranks spend their cores on
+        // checks only and receive (alpha, z) at the end.
         const size_t W = (size_t)dist_world(), me = (size_t)dist_rank();
-        const size_t per = (m + W - 1) / W, rec = (size_t)(lg_n + 1) * 4 + 12 + 1;      // words per instance record
-        std::vector<uint64_t> mine(per * rec, 0), all(per * rec * W, 0);
-        std::atomic<size_t> nxt{0};
+        const size_t BS = 16, per_blk = W * BS, nblocks = (m + per_blk - 1) / per_blk;
+        const size_t rec = (size_t)(lg_n + 1) * 4 + 12 + 1;                              // words per instance record
+        const size_t ntask = nblocks * BS;                                               // this rank's tasks, in order
+        std::vector<uint64_t> mine(ntask * rec, 0), all(nblocks * per_blk * rec, 0);
+        std::vector<std::atomic<int>> tdone(ntask);
+        for (auto& f : tdone) f.store(0, std::memory_order_relaxed);
+        std::atomic<size_t> nxt{0}, ready{0};                                            // ready: blocks gathered so far
+        std::atomic<int> stop{0};
+        auto inst_of = [&](size_t b, size_t r, size_t j) { return b * per_blk + j * W + r; };
         auto share = [&]() {
             for (;;) {
-                const size_t j = nxt.fetch_add(1, std::memory_order_relaxed);
-                const size_t i = j * W + me;
-                if (j >= per || i >= m) return;
-                const uint64_t* qi = insts + i * iw;
-                uint64_t* r = mine.data() + j * rec;
-                int code = HALO_EREJECT;
-                if ((size_t)qi[12] == d) code = pcdl_succinct_check<C>(qi, r, r + (size_t)(lg_n + 1) * 4);
-                r[rec - 1] = (uint64_t)(int64_t)code;
+                const size_t t = nxt.fetch_add(1, std::memory_order_relaxed);
+                if (t >= ntask || stop.load(std::memory_order_relaxed)) return;
+                const size_t i = inst_of(t / BS, me, t % BS);
+                if (i < m) {
+                    const uint64_t* qi = insts + i * iw;
+                    uint64_t* r = mine.data() + t * rec;
+                    int code = HALO_EREJECT;
+                    if ((size_t)qi[12] == d) code = pcdl_succinct_check<C>(qi, r, r + (size_t)(lg_n + 1) * 4);
+                    r[rec - 1] = (uint64_t)(int64_t)code;
+                }
+                tdone[t].store(1, std::memory_order_release);
             }
         };
-        {
-            const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-            Workers wk;
-            wk.spawn((unsigned)std::min<size_t>(per, std::max<size_t>(1, hw / W)) - 1, share);
-            share();
-            wk.join();
-        }
-        if (int e = dist_allgather_host(mine.data(), all.data(), per * rec * 8)) return e;
+        // rank 0: the serial sponge over gathered blocks, in instance order
         Transcript<C> trs(LABEL_ASDL);
+        auto rec_of = [&](size_t i) {                                                    // record of instance i in `all`
+            const size_t b = i / per_blk, o = i % per_blk;
+            return all.data() + ((b * W + o % W) * BS + o / W) * rec;
+        };
+        auto sponge = [&]() {
+            for (size_t b = 0; b < nblocks; ++b) {
+                while (ready.load(std::memory_order_acquire) <= b) { if (stop.load(std::memory_order_relaxed)) return; std::this_thread::yield(); }
+                for (size_t i = b * per_blk; i < std::min(m, (b + 1) * per_blk); ++i) {
+                    const Fe<S>* x = (const Fe<S>*)rec_of(i);
+                    for (unsigned k = 0; k <= lg_n; ++k) trs.absorb_scalar(x[k]);
+                }
+            }
+        };
+        const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        const size_t cores = std::max<size_t>(1, hw / W);
+        Workers wk, sp;
+        if (me == 0) sp.spawn(1, sponge);
+        const bool own_sponge_inline = me == 0 && sp.size() == 0;
+        wk.spawn((unsigned)std::max<size_t>(1, cores > (me == 0 ? 2u : 1u) ? cores - (me == 0 ? 2 : 1) : 1), share);
+        int bad_code = 0;
+        int gather_rc = HALO_OK;
+        for (size_t b = 0; b < nblocks && !bad_code && !gather_rc; ++b) {
+            for (size_t j = 0; j < BS; ++j)
+                while (!tdone[b * BS + j].load(std::memory_order_acquire)) { if (wk.size() == 0) share(); else std::this_thread::yield(); }
+            gather_rc = dist_allgather_host(mine.data() + b * BS * rec, all.data() + b * per_blk * rec, BS * rec * 8);
+            if (gather_rc) break;
+            for (size_t i = b * per_blk; i < std::min(m, (b + 1) * per_blk) && !bad_code; ++i)
+                bad_code = (int)(int64_t)rec_of(i)[rec - 1];
+            if (!bad_code) ready.store(b + 1, std::memory_order_release);
+        }
+        if (bad_code || gather_rc) stop.store(1, std::memory_order_relaxed);
+        wk.join();
+        if (own_sponge_inline && !bad_code && !gather_rc) sponge();
+        sp.join();
+        if (gather_rc) return gather_rc;
+        if (bad_code) { last_err() = "acc: an instance failed its succinct check (sharded)"; return bad_code; }
         for (size_t i = 0; i < m; ++i) {
-            const uint64_t* r = all.data() + ((i % W) * per + i / W) * rec;
-            const int code = (int)(int64_t)r[rec - 1];
-            if (code) { last_err() = "acc: an instance failed its succinct check (sharded)"; return code; }
+            const uint64_t* r = rec_of(i);
             memcpy(out->xis.data() + i * (lg_n + 1), r, (size_t)(lg_n + 1) * 32);
             memcpy(Us.data() + 12 * i, r + (size_t)(lg_n + 1) * 4, 96);
-            for (unsigned k = 0; k <= lg_n; ++k) trs.absorb_scalar(out->xis[i * (lg_n + 1) + k]);
         }
-        lap("sharded succinct checks + gather + sponge");
-        for (size_t i = 0; i < m; ++i) trs.absorb_point(H::from_words(Us.data() + 12 * i));
-        const SF alpha = trs.challenge();
+        lap("sharded succinct checks + gathers + sponge");
+        // alpha and z come from rank 0's transcript (z is the next squeeze after alpha, as in the single-GPU path below)
+        SF az[2] = {fe_zero<S>(), fe_zero<S>()};
+        if (me == 0) {
+            for (size_t i = 0; i < m; ++i) trs.absorb_point(H::from_words(Us.data() + 12 * i));
+            az[0] = trs.challenge();
+            az[1] = trs.challenge();
+        }
+        std::vector<SF> gath(2 * W);
+        if (int e = dist_allgather_host(az, gath.data(), 64)) return e;
+        const SF alpha = gath[0];
+        out->z = gath[1];
         out->alphas.resize(m);
         SF cur = fe_one<S>();
         for (size_t i = 0; i < m; ++i) { out->alphas[i] = cur; cur = fe_mul<S>(cur, alpha); }
         uint64_t Cw[12];
         if (int e = halo_msm_proj(C, Us.data(), (const uint64_t*)out->alphas.data(), m, Cw)) return e;
         out->Cbar = H::from_words(Cw);
-        out->z = trs.challenge();
         return HALO_OK;
     }
     // 4. m independent succinct checks (each sequential inside) on worker threads that take the instances in
