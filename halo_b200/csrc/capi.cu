@@ -265,6 +265,17 @@ __global__ void field_op_kernel(int op, const Fe<F>* a, const Fe<F>* b, Fe<F>* o
     o[i] = r;
 }
 
+// ---- SASS probes: one multiplication / one squaring per thread and nothing else, so that `cuobjdump -sass` shows the
+// instruction mix of fe_mul / fe_sqr in isolation (tools/sass_histogram.py -> profiles/).  Never launched.
+template <int F> __global__ void sass_probe_mul(const Fe<F>* a, const Fe<F>* b, Fe<F>* o) {
+    o[threadIdx.x] = fe_mul<F>(a[threadIdx.x], b[threadIdx.x]);
+}
+template <int F> __global__ void sass_probe_sqr(const Fe<F>* a, Fe<F>* o) {
+    o[threadIdx.x] = fe_sqr<F>(a[threadIdx.x]);
+}
+template __global__ void sass_probe_mul<1>(const Fe<1>*, const Fe<1>*, Fe<1>*);
+template __global__ void sass_probe_sqr<1>(const Fe<1>*, Fe<1>*);
+
 // ---- arithmetic micro-benchmarks ----
 template <int F>
 __global__ void bench_modmul_kernel(int iters, Fe<F>* out) {
@@ -637,7 +648,7 @@ int halo_gen_points(int curve, uint64_t seed, size_t first, size_t n, uint64_t* 
 HALO_API_END
 }
 
-int halo_set_tuning(int key, int value) { HALO_API_BEGIN LOCK(); if (key < 0 || key >= 8) return HALO_EINVAL; rt().tune[key] = value; return HALO_OK; HALO_API_END }
+int halo_set_tuning(int key, int value) { HALO_API_BEGIN LOCK(); if (key < 0 || key >= 16) return HALO_EINVAL; rt().tune[key] = value; return HALO_OK; HALO_API_END }
 int halo_msm_set_window(int c) { HALO_API_BEGIN LOCK(); rt().msm_window_override = c; return HALO_OK; HALO_API_END }
 
 int halo_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const void* d_scalars, size_t k, uint64_t out_xyz[12]) { HALO_API_BEGIN

@@ -274,6 +274,257 @@ __global__ void __launch_bounds__(128, 4) msm_accumulate(const Affine<C>* __rest
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// 5b. bucket accumulation with BATCHED AFFINE additions (large problems).  An affine addition costs 1 inversion +
+//     2M + 1S; Montgomery's trick shares one inversion among the independent additions of a batch at 3M each, so an
+//     addition is 5M + 1S = 6 multiplications instead of the 8M + 2S of the XYZZ mixed addition -- provided the
+//     inversion is cheap and the batch large.  The inversion is fe_inv_safegcd (~1/5 of a Fermat ladder); the batch
+//     is built per THREAD: a thread owns G consecutive positions of the bucket-sorted index array (whatever buckets
+//     they belong to) and reduces every bucket segment in it pairwise, round after round: round 0 adds positions
+//     (0,1), (2,3), ... of each segment, round 1 the results, and so on -- G/2, G/4, ... independent additions per
+//     round, one inversion per round.  When a round would have fewer than BA_MIN_PAIRS additions the inversion no
+//     longer pays and the remaining few items per segment are added with XYZZ mixed additions.  Intermediate points
+//     live in a thread-private, lane-interleaved scratch (a warp's accesses to slot q are one contiguous run).
+//     A segment that is a whole bucket goes to the bucket array; a bucket that continues across a thread boundary
+//     leaves "head" / "tail" partial sums, added up by msm_ba_fixup.  Every case of the group law is handled
+//     (identity inputs, P + P, P - P): the reference's generator set is duplicate-heavy.
+//     No thread owns more than G points whatever the scalar distribution, so the task list is not needed.
+//     MEASURED (profiles/r2g_msm_accumulate_ba_ncu.txt): correct on every edge case, but slower than the task path on
+//     this field -- 3.17 ms vs 2.56 ms at 2^20 points.  32 % fewer wide multiplies, yet only 13 % fewer instructions
+//     (inversions, planning, the second pass over the operands), 3.3 warps per scheduler, and every addition waits
+//     for operands it has just requested (long-scoreboard 2.5 stalls per issue) where the task path prefetches its
+//     next base.  Kept as an opt-in path (tuning key 8); the default is the task path.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int BA_T = 128;                 // threads per CTA
+constexpr u32 BA_MAX_G = 256;             // positions per thread (masks are 256 bits)
+constexpr u32 BA_MIN_PAIRS = 24;          // below this an inversion (~50 multiplications) costs more than it saves
+
+__device__ __forceinline__ u32 upper_bound_u32(const u32* __restrict__ a, u32 n, u32 v) {   // first i with a[i] > v
+    u32 lo = 0, hi = n;
+    while (lo < hi) { const u32 mid = (lo + hi) >> 1; if (__ldg(a + mid) <= v) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+template <int F> __device__ __forceinline__ Fe<F> ld_fe_plain(const Fe<F>* p) {       // scratch written by this kernel: no __ldg
+    Fe<F> r;
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    const uint4 a = q[0], b = q[1];
+    r.l[0] = a.x; r.l[1] = a.y; r.l[2] = a.z; r.l[3] = a.w; r.l[4] = b.x; r.l[5] = b.y; r.l[6] = b.z; r.l[7] = b.w;
+    return r;
+}
+// denominator of P1 + P2 and the case: 0 = chord (x2 - x1), 1 = tangent (2 y1), 2 = no inversion needed (an identity
+// input, or P + (-P))
+template <int C>
+__device__ __forceinline__ int ba_pair_case(const Affine<C>& p1, const Affine<C>& p2, Fe<CurveTraits<C>::BASE>& den) {
+    constexpr int B = CurveTraits<C>::BASE;
+    if (affine_is_identity<C>(p1) || affine_is_identity<C>(p2)) { den = fe_one<B>(); return 2; }
+    if (fe_eq<B>(p1.x, p2.x)) {
+        if (fe_eq<B>(p1.y, p2.y)) { den = fe_dbl<B>(p1.y); return 1; }     // y != 0: the curves have no point of order 2
+        den = fe_one<B>();
+        return 2;
+    }
+    den = fe_sub<B>(p2.x, p1.x);
+    return 0;
+}
+
+template <int C>
+__global__ void __launch_bounds__(BA_T, 4) msm_accumulate_ba(const Affine<C>* __restrict__ bases, const u32* __restrict__ idx,
+                                                             const u32* __restrict__ offsets, const u32* __restrict__ counts,
+                                                             u32 nb, u32 G, Affine<C>* Wbase, Fe<CurveTraits<C>::BASE>* Pbase,
+                                                             XYZZ<C>* __restrict__ buckets, XYZZ<C>* __restrict__ head,
+                                                             XYZZ<C>* __restrict__ tail) {
+    constexpr int B = CurveTraits<C>::BASE;
+    __shared__ u32 s_mask[8][BA_T], s_new[8][BA_T], s_pair[8][BA_T];     // per-thread 256-bit masks, conflict-free columns
+    const u32 tid = threadIdx.x, lane = tid & 31u;
+    const u32 total = __ldg(offsets + nb - 1) + __ldg(counts + nb - 1);
+    const u32 per_chunk = BA_T * G;
+    const u32 nchunks = (u32)(((u64)total + per_chunk - 1) / per_chunk);
+    const size_t warp_id = (size_t)blockIdx.x * (BA_T / 32) + (tid >> 5);
+    Affine<C>* W = Wbase + warp_id * (size_t)G * 32 + lane;               // slot q of this thread: W[q * 32]
+    Fe<B>* P = Pbase + warp_id * (size_t)(G / 2) * 32 + lane;             // prefix product of pair j: P[j * 32]
+#define BA_BIT(m, i) ((m[(i) >> 5][tid] >> ((i) & 31u)) & 1u)
+#define BA_SET(m, i) (m[(i) >> 5][tid] |= 1u << ((i) & 31u))
+    for (u32 chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
+        const u32 vt = chunk * BA_T + tid;                                // virtual thread: positions [vt G, vt G + G)
+        const u64 p0w = (u64)vt * G;
+        if (p0w >= total) continue;
+        const u32 p0 = (u32)p0w, p1 = (u32)(p0w + G < total ? p0w + G : total);
+        store_xyzz(head + vt, xyzz_identity<C>());
+        store_xyzz(tail + vt, xyzz_identity<C>());
+        const u32 b0 = upper_bound_u32(offsets, nb, p0) - 1u;             // the (non-empty) bucket holding position p0
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s_mask[w][tid] = 0u;
+        s_mask[0][tid] = 1u;
+        for (u32 b = b0 + 1; b < nb; ++b) {                               // segment starts inside (p0, p1)
+            const u32 o = __ldg(offsets + b);
+            if (o >= p1) break;
+            BA_SET(s_mask, o - p0);
+        }
+        u32 n = p1 - p0, round = 0;
+        auto load_pt = [&](u32 a) -> Affine<C> {
+            Affine<C> pt;
+            if (round == 0) {
+                const u32 e = __ldg(idx + p0 + a);
+                pt = load_affine(bases + (e & 0x7fffffffu));
+                if (e >> 31) pt.y = fe_neg<B>(pt.y);                      // -(0,0) stays (0,0)
+            } else {
+                pt.x = ld_fe_plain(&W[(size_t)a * 32].x); pt.y = ld_fe_plain(&W[(size_t)a * 32].y);
+            }
+            return pt;
+        };
+        for (;;) {
+            // plan the round: output slot q takes items (a, a+1) of one segment, or a lone last item
+#pragma unroll
+            for (int w = 0; w < 8; ++w) { s_new[w][tid] = 0u; s_pair[w][tid] = 0u; }
+            u32 np = 0, q = 0, a = 0;
+            while (a < n) {
+                const bool pr = a + 1 < n && !BA_BIT(s_mask, a + 1);
+                if (BA_BIT(s_mask, a)) BA_SET(s_new, q);
+                if (pr) { BA_SET(s_pair, q); ++np; }
+                a += 1u + (pr ? 1u : 0u);
+                ++q;
+            }
+            const u32 nout = q;
+            if (np < BA_MIN_PAIRS) break;
+            // pass 1, slots in descending order: prefix products of the denominators
+            Fe<B> run = fe_one<B>();
+            u32 j = 0;
+            a = n;
+            for (q = nout; q-- > 0;) {
+                const bool pr = BA_BIT(s_pair, q) != 0u;
+                a -= 1u + (pr ? 1u : 0u);
+                if (!pr) continue;
+                Fe<B> den;
+                Fe<B> x1, x2;
+                if (round == 0) {
+                    x1 = load_fe(&bases[__ldg(idx + p0 + a) & 0x7fffffffu].x);
+                    x2 = load_fe(&bases[__ldg(idx + p0 + a + 1) & 0x7fffffffu].x);
+                } else {
+                    x1 = ld_fe_plain(&W[(size_t)a * 32].x); x2 = ld_fe_plain(&W[(size_t)(a + 1) * 32].x);
+                }
+                if (fe_eq<B>(x1, x2) || fe_is_zero<B>(x1) || fe_is_zero<B>(x2)) {          // rare: look at the whole points
+                    const Affine<C> q1 = load_pt(a), q2 = load_pt(a + 1);
+                    ba_pair_case<C>(q1, q2, den);
+                } else den = fe_sub<B>(x2, x1);
+                store_fe(&P[(size_t)j * 32], run);
+                run = fe_mul<B>(run, den);
+                ++j;
+            }
+            Fe<B> inv = fe_inv_safegcd<B>(run);
+            // pass 2, ascending: 1/den_j = inv * prefix_j, then inv *= den_j; results overwrite the scratch in place
+            // (slot q <= first input a of every slot, so nothing still needed is overwritten)
+            a = 0;
+            for (q = 0; q < nout; ++q) {
+                const bool pr = BA_BIT(s_pair, q) != 0u;
+                if (!pr) {
+                    if (round == 0 || a != q) {
+                        const Affine<C> pt = load_pt(a);
+                        store_fe(&W[(size_t)q * 32].x, pt.x); store_fe(&W[(size_t)q * 32].y, pt.y);
+                    }
+                    a += 1;
+                    continue;
+                }
+                --j;
+                const Affine<C> q1 = load_pt(a), q2 = load_pt(a + 1);
+                Fe<B> den;
+                const int cs = ba_pair_case<C>(q1, q2, den);
+                Affine<C> r;
+                if (cs == 2) {
+                    if (affine_is_identity<C>(q1)) r = q2;
+                    else if (affine_is_identity<C>(q2)) r = q1;
+                    else { r.x = fe_zero<B>(); r.y = fe_zero<B>(); }
+                } else {
+                    const Fe<B> dinv = fe_mul<B>(inv, ld_fe_plain(&P[(size_t)j * 32]));
+                    inv = fe_mul<B>(inv, den);
+                    Fe<B> num;
+                    if (cs == 0) num = fe_sub<B>(q2.y, q1.y);
+                    else { const Fe<B> xx = fe_sqr<B>(q1.x); num = fe_add<B>(fe_dbl<B>(xx), xx); }
+                    const Fe<B> lam = fe_mul<B>(num, dinv);
+                    r.x = fe_sub<B>(fe_sub<B>(fe_sqr<B>(lam), q1.x), q2.x);
+                    r.y = fe_sub<B>(fe_mul<B>(lam, fe_sub<B>(q1.x, r.x)), q1.y);
+                }
+                store_fe(&W[(size_t)q * 32].x, r.x); store_fe(&W[(size_t)q * 32].y, r.y);
+                a += 2;
+            }
+#pragma unroll
+            for (int w = 0; w < 8; ++w) s_mask[w][tid] = s_new[w][tid];
+            n = nout;
+            ++round;
+        }
+        // the few items left per segment: XYZZ mixed additions, then out to the bucket / the boundary partial sums
+        {
+            XYZZ<C> acc = xyzz_identity<C>();
+            u32 b = b0;
+            bool first = true;
+            auto flush = [&](bool last) {
+                const u32 ob = __ldg(offsets + b);
+                const bool is_head = first && ob < p0;
+                const bool is_tail = last && (u64)ob + __ldg(counts + b) > (u64)p1;
+                store_xyzz(is_head ? head + vt : is_tail ? tail + vt : buckets + b, acc);
+            };
+            for (u32 a = 0; a < n; ++a) {
+                if (a > 0 && BA_BIT(s_mask, a)) {
+                    flush(false);
+                    first = false;
+                    do { ++b; } while (__ldg(counts + b) == 0u);
+                    acc = xyzz_identity<C>();
+                }
+                const Affine<C> pt = load_pt(a);
+                xyzz_madd<C>(acc, pt, false);
+            }
+            flush(true);
+        }
+    }
+#undef BA_BIT
+#undef BA_SET
+}
+
+template <int C> __device__ __forceinline__ XYZZ<C> xyzz_shfl_down(const XYZZ<C>& v, int d);
+template <int C> __device__ __forceinline__ XYZZ<C> warp_sum_xyzz(XYZZ<C> acc, u32 live);
+// Thread boundaries v*G inside a bucket: the bucket is tail[v-1] + head[v] + ... + head[last].  Only the FIRST boundary
+// inside a bucket acts.  The sum is almost always two terms: one THREAD per boundary adds runs of up to BA_FIX_SHORT
+// terms; longer runs (skewed scalar distributions: a bucket spanning many threads) are queued for msm_ba_fixup_long,
+// one warp per run.
+constexpr u32 BA_FIX_SHORT = 8;
+template <int C>
+__global__ void __launch_bounds__(128) msm_ba_fixup(const u32* __restrict__ offsets, const u32* __restrict__ counts, u32 nb, u32 G,
+                                                    const XYZZ<C>* __restrict__ head, const XYZZ<C>* __restrict__ tail,
+                                                    XYZZ<C>* __restrict__ buckets, u32* __restrict__ nlong, u32* __restrict__ longs) {
+    const u32 total = __ldg(offsets + nb - 1) + __ldg(counts + nb - 1);
+    const u32 VT = (u32)(((u64)total + G - 1) / G);
+    const u64 v = (u64)blockIdx.x * blockDim.x + threadIdx.x + 1;
+    if (v >= VT) return;
+    const u64 pos = v * G;
+    const u32 b = upper_bound_u32(offsets, nb, (u32)(pos - 1)) - 1u;      // bucket holding the position before the boundary
+    const u64 ob = __ldg(offsets + b), end = ob + __ldg(counts + b);
+    if (end <= pos) return;                                               // the bucket ends at the boundary
+    if (ob < (v - 1) * G) return;                                         // an earlier boundary lies inside it too
+    const u64 last = (end - 1) / G;
+    if (last - (v - 1) + 1 > BA_FIX_SHORT) { longs[atomicAdd(nlong, 1u)] = (u32)v; return; }
+    XYZZ<C> acc = load_xyzz(tail + (v - 1));
+    for (u64 u = v; u <= last; ++u) { const XYZZ<C> x = load_xyzz(head + u); xyzz_add<C>(acc, x); }
+    store_xyzz(buckets + b, acc);
+}
+template <int C>
+__global__ void __launch_bounds__(128) msm_ba_fixup_long(const u32* __restrict__ offsets, const u32* __restrict__ counts, u32 nb, u32 G,
+                                                         const XYZZ<C>* __restrict__ head, const XYZZ<C>* __restrict__ tail,
+                                                         XYZZ<C>* __restrict__ buckets, const u32* __restrict__ nlong,
+                                                         const u32* __restrict__ longs) {
+    const u32 lane = threadIdx.x & 31u;
+    const u32 nwarps = gridDim.x * (blockDim.x >> 5), n = *nlong;
+    for (u32 w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w < n; w += nwarps) {
+        const u64 v = longs[w], pos = v * G;
+        const u32 b = upper_bound_u32(offsets, nb, (u32)(pos - 1)) - 1u;
+        const u64 end = (u64)__ldg(offsets + b) + __ldg(counts + b), last = (end - 1) / G;
+        XYZZ<C> acc = xyzz_identity<C>();
+        for (u64 u = v - 1 + lane; u <= last; u += 32) {
+            const XYZZ<C> x = load_xyzz(u == v - 1 ? tail + u : head + u);
+            xyzz_add<C>(acc, x);
+        }
+        acc = warp_sum_xyzz<C>(acc, 32u);
+        if (lane == 0) store_xyzz(buckets + b, acc);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // 6. multi-task buckets: one warp adds the partial results of one bucket
 // ---------------------------------------------------------------------------------------------------------
 template <int C> __device__ __forceinline__ XYZZ<C> xyzz_shfl_down(const XYZZ<C>& v, int d) {
@@ -398,6 +649,7 @@ struct MsmPlan {
     size_t B, nb;         // buckets per window, total buckets
     u32 L;                // max points per task
     size_t max_tasks, max_partial;
+    u32 ba_G;             // > 0: batched-affine accumulation with this many positions per thread (5b)
 };
 static MsmPlan make_plan(size_t k, size_t nbatch) {
     MsmPlan p;
@@ -416,6 +668,11 @@ static MsmPlan make_plan(size_t k, size_t nbatch) {
     }
     p.max_tasks = p.nb + work / p.L + 1;
     p.max_partial = 2 * (work / p.L) + 2;
+    // Batched-affine accumulation is OPT-IN (tuning key 8 = 64 / 128 / 256 positions per thread): measured on B200 at
+    // 2^20 points it takes 3.17 ms against 2.56 ms for the XYZZ task path (only 13 % fewer
+    // instructions per addition on this 255-bit field, and latency-bound where the task path is pipe-bound).
+    const int t8 = rt().tune[8];
+    p.ba_G = (t8 == 64 || t8 == 128 || t8 == 256) ? (u32)t8 : 0u;
     return p;
 }
 
@@ -457,8 +714,11 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     big = cbase + P.nb;
     chunks = (uint2*)(big + P.nb);
     if (int e = ws_get(WS_BUCKETS, P.nb * sizeof(XYZZ<C>), (void**)&buckets)) return e;
-    if (int e = ws_get(WS_TMP3, 2 * P.max_partial * sizeof(XYZZ<C>), (void**)&partial)) return e;
-    partial2 = partial + P.max_partial;
+    partial = partial2 = nullptr;
+    if (!P.ba_G) {
+        if (int e = ws_get(WS_TMP3, 2 * P.max_partial * sizeof(XYZZ<C>), (void**)&partial)) return e;
+        partial2 = partial + P.max_partial;
+    }
     // tree reduction: main ping-pong (nb/2, nb/4) and pending ping-pong (nb/2 each)
     const size_t half = P.nb / 2 + P.nwt;
     if (int e = ws_get(WS_SEGSUM, (half + half / 2 + 1) * sizeof(XYZZ<C>), (void**)&lvl[0])) return e;
@@ -477,6 +737,27 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     prof_mark("scan");
     msm_scatter<SF><<<grid_pts, 256, 0, st>>>(d_scalars, k, total, P.c, P.nwin, cursor, idx);
     prof_mark("scatter");
+    if (P.ba_G) {
+        // batched-affine accumulation (5b): persistent grid, scratch per resident warp
+        const unsigned grid = (unsigned)R.sm_count * 4;
+        const size_t warps = (size_t)grid * (BA_T / 32);
+        Affine<C>* W; Fe<CurveTraits<C>::BASE>* Pp; XYZZ<C>* head;
+        if (int e = ws_get(WS_BA_W, warps * P.ba_G * 32 * sizeof(Affine<C>), (void**)&W)) return e;
+        if (int e = ws_get(WS_BA_P, warps * (P.ba_G / 2) * 32 * 32, (void**)&Pp)) return e;
+        const size_t vt_max = (P.nwt * k + P.ba_G - 1) / P.ba_G + 1;
+        if (int e = ws_get(WS_TMP3, 2 * vt_max * sizeof(XYZZ<C>), (void**)&head)) return e;
+        HALO_CUDA(cudaMemsetAsync(buckets, 0, P.nb * sizeof(XYZZ<C>), st));          // empty buckets are the identity
+        prof_mark("tasks");
+        if (int e = msm_wait_bases(st)) return e;                                     // bases uploaded on copy_stream
+        msm_accumulate_ba<C><<<grid, BA_T, 0, st>>>(d_bases, idx, offsets, counts, (u32)P.nb, P.ba_G, W, Pp, buckets, head, head + vt_max);
+        prof_mark("accumulate");
+        // the queue of long runs: counter in the zero-filled meta block, entries in the (otherwise unused) `big` array
+        msm_ba_fixup<C><<<(unsigned)((vt_max + 127) / 128), 128, 0, st>>>(offsets, counts, (u32)P.nb, P.ba_G, head, head + vt_max, buckets,
+                                                                        &meta->nbig, big);
+        msm_ba_fixup_long<C><<<R.sm_count, 128, 0, st>>>(offsets, counts, (u32)P.nb, P.ba_G, head, head + vt_max, buckets, &meta->nbig, big);
+        prof_mark("fixup");
+        R.launches += 6;
+    } else {
     msm_task_hist<<<grid_b, 256, 0, st>>>(counts, P.nb, P.L, hist, meta, pslot, cbase, chunks, big);
     scan_partials<<<1, 256, 0, st>>>(hist, P.L + 1, &meta->ntasks);
     msm_task_emit<<<grid_b, 256, 0, st>>>(counts, P.nb, P.L, hist, tasks);
@@ -490,6 +771,7 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     msm_fixup2<C><<<R.sm_count, 128, 0, st>>>(big, meta, counts, cbase, P.L, partial2, buckets);
     prof_mark("fixup");
     R.launches += 8;
+    }
     // bucket reduction: c-1 tree levels, then the per-window combine
     {
         const XYZZ<C>*m_in = buckets, *p_in = nullptr;
@@ -721,6 +1003,7 @@ int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbat
         if (done) return HALO_OK;
     }
     MsmPlan P = make_plan(k, nbatch);
+    if (base_stride) P.ba_G = 0;                          // per-MSM base sets (the IPA's L/R pair): task path
     HALO_CHECK(P.nwt * k < ((size_t)1 << 32), HALO_EINVAL, "msm: batch too large (nbatch*nwin*k must be < 2^32)");
     XYZZ<C>* d_win = nullptr;
     if (int e = msm_enqueue<C>((const Affine<C>*)d_bases, (const Fe<CurveTraits<C>::SCALAR>*)d_scalars, k, P, base_stride, &d_win)) return e;
@@ -748,6 +1031,7 @@ int msm_windows_device(const void* d_bases, const void* d_scalars, size_t k, siz
                        void** d_winsum, int* c_out, int* nwin_out) {
     HALO_CHECK(k > 0 && k < ((size_t)1 << 31), HALO_EINVAL, "msm: k must be in [1, 2^31)");
     MsmPlan P = make_plan(k, nbatch);
+    if (base_stride) P.ba_G = 0;
     HALO_CHECK(P.nwt * k < ((size_t)1 << 32), HALO_EINVAL, "msm: batch too large (nbatch*nwin*k must be < 2^32)");
     XYZZ<C>* d_win = nullptr;
     if (int e = msm_enqueue<C>((const Affine<C>*)d_bases, (const Fe<CurveTraits<C>::SCALAR>*)d_scalars, k, P, base_stride, &d_win)) return e;

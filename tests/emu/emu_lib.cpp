@@ -20,6 +20,7 @@ template <int F> static void binop(int op, const u64* a, const u64* b, u64* o, s
             case 3: r = fe_inv<F>(x); break;
             case 4: r = fe_to_canonical<F>(x); break;
             case 5: r = fe_from_canonical<F>(x); break;
+            case 7: r = fe_inv_safegcd<F>(x); break;
             default: r = fe_sqr<F>(x);
         }
         memcpy(o + 4 * i, r.l, 32);

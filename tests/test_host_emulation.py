@@ -110,3 +110,26 @@ def test_curve_ops(emu, oracle, curve):
     kc = O.field_to_canonical(sfield, k)
     emu.emu_mul(curve, _p(np.ascontiguousarray(a)), _p(kc), _p(o_xyz))
     assert (O.point_to_affine(curve, o_xyz) == O.point_to_affine(curve, O.point_mul(curve, a, k[0]))).all()
+
+
+@pytest.mark.parametrize("field", [0, 1])
+def test_safegcd_inversion(emu, oracle, field):
+    """fe_inv_safegcd (divsteps on 30-bit limbs, the inversion of the batched-affine bucket accumulation) against the
+    oracle's Fermat inverse: random elements, the edges of the range, small values and powers of two; 0 -> 0."""
+    O = oracle
+    p = O.MODULUS[field]
+    n = 4000
+    a = O.random_scalars(field, n, 777 + field)
+    ints = [0, 1, 2, 3, p - 1, p - 2, (p - 1) // 2, (p + 1) // 2, (1 << 254) - 1, 1 << 253, (1 << 30) - 1, 1 << 30, (1 << 30) + 1]
+    ints += [1 << k for k in range(0, 254, 7)] + [p - (1 << k) for k in range(0, 254, 11)]
+    edge = O.ints_to_mont(field, ints)
+    raw = np.array([O.int_to_limbs(x) for x in ints], dtype=np.uint64)      # the same integers as raw limb patterns
+    a[: len(edge)] = edge
+    a[len(edge): 2 * len(edge)] = raw
+    out = np.empty_like(a)
+    emu.emu_field_op(field, 7, _p(a), _p(a), _p(out), ctypes.c_size_t(n))
+    assert (out == O.field_inv(field, a)).all(), np.flatnonzero((out != O.field_inv(field, a)).any(axis=1))[:10]
+    one = O.ints_to_mont(field, [1])[0]
+    nz = a.any(axis=1)
+    assert (O.field_mul(field, a[nz], out[nz]) == one).all()
+    assert (out[~nz] == 0).all()

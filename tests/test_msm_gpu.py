@@ -256,3 +256,51 @@ def test_msm_beyond_oracle_sizes_known_discrete_logs(hb, oracle, curve, log_k):
     t = int((vals * ms.astype(object)).sum()) % r * pow(1 << 256, -1, r) % r
     exp = O.point_mul(curve, O.generator(curve), O.ints_to_mont(sf, [t])[0])
     assert (_aff(O, curve, got) == _aff(O, curve, exp)).all()
+
+
+@pytest.mark.parametrize("curve", [0, 1])
+@pytest.mark.parametrize("G", [64, 128, 256])
+def test_msm_batched_affine_path_forced(hb, oracle, curve, G):
+    """The batched-affine bucket accumulation (msm_accumulate_ba, tuning key 8) forced at sizes the oracle handles, on the
+    inputs that exercise every case of the affine group law inside a batch: identity bases, duplicates (P + P),
+    negated pairs with equal scalars (P - P), all-equal scalars (one bucket per window, spanning many thread
+    boundaries: head / tail partial sums), tiny scalars, ragged sizes around the per-thread range.  Results must equal
+    the oracle's and the task path's bit for bit."""
+    O = oracle
+    lib = hb._lib.lib
+    sf, bf = O.SCALAR_FIELD[curve], O.BASE_FIELD[curve]
+
+    def run(sc, pts):
+        lib.halo_set_tuning(8, G); lib.halo_set_tuning(1, 1)          # batched affine on, one-launch small path off
+        try:
+            got = hb.group.point_dot_affine(curve, sc, pts)
+        finally:
+            lib.halo_set_tuning(8, 0); lib.halo_set_tuning(1, 0)
+        exp = O.msm(curve, pts, sc)
+        assert (_aff(O, curve, got) == _aff(O, curve, exp)).all()
+        old = hb.group.point_dot_affine(curve, sc, pts)                # the default task path
+        assert (_aff(O, curve, old) == _aff(O, curve, exp)).all()
+
+    for k in (1, 2, 3, G - 1, G, G + 1, 1000, 5000, (1 << 14) + 5):
+        run(O.random_scalars(sf, k, 4000 + k + G), O.points_arith(curve, k, k0=0x1000 + k))
+    k = 6000
+    pts = O.points_arith(curve, k).copy()
+    neg_y = lambda y: O.field_sub(bf, np.zeros((1, 4), dtype=np.uint64), y.reshape(1, 4))[0]
+    pts[17] = 0; pts[300:340] = 0                                      # identity bases
+    pts[1000:1400] = pts[1000]                                         # 400 copies of one point
+    pts[2000:2200:2] = pts[2001:2200:2]                                # adjacent duplicates
+    for i in range(3000, 3100, 2):                                     # P, -P pairs
+        pts[i + 1, 0:4] = pts[i, 0:4]; pts[i + 1, 4:8] = neg_y(pts[i, 4:8])
+    sc = O.random_scalars(sf, k, 555 + G)
+    sc[1000:1400] = sc[1000]                                           # equal scalars on equal points: doublings in every round
+    sc[2000:2200:2] = sc[2001:2200:2]
+    sc[3000:3100:2] = sc[3001:3100:2]                                  # s P + s (-P) = 0
+    sc[50:60] = 0
+    run(sc, pts)
+    run(np.ascontiguousarray(np.tile(sc[7], (k, 1))), pts)             # all equal: one bucket per window
+    run(O.ints_to_mont(sf, [(i * 7) % 3 for i in range(k)]), pts)      # digits 0, 1, 2 only
+    p = O.MODULUS[sf]
+    run(O.ints_to_mont(sf, [p - 1 - (i % 5) for i in range(k)]), pts)  # top-heavy
+    run(O.edge_scalars(sf, k, 98), pts)
+    same = np.ascontiguousarray(np.tile(pts[5], (k, 1)))               # ONE point k times: a pure doubling tree
+    run(np.ascontiguousarray(np.tile(sc[9], (k, 1))), same)

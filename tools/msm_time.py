@@ -5,6 +5,8 @@ import numpy as np, torch
 import halo_b200
 from halo_b200._lib import lib, check
 halo_b200.init()
+if os.environ.get('HALO_TUNE8'):
+    lib.halo_set_tuning(8, int(os.environ['HALO_TUNE8']))
 lgs = [int(x) for x in sys.argv[1:]] or [12, 16, 18, 20]
 kmax = 1 << max(lgs)
 d_pts = torch.empty((kmax, 8), dtype=torch.int64, device="cuda")
