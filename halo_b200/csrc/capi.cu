@@ -63,7 +63,7 @@ int upload_staged(void* d_dst, const void* h_src, size_t bytes, cudaStream_t ord
     // the destination may still be read by queued work: start after the library stream's current tail
     cudaEvent_t go;
     HALO_CUDA(cudaEventCreateWithFlags(&go, cudaEventDisableTiming));
-    HALO_CUDA(cudaEventRecord(go, R.stream));
+    HALO_CUDA(cudaEventRecord(go, order_stream));          // (the library stream unless the caller orders the copy elsewhere)
     int dev = 0;
     HALO_CUDA(cudaGetDevice(&dev));
     const size_t nchunks = (bytes + CH - 1) / CH;
@@ -115,6 +115,10 @@ int msm_wait_bases(cudaStream_t st) {
         HALO_CHECK(R.upload_rc == HALO_OK, HALO_ECUDA, "msm: staged upload of the base points failed");
     }
     if (R.wait_copy) { HALO_CUDA(cudaStreamWaitEvent(st, R.copy_done, 0)); R.wait_copy = false; }
+    if (R.bases_hook) {
+        auto h = R.bases_hook;
+        if (int e = h(st)) return e;
+    }
     return HALO_OK;
 }
 void msm_upload_finish() {
@@ -180,6 +184,7 @@ int prof_mark(const char* name) {
 
 template <int C> int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, uint64_t* out_xyz,
                                 ptrdiff_t base_stride);
+template <int C> int msm_host_chunked(const uint64_t* h_bases, const uint64_t* h_scalars, size_t k, uint64_t* out_xyz);
 template <int F> int ntt_device(Fe<F>* data, Fe<F>* out, int log_n, size_t batch, bool inverse, const Fe<F>* coset);
 template <int F> int ntt_fold_device(const Fe<F>* coeffs, size_t len, int log_n, Fe<F>* out);
 template <int C> int pcdl_commit(const uint64_t*, size_t, size_t, const uint64_t*, uint64_t*);
@@ -471,6 +476,7 @@ int halo_shutdown(void) { HALO_API_BEGIN
     if (R.copy_stream) cudaStreamDestroy(R.copy_stream);
     if (R.copy_done) cudaEventDestroy(R.copy_done);
     if (R.copy_go) cudaEventDestroy(R.copy_go);
+    for (auto& ev : R.chunk_ev) { if (ev) cudaEventDestroy(ev); ev = nullptr; }
     R.copy_stream = nullptr; R.copy_done = nullptr;
     R.own_stream = R.stream = nullptr;
     R.inited = false;
@@ -686,6 +692,10 @@ int halo_msm(int curve, const uint64_t* bases_xy, size_t base_off, const uint64_
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
     HALO_CHECK(out_xyz && (scalars || k == 0), HALO_EINVAL, "msm: null pointer");
+    // large MSMs over caller-supplied bases: upload pipelined with the accumulation by point range (tuning key 9 = 1: off)
+    if (bases_xy && k >= ((size_t)1 << 19) && k < ((size_t)1 << 27) && rt().tune[9] != 1 && rt().tune[8] == 0)
+        return curve == 0 ? msm_host_chunked<0>(bases_xy + 8 * base_off, scalars, k, out_xyz)
+                          : msm_host_chunked<1>(bases_xy + 8 * base_off, scalars, k, out_xyz);
     void *d_s = nullptr, *d_b = nullptr;
     if (int e = msm_upload_inputs(bases_xy, base_off, scalars, k, &d_s, &d_b)) { msm_upload_finish(); return e; }
     if (d_b) base_off = 0;

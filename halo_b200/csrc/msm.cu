@@ -25,6 +25,8 @@
 // scalars are badly skewed.
 #include "runtime.cuh"
 #include <algorithm>
+#include <atomic>
+#include <functional>
 #include <thread>
 
 namespace halo {
@@ -248,7 +250,9 @@ __global__ void __launch_bounds__(128, 4) msm_accumulate(const Affine<C>* __rest
                                                          const TaskMeta* __restrict__ meta, u32 L,
                                                          const u32* __restrict__ pslot,
                                                          XYZZ<C>* __restrict__ buckets, XYZZ<C>* __restrict__ partial,
-                                                         u32 buckets_per_msm, ptrdiff_t base_stride) {
+                                                         u32 buckets_per_msm, ptrdiff_t base_stride, int into) {
+    // into != 0: the bucket array already holds the sums of earlier point ranges of the same MSM (msm_host_chunked):
+    // a bucket's task starts from the stored value instead of the identity
     size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (t >= meta->ntasks) return;
     const uint2 tk = tasks[t];
@@ -258,7 +262,7 @@ __global__ void __launch_bounds__(128, 4) msm_accumulate(const Affine<C>* __rest
     const u32* my = idx + offsets[b] + seg * L;
     XYZZ<C>* dest = cnt_b > L ? partial + pslot[b] + seg : buckets + b;
     if (base_stride) bases += (ptrdiff_t)(b / buckets_per_msm) * base_stride;      // MSM j of a batch reads bases + j*stride
-    XYZZ<C> acc = xyzz_identity<C>();
+    XYZZ<C> acc = (into && cnt_b <= L) ? load_xyzz(buckets + b) : xyzz_identity<C>();
     if (cnt) {
         u32 e = __ldg(my);
         Affine<C> p = load_affine(bases + (e & 0x7fffffffu));
@@ -546,7 +550,7 @@ template <int C>
 __global__ void __launch_bounds__(128, 2) msm_fixup(const uint2* __restrict__ chunks, const TaskMeta* __restrict__ meta,
                                                     const u32* __restrict__ counts, const u32* __restrict__ pslot,
                                                     const u32* __restrict__ cbase, u32 L, const XYZZ<C>* __restrict__ partial,
-                                                    XYZZ<C>* __restrict__ partial2, XYZZ<C>* __restrict__ buckets) {
+                                                    XYZZ<C>* __restrict__ partial2, XYZZ<C>* __restrict__ buckets, int into) {
     const u32 lane = threadIdx.x & 31;
     const u32 nwarps = gridDim.x * (blockDim.x >> 5);
     const u32 nchunks = meta->nchunks;
@@ -559,14 +563,17 @@ __global__ void __launch_bounds__(128, 2) msm_fixup(const uint2* __restrict__ ch
         XYZZ<C> acc = xyzz_identity<C>();
         for (u32 s = lo + lane; s < hi; s += 32) { XYZZ<C> v = load_xyzz(src + s); xyzz_add<C>(acc, v); }
         acc = warp_sum_xyzz<C>(acc, hi - lo);
-        if (lane == 0) store_xyzz(nt <= FIXUP_CHUNK ? buckets + b : partial2 + cbase[b] + q, acc);
+        if (lane == 0) {
+            if (into && nt <= FIXUP_CHUNK) { const XYZZ<C> old = load_xyzz(buckets + b); xyzz_add<C>(acc, old); }
+            store_xyzz(nt <= FIXUP_CHUNK ? buckets + b : partial2 + cbase[b] + q, acc);
+        }
     }
 }
 // pass 2: buckets with more than FIXUP_CHUNK partial results: one warp adds the chunk sums
 template <int C>
 __global__ void __launch_bounds__(128, 2) msm_fixup2(const u32* __restrict__ big, const TaskMeta* __restrict__ meta,
                                                      const u32* __restrict__ counts, const u32* __restrict__ cbase, u32 L,
-                                                     const XYZZ<C>* __restrict__ partial2, XYZZ<C>* __restrict__ buckets) {
+                                                     const XYZZ<C>* __restrict__ partial2, XYZZ<C>* __restrict__ buckets, int into) {
     const u32 lane = threadIdx.x & 31;
     const u32 nwarps = gridDim.x * (blockDim.x >> 5);
     const u32 nbig = meta->nbig;
@@ -578,7 +585,10 @@ __global__ void __launch_bounds__(128, 2) msm_fixup2(const u32* __restrict__ big
         XYZZ<C> acc = xyzz_identity<C>();
         for (u32 s = lane; s < nch; s += 32) { XYZZ<C> v = load_xyzz(src + s); xyzz_add<C>(acc, v); }
         acc = warp_sum_xyzz<C>(acc, nch);
-        if (lane == 0) store_xyzz(buckets + b, acc);
+        if (lane == 0) {
+            if (into) { const XYZZ<C> old = load_xyzz(buckets + b); xyzz_add<C>(acc, old); }
+            store_xyzz(buckets + b, acc);
+        }
     }
 }
 
@@ -688,7 +698,9 @@ static int scan_u32(const u32* in, size_t n, u32* out, u32* out2, u32* bsum /*>=
 // Enqueues the whole device pipeline on the runtime stream and leaves nwt window sums (XYZZ) in *d_winsum_out.
 template <int C>
 static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR>* d_scalars, size_t k,
-                       const MsmPlan& P, ptrdiff_t base_stride, XYZZ<C>** d_winsum_out) {
+                       const MsmPlan& P, ptrdiff_t base_stride, XYZZ<C>** d_winsum_out, int into = 0, bool reduce = true) {
+    // into: accumulate on top of the bucket array's contents; reduce = false: stop after the buckets (more point
+    // ranges of the same MSM follow)
     constexpr int SF = CurveTraits<C>::SCALAR;
     Runtime& R = rt();
     cudaStream_t st = R.stream;
@@ -727,7 +739,7 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     lvl[3] = lvl[2] + half;
     if (int e = ws_get(WS_WINSUM, P.nwt * sizeof(XYZZ<C>), (void**)&winsum)) return e;
 
-    if (int e = prof_begin()) return e;
+    if (!into) if (int e = prof_begin()) return e;
     HALO_CUDA(cudaMemsetAsync(counts, 0, zero_words * 4, st));
     const int grid_pts = (int)std::min<size_t>((total + 255) / 256, (size_t)R.sm_count * 8);
     const int grid_b = (int)std::min<size_t>((P.nb + 255) / 256, (size_t)R.sm_count * 8);
@@ -765,13 +777,14 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     if (int e = msm_wait_bases(st)) return e;                                                         // bases uploaded on copy_stream
     msm_accumulate<C><<<(unsigned)((P.max_tasks + 127) / 128), 128, 0, st>>>(d_bases, idx, offsets, counts, tasks, meta,
                                                                            P.L, pslot, buckets, partial,
-                                                                           (u32)(P.B * P.nwin), base_stride);
+                                                                           (u32)(P.B * P.nwin), base_stride, into);
     prof_mark("accumulate");
-    msm_fixup<C><<<R.sm_count * 4, 128, 0, st>>>(chunks, meta, counts, pslot, cbase, P.L, partial, partial2, buckets);
-    msm_fixup2<C><<<R.sm_count, 128, 0, st>>>(big, meta, counts, cbase, P.L, partial2, buckets);
+    msm_fixup<C><<<R.sm_count * 4, 128, 0, st>>>(chunks, meta, counts, pslot, cbase, P.L, partial, partial2, buckets, into);
+    msm_fixup2<C><<<R.sm_count, 128, 0, st>>>(big, meta, counts, cbase, P.L, partial2, buckets, into);
     prof_mark("fixup");
     R.launches += 8;
     }
+    if (!reduce) { HALO_CUDA(cudaGetLastError()); return HALO_OK; }
     // bucket reduction: c-1 tree levels, then the per-window combine
     {
         const XYZZ<C>*m_in = buckets, *p_in = nullptr;
@@ -984,6 +997,100 @@ static int msm_small(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR>*
     *done = true;
     return HALO_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// One MSM over HOST buffers, pipelined by point range.  halo_msm used to upload all scalars, sort, and then wait for
+// ALL base points before the first addition: 96 B per point over the link sat in front of the accumulation.  Here the
+// points are cut into NCH ranges; range i is uploaded (scalars, then bases) while range i-1 is being sorted and
+// accumulated INTO THE SAME bucket array (`into` mode of the kernels above), and the bucket reduction runs once at
+// the end.  Same window width and buckets as the unchunked MSM of k points, so the result is the same group element.
+// Pinned or registered buffers: every copy asynchronous.  Pageable buffers (a Rust Vec): staged through pinned chunks
+// by a helper thread (upload_staged) while this thread enqueues the kernels.  Four ranges in both cases.
+// ---------------------------------------------------------------------------------------------------------
+template <int C>
+int msm_host_chunked(const uint64_t* h_bases, const uint64_t* h_scalars, size_t k, uint64_t* out_xyz) {
+    Runtime& R = rt();
+    cudaStream_t st = R.stream;
+    const bool pageable = host_ptr_is_pageable(h_bases) || host_ptr_is_pageable(h_scalars);
+    const int t10 = R.tune[10];                                           // experiment knob: number of ranges (2..16)
+    const int NCH = (t10 >= 2 && t10 <= 16) ? t10 : 4;                    // tools/e2e_chunks.py: flat from 2 to 8 (pinned), best at 4 (pageable)
+    char *d_s, *d_b;
+    if (int e = ws_get(WS_SCALARS, k * 32, (void**)&d_s)) return e;
+    if (int e = ws_get(WS_BASES, k * 64, (void**)&d_b)) return e;
+    for (int i = 0; i < 2 * NCH; ++i)
+        if (!R.chunk_ev[i]) HALO_CUDA(cudaEventCreateWithFlags(&R.chunk_ev[i], cudaEventDisableTiming));
+    HALO_CUDA(cudaEventRecord(R.copy_go, st));                            // the copies start behind what is already queued
+    HALO_CUDA(cudaStreamWaitEvent(R.copy_stream, R.copy_go, 0));
+    const MsmPlan P0 = make_plan(k, 1);
+    HALO_CHECK(P0.nwt * k < ((size_t)1 << 32), HALO_EINVAL, "msm: too large (nwin*k must be < 2^32)");
+    auto range = [&](int i, size_t& lo, size_t& hi) { lo = k * i / NCH; hi = k * (i + 1) / NCH; };
+    std::atomic<int> recorded{0};                                         // events recorded so far (pageable path)
+    std::atomic<int> up_rc{HALO_OK};
+    Workers up;
+    if (!pageable) {
+        for (int i = 0; i < NCH; ++i) {
+            size_t lo, hi; range(i, lo, hi);
+            HALO_CUDA(cudaMemcpyAsync(d_s + lo * 32, h_scalars + lo * 4, (hi - lo) * 32, cudaMemcpyHostToDevice, R.copy_stream));
+            HALO_CUDA(cudaEventRecord(R.chunk_ev[2 * i], R.copy_stream));
+            HALO_CUDA(cudaMemcpyAsync(d_b + lo * 64, h_bases + lo * 8, (hi - lo) * 64, cudaMemcpyHostToDevice, R.copy_stream));
+            HALO_CUDA(cudaEventRecord(R.chunk_ev[2 * i + 1], R.copy_stream));
+        }
+        recorded.store(2 * NCH);
+    } else {
+        up.spawn(1, [&]() {
+            int rc = cudaSetDevice(R.device) == cudaSuccess ? HALO_OK : HALO_ECUDA;
+            for (int i = 0; i < NCH && !rc; ++i) {
+                size_t lo, hi; range(i, lo, hi);
+                rc = upload_staged(d_s + lo * 32, h_scalars + lo * 4, (hi - lo) * 32, R.copy_stream);
+                if (!rc && cudaEventRecord(R.chunk_ev[2 * i], R.copy_stream) != cudaSuccess) rc = HALO_ECUDA;
+                if (!rc) recorded.store(2 * i + 1, std::memory_order_release);
+                if (!rc) rc = upload_staged(d_b + lo * 64, h_bases + lo * 8, (hi - lo) * 64, R.copy_stream);
+                if (!rc && cudaEventRecord(R.chunk_ev[2 * i + 1], R.copy_stream) != cudaSuccess) rc = HALO_ECUDA;
+                if (!rc) recorded.store(2 * i + 2, std::memory_order_release);
+            }
+            if (rc) up_rc.store(rc);
+        });
+        HALO_CHECK(up.size() == 1, HALO_ECUDA, "msm: could not start the upload thread");
+    }
+    // wait (on the host) until event e has been recorded by the upload thread, then make `s` wait for it on the device
+    auto wait_event = [&](int e, cudaStream_t s) -> int {
+        while (recorded.load(std::memory_order_acquire) <= e) {
+            if (up_rc.load()) { last_err() = "msm: staged upload failed"; return up_rc.load(); }
+            std::this_thread::yield();
+        }
+        HALO_CUDA(cudaStreamWaitEvent(s, R.chunk_ev[e], 0));
+        return HALO_OK;
+    };
+    XYZZ<C>* d_win = nullptr;
+    int rc = HALO_OK;
+    for (int i = 0; i < NCH && !rc; ++i) {
+        size_t lo, hi; range(i, lo, hi);
+        MsmPlan P = P0;                                                   // same windows and buckets, task sizes for this range
+        const size_t kc = hi - lo, work = kc * P.nwt;
+        P.L = work >= ((size_t)1 << 23) ? 128 : work >= ((size_t)1 << 20) ? 32 : 16;
+        if (work >= ((size_t)1 << 23)) { const size_t mean4 = 4 * (kc / P.B); if (mean4 > P.L) P.L = (u32)std::min<size_t>(mean4, MSM_MAX_L); }
+        P.max_tasks = P.nb + work / P.L + 1;
+        P.max_partial = 2 * (work / P.L) + 2;
+        P.ba_G = 0;
+        rc = wait_event(2 * i, st);
+        if (rc) break;
+        R.bases_hook = [&, i](cudaStream_t s) { return wait_event(2 * i + 1, s); };
+        rc = msm_enqueue<C>((const Affine<C>*)(d_b + lo * 64), (const Fe<CurveTraits<C>::SCALAR>*)(d_s + lo * 32), kc, P, 0, &d_win,
+                            i > 0, i == NCH - 1);
+        R.bases_hook = nullptr;
+    }
+    if (rc) up_rc.store(rc);                                              // lets the upload thread's waiters stop
+    up.join();
+    if (rc) { cudaStreamSynchronize(R.copy_stream); cudaStreamSynchronize(st); return rc; }
+    void* h = nullptr;
+    if (int e = pinned_get(P0.nwt * sizeof(XYZZ<C>), &h)) return e;
+    HALO_CUDA(cudaMemcpyAsync(h, d_win, P0.nwt * sizeof(XYZZ<C>), cudaMemcpyDeviceToHost, st));
+    HALO_CUDA(cudaStreamSynchronize(st));
+    msm_combine_host<C>((const XYZZ<C>*)h, P0, out_xyz);
+    return HALO_OK;
+}
+template int msm_host_chunked<0>(const uint64_t*, const uint64_t*, size_t, uint64_t*);
+template int msm_host_chunked<1>(const uint64_t*, const uint64_t*, size_t, uint64_t*);
 
 // nbatch MSMs of k points; MSM j uses bases + j*base_stride (0: all share one base set); scalars: nbatch x k
 // elements, out: nbatch x 12 words

@@ -7,6 +7,7 @@
 #include <string>
 #include <vector>
 #include <thread>
+#include <functional>
 #include <cstdio>
 #include "curve.cuh"
 #include "../../include/halo_b200.h"
@@ -40,13 +41,17 @@ struct Runtime {
     // first kernel that reads the bases
     std::thread upload_thread;
     int upload_rc = 0;
+    // chunked host MSM (msm_host_chunked): one event per uploaded piece, and the action the pipeline runs right before
+    // its first kernel that reads the bases
+    cudaEvent_t chunk_ev[32] = {};
+    std::function<int(cudaStream_t)> bases_hook;
     ResidentParams pp[2];
     std::vector<DeviceBuf> arena;   // indexed slots
     void* pinned = nullptr;         // pinned host staging
     size_t pinned_cap = 0;
     // staged upload of large pageable buffers: UP_THREADS workers, two pinned chunks and one stream each
     static constexpr int UP_THREADS = 8, UP_SLOTS = 2;
-    static constexpr size_t UP_CHUNK = (size_t)8 << 20;
+    static constexpr size_t UP_CHUNK = (size_t)2 << 20;
     void* up_buf[UP_THREADS][UP_SLOTS] = {};
     cudaEvent_t up_ev[UP_THREADS][UP_SLOTS] = {};
     cudaStream_t up_stream[UP_THREADS] = {};

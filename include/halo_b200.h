@@ -87,6 +87,8 @@ int halo_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const
  * key 5 = 1 makes the PLONK prover always take the 16-coset coefficient-division path for the quotient,
  * key 6 = 1 makes the PLONK prover transform and commit all-zero columns like any other (no sparse-column path),
  * key 7 = 1 prints a per-round phase trace of halo_pcdl_open to stderr,
+ * key 9 = 1 disables the point-range pipelining of halo_msm over host buffers (upload overlapped with accumulation),
+ * key 10 = number of point ranges of that pipeline (2..16; default 4),
  * key 8 = 64 / 128 / 256: bucket accumulation of the general MSM pipeline by batched affine additions with that many
  *        positions per thread (opt-in: measured slower than the default XYZZ task path on these 255-bit fields) */
 int halo_set_tuning(int key, int value);

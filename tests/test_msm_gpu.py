@@ -304,3 +304,46 @@ def test_msm_batched_affine_path_forced(hb, oracle, curve, G):
     run(O.edge_scalars(sf, k, 98), pts)
     same = np.ascontiguousarray(np.tile(pts[5], (k, 1)))               # ONE point k times: a pure doubling tree
     run(np.ascontiguousarray(np.tile(sc[9], (k, 1))), same)
+
+
+@pytest.mark.parametrize("curve", [0, 1])
+def test_msm_host_buffers_pipelined_by_point_range(hb, oracle, curve):
+    """halo_msm over host buffers of >= 2^19 points uploads and accumulates by point range into one bucket array
+    (msm_host_chunked): 4 ranges from pinned memory, 2 staged ranges from pageable memory.  Both must equal the oracle
+    and the unchunked path (tuning key 9 = 1), on a ragged size with identity / duplicate / negated bases placed across
+    the range boundaries and scalars that leave some ranges' buckets empty."""
+    import ctypes
+    import torch
+    O = oracle
+    lib = hb._lib.lib
+    sf, bf = O.SCALAR_FIELD[curve], O.BASE_FIELD[curve]
+    k = (1 << 19) + 37
+    pts = O.points_arith(curve, k, k0=0x515 + curve).copy()
+    sc = O.random_scalars(sf, k, 6100 + curve)
+    q = k // 4
+    pts[q - 1] = pts[q]; sc[q - 1] = sc[q]                                    # the same term on both sides of a boundary
+    pts[2 * q] = pts[5]; pts[2 * q, 4:8] = O.field_sub(bf, np.zeros((1, 4), dtype=np.uint64), pts[5, 4:8].reshape(1, 4))[0]
+    sc[2 * q] = sc[5]                                                         # s P in range 0, s (-P) in range 2
+    pts[3 * q: 3 * q + 50] = 0                                                # identity bases
+    sc[q: q + 20000] = sc[7]                                                  # one bucket per window for part of range 1
+    sc[k - 5000:] = 0                                                         # nothing to add at the end of the last range
+    exp = _aff(O, curve, O.msm(curve, pts, sc))
+    got = hb.group.point_dot_affine(curve, sc, pts)                           # pageable numpy buffers: 2 staged ranges
+    assert (_aff(O, curve, got) == exp).all()
+    hp = torch.from_numpy(pts.view(np.int64)).pin_memory()
+    hs = torch.from_numpy(sc.view(np.int64)).pin_memory()
+    u64p = ctypes.POINTER(ctypes.c_uint64)
+    out = np.zeros(12, dtype=np.uint64)
+
+    def pinned():
+        hb._lib.check(lib.halo_msm(curve, ctypes.cast(hp.data_ptr(), u64p), ctypes.c_size_t(0), ctypes.cast(hs.data_ptr(), u64p),
+                                   ctypes.c_size_t(k), out.ctypes.data_as(u64p)))
+        return out.copy()
+    assert (_aff(O, curve, pinned()) == exp).all()                            # 4 ranges, asynchronous copies
+    assert (_aff(O, curve, pinned()) == exp).all()                            # again: the bucket array starts from scratch
+    lib.halo_set_tuning(9, 1)
+    try:
+        assert (_aff(O, curve, pinned()) == exp).all()                        # unchunked
+        assert (_aff(O, curve, hb.group.point_dot_affine(curve, sc, pts)) == exp).all()
+    finally:
+        lib.halo_set_tuning(9, 0)
