@@ -137,6 +137,25 @@ int halo_acc_hpoly(int field, const uint64_t* xis, const uint64_t* alphas, size_
 /* ≙ HPoly::eval (pcdl.rs:221-233), host */
 int halo_hpoly_eval(int field, const uint64_t* xis, size_t lg_n, const uint64_t z[4], uint64_t out[4]);
 
+/* ---- wire formats  ≙ the derived CanonicalSerialize / CanonicalDeserialize (ark-serialize 0.5, Compress::Yes) of Instance,
+ * EvalProof and Accumulator (crates/accumulation/src/pcdl.rs:26,159; acc.rs:22) as qs.bin is written
+ * (crates/accumulation/src/main.rs:59-91).  Host code; no device and no halo_init needed.
+ *   scalar: 32 bytes little-endian canonical integer.   point: affine form, 32 bytes LE canonical x + 1 flag byte
+ *   (bit 7: y is the larger root, bit 6: infinity).   usize: u64 LE.   Vec: u64 LE length + items.   Option: 0 / 1 + item.
+ * Instance = C d z v Ls Rs U c C_bar? w_prime?; an Accumulator is its instance q, byte for byte.
+ * Deserialisation validates what ark's does (scalars below the modulus, x below the modulus with x^3 + 5 a square, not
+ * both flags) and additionally requires what the flat layout assumes: Ls and Rs of lg(d + 1) points, C_bar and w_prime
+ * both present or both absent.  Malformed input -> HALO_EINVAL. */
+int halo_point_compress(int curve, const uint64_t xyz[12], uint8_t out[33]);
+int halo_point_decompress(int curve, const uint8_t in[33], uint64_t out_xyz[12]);
+int halo_scalar_serialize(int field, const uint64_t s[4], uint8_t out[32]);
+int halo_scalar_deserialize(int field, const uint8_t in[32], uint64_t out[4]);
+/* *written (may be NULL) always receives the size needed: 253 + 66 lg n bytes with hiding, 188 + 66 lg n without */
+int halo_instance_serialize(int curve, const uint64_t* instance, uint8_t* out, size_t cap, size_t* written);
+/* out_instance: halo_instance_words(lg n) words for the d found in the bytes; *consumed (may be NULL) = bytes read */
+int halo_instance_deserialize(int curve, const uint8_t* bytes, size_t len, uint64_t* out_instance, size_t cap_words,
+                              size_t* consumed);
+
 /* ---- multi-GPU: one process per GPU, the library owns an NCCL communicator ------------------
  * The reference is a single process with rayon; a host that wants N GPUs runs N ranks (threads of a launcher, MPI
  * ranks, torchrun workers), each of which calls halo_init(device) and then halo_dist_init.  Rank 0 obtains the 128-byte

@@ -11,6 +11,7 @@
 // at crates/group/src/pp.rs:36-53.
 #include "pcdl.hpp"
 #include "plonk.hpp"
+#include "serialize.hpp"
 #include <cstdio>
 #include <map>
 
@@ -431,4 +432,42 @@ void orc_fold_generators(int curve, const u64* gl_xy, const u64* gr_xy, const u6
     }
 }
 
+}  // extern "C"
+
+// ---- ark-serialize compressed encodings (serialize.hpp) ----
+extern "C" {
+void orc_point_compress(int curve, const u64* xyz, uint8_t* out33) {
+    std::vector<uint8_t> b;
+    if (curve == 0) ser::write_point<0>(Jac<0>::from_raw(xyz), b); else ser::write_point<1>(Jac<1>::from_raw(xyz), b);
+    memcpy(out33, b.data(), 33);
+}
+int orc_point_decompress(int curve, const uint8_t* in33, u64* out_xyz) {
+    if (curve == 0) { Jac<0> p; if (!ser::read_point<0>(in33, &p)) return 1; p.to_raw(out_xyz); }
+    else { Jac<1> p; if (!ser::read_point<1>(in33, &p)) return 1; p.to_raw(out_xyz); }
+    return 0;
+}
+// returns the number of bytes written (0 if cap is too small)
+size_t orc_instance_serialize(int curve, const u64* inst, uint8_t* out, size_t cap) {
+    std::vector<uint8_t> b;
+    if (curve == 0) ser::write_instance<0>(instance_from_flat<0>(inst), b); else ser::write_instance<1>(instance_from_flat<1>(inst), b);
+    if (b.size() > cap) return 0;
+    memcpy(out, b.data(), b.size());
+    return b.size();
+}
+// returns bytes consumed (0 = malformed); *lg_n receives the length of Ls
+size_t orc_instance_deserialize(int curve, const uint8_t* in, size_t len, u64* out_inst, size_t cap_words, unsigned* lg_n) {
+    size_t used = 0;
+    if (curve == 0) {
+        Instance<0> q; used = ser::read_instance<0>(in, len, &q);
+        if (!used || q.pi.Ls.size() != q.pi.Rs.size() || instance_words((unsigned)q.pi.Ls.size()) > cap_words) return 0;
+        if (((size_t)1 << q.pi.Ls.size()) != q.d + 1) return 0;
+        instance_to_flat<0>(q, out_inst); *lg_n = (unsigned)q.pi.Ls.size();
+    } else {
+        Instance<1> q; used = ser::read_instance<1>(in, len, &q);
+        if (!used || q.pi.Ls.size() != q.pi.Rs.size() || instance_words((unsigned)q.pi.Ls.size()) > cap_words) return 0;
+        if (((size_t)1 << q.pi.Ls.size()) != q.d + 1) return 0;
+        instance_to_flat<1>(q, out_inst); *lg_n = (unsigned)q.pi.Ls.size();
+    }
+    return used;
+}
 }  // extern "C"

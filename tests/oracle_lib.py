@@ -446,3 +446,40 @@ def plonk_verify(curve, lg_n, C_qs, public_inputs, public_input_count, acc_prev,
     if rc < 0:
         raise OracleError(last_error())
     return rc == 0
+
+
+# ---------------- ark-serialize compressed encodings (oracle/serialize.hpp) ----------------
+_u8p = ctypes.POINTER(ctypes.c_uint8)
+_lib.orc_instance_serialize.restype = ctypes.c_size_t
+_lib.orc_instance_deserialize.restype = ctypes.c_size_t
+
+
+def point_compress(curve, xyz):
+    out = (ctypes.c_uint8 * 33)()
+    _lib.orc_point_compress(curve, _p(_c(xyz).reshape(12)), out)
+    return bytes(out)
+
+
+def point_decompress(curve, data):
+    """Returns the Jacobian point, or None when the bytes are not a valid compressed point."""
+    buf = (ctypes.c_uint8 * 33).from_buffer_copy(bytes(data[:33]))
+    out = np.empty(12, dtype=np.uint64)
+    return out if _lib.orc_point_decompress(curve, buf, _p(out)) == 0 else None
+
+
+def instance_serialize(curve, inst):
+    cap = 4096 + 66 * 64
+    out = (ctypes.c_uint8 * cap)()
+    n = _lib.orc_instance_serialize(curve, _p(_c(inst)), out, ctypes.c_size_t(cap))
+    assert n > 0
+    return bytes(out[:n])
+
+
+def instance_deserialize(curve, data):
+    """Returns (flat instance, bytes consumed) or None."""
+    data = bytes(data)
+    buf = (ctypes.c_uint8 * len(data)).from_buffer_copy(data)
+    out = np.zeros(instance_words(40), dtype=np.uint64)
+    lg = ctypes.c_uint(0)
+    used = _lib.orc_instance_deserialize(curve, buf, ctypes.c_size_t(len(data)), _p(out), ctypes.c_size_t(out.shape[0]), ctypes.byref(lg))
+    return (out[:instance_words(lg.value)].copy(), used) if used else None

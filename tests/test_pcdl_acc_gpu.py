@@ -192,3 +192,28 @@ def test_fold_variants_give_the_same_proof(hb, oracle, params, curve):
         finally:
             lib.halo_set_tuning(0, 0); lib.halo_set_tuning(3, 0); lib.halo_set_tuning(4, 0)
         same_instance(O, curve, q.w, exp if size == n else O.instance_open(curve, p[:size], size - 1, z))
+
+
+def test_wire_format_of_gpu_produced_objects(hb, oracle, params):
+    """tools/gen_qs.py's content at small sizes: hiding instances and their accumulators produced on the GPU, written as
+    Vec<(usize, Instance, Accumulator)>::serialize_compressed (crates/accumulation/src/main.rs:59-91), read back, and
+    the parsed objects pass check / decider on the GPU and in the oracle; bytes equal the oracle's encoding."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import gen_qs
+    O = oracle
+    ents = gen_qs.generate(0, 2, 9, seed=7, log=lambda *_: None)
+    blob = hb.serialize.qs_serialize(ents)
+    # a hiding instance is 253 + 66 lg n bytes; the accumulator's opening of h(X) is not hiding (acc.rs:190): 188 + 66 lg n
+    assert len(blob) == 8 + sum(8 + (253 + 66 * lg) + (188 + 66 * lg) for lg in range(2, 10))
+    back = hb.serialize.qs_deserialize(0, blob)
+    assert len(back) == 8
+    for (n, q, a), (n2, q2, a2) in zip(ents, back):
+        assert n == n2 and q2.d == n - 1 and q2.pi.hiding and not a2.q.pi.hiding
+        same_instance(O, 0, q2.w, q.w)
+        same_instance(O, 0, a2.q.w, a.q.w)
+        q2.check()
+        hb.acc.verifier(0, [q2], a2)
+        hb.acc.decider(0, a2)
+        assert O.pcdl_check(0, q2.w) and O.acc_decider(0, a2.q.w)
+        assert hb.serialize.instance_serialize(q) == O.instance_serialize(0, q.w)
