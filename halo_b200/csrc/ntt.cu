@@ -25,7 +25,7 @@ namespace halo {
 
 constexpr int NTT_LOG_TILE = 11;             // 2048 elements = 64 KB of shared memory per CTA
 constexpr int NTT_THREADS = 256;
-constexpr int NTT_Q = 2;                     // strided passes move runs of 4 elements = 128 B
+constexpr int NTT_Q = 2;                     // strided passes move runs of at least 4 elements = 128 B (q = 11 - s)
 
 template <int F> __device__ __forceinline__ Fe<F> ldg_fe(const Fe<F>* p) {
     Fe<F> r;
@@ -270,7 +270,10 @@ int ntt_device(Fe<F>* data, Fe<F>* out, int log_n, size_t batch, bool inverse, c
     int t0 = 0;
     for (int p = 0; p < np; ++p) {
         int s = rem / np + (p < rem % np ? 1 : 0);
-        P.t0 = t0; P.s = s; P.q = NTT_Q; P.last = 0;
+        // every strided pass fills the whole 2^11-element tile: 2^s rows of 2^q consecutive elements with q = 11 - s >= 2
+        // (round 1 fixed q = 2, so the 5- and 6-stage passes of 2^16 / 2^22 transforms ran on tiles of 128 - 256 elements
+        // with most of the CTA idle); the bits below this pass's stages number n - t0 - s >= 11 > q
+        P.t0 = t0; P.s = s; P.q = NTT_LOG_TILE - s; P.last = 0;
         dim3 grid((unsigned)(N >> (s + P.q)), (unsigned)batch);
         ntt_pass_kernel<F><<<grid, NTT_THREADS, (size_t)32 << (s + P.q), st>>>(data, out, tw, P, scale);
         R.launches += 1;
