@@ -9,7 +9,67 @@
 
 namespace halo {
 
-Runtime& rt() { static Runtime r; return r; }
+static Runtime& main_rt() { static Runtime r; return r; }
+static thread_local Runtime* t_lane = nullptr;
+static Runtime* g_lane = nullptr;
+Runtime& rt() { return t_lane ? *t_lane : main_rt(); }
+LaneScope::LaneScope(Runtime* r) { t_lane = r; }
+LaneScope::~LaneScope() { t_lane = nullptr; }
+
+Runtime* lane_get() {
+    Runtime& M = main_rt();
+    if (!M.inited) return nullptr;
+    if (!g_lane) {
+        Runtime* L = new (std::nothrow) Runtime();
+        if (!L) return nullptr;
+        L->is_lane = true;
+        L->device = M.device;
+        L->sm_count = M.sm_count;
+        bool ok = cudaStreamCreateWithFlags(&L->own_stream, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaStreamCreateWithFlags(&L->copy_stream, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaEventCreateWithFlags(&L->copy_done, cudaEventDisableTiming) == cudaSuccess &&
+                  cudaEventCreateWithFlags(&L->copy_go, cudaEventDisableTiming) == cudaSuccess;
+        if (!ok) { cudaGetLastError(); delete L; return nullptr; }
+        L->stream = L->own_stream;
+        L->arena.resize(WS_COUNT);
+        L->inited = true;
+        g_lane = L;
+    }
+    Runtime* L = g_lane;
+    for (int c = 0; c < 2; ++c) L->pp[c] = M.pp[c];
+    for (int f = 0; f < 2; ++f) { L->ntt_tw[f] = M.ntt_tw[f]; L->ntt_logmax[f] = M.ntt_logmax[f]; }
+    for (int i = 0; i < 16; ++i) L->tune[i] = M.tune[i];
+    L->msm_window_override = M.msm_window_override;
+    return L;
+}
+void lane_finish(Runtime* lane) {
+    Runtime& M = main_rt();
+    M.launches += lane->launches;
+    lane->launches = 0;
+}
+// releases the lane's own resources (the resident tables it points to belong to the main runtime)
+static void lane_release() {
+    Runtime* L = g_lane;
+    if (!L) return;
+    cudaStreamSynchronize(L->stream);
+    for (auto& b : L->arena) if (b.p) cudaFree(b.p);
+    if (L->pinned) cudaFreeHost(L->pinned);
+    for (int t = 0; t < Runtime::UP_THREADS; ++t) {
+        for (int k = 0; k < Runtime::UP_SLOTS; ++k) {
+            if (L->up_buf[t][k]) cudaFreeHost(L->up_buf[t][k]);
+            if (L->up_ev[t][k]) cudaEventDestroy(L->up_ev[t][k]);
+        }
+        if (L->up_stream[t]) cudaStreamDestroy(L->up_stream[t]);
+    }
+    cudaStreamDestroy(L->own_stream);
+    cudaStreamDestroy(L->copy_stream);
+    cudaEventDestroy(L->copy_done);
+    cudaEventDestroy(L->copy_go);
+    for (auto& ev : L->chunk_ev) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : L->prof_ev) if (ev) cudaEventDestroy(ev);
+    delete L;
+    g_lane = nullptr;
+}
 
 int ws_get(int slot, size_t bytes, void** out) {
     Runtime& R = rt();
@@ -452,6 +512,7 @@ int halo_shutdown(void) { HALO_API_BEGIN
     Runtime& R = rt();
     if (!R.inited) return HALO_OK;
     cudaStreamSynchronize(R.stream);
+    lane_release();
     for (auto& b : R.arena) if (b.p) cudaFree(b.p);
     R.arena.clear();
     for (int c = 0; c < 2; ++c) {

@@ -664,6 +664,7 @@ static int ensure_fold_table(size_t n, const Affine<C>** out) {
     ResidentParams& P = R.pp[C];
     *out = nullptr;
     if (P.d_fold_tab && P.fold_tab_n == n) { *out = (const Affine<C>*)P.d_fold_tab; return HALO_OK; }
+    if (R.is_lane) return HALO_OK;                         // a lane only borrows the main runtime's table: ladder fold without one
     HALO_CUDA(cudaStreamSynchronize(st));
     if (P.d_fold_tab) { cudaFree(P.d_fold_tab); P.d_fold_tab = nullptr; P.fold_tab_n = 0; }
     const size_t m = n / 2;
@@ -708,6 +709,25 @@ int fold_table_build(size_t n) {
 }
 template int fold_table_build<0>(size_t);
 template int fold_table_build<1>(size_t);
+
+// fixed-base table for the first fold (tuning knob 0: 1 = never, 2 = for every size; by default for openings over the
+// whole parameter set of at least 2^16 generators, the size a prover keeps using)
+template <int C>
+static bool open_uses_fold_table(size_t n) {
+    Runtime& R = rt();
+    const int tail_lg = R.tune[3] == 0 ? 15 : R.tune[3];
+    const size_t tail_max = tail_lg < 0 ? 0 : (size_t)1 << tail_lg;
+    return R.tune[0] != 1 && R.tune[2] != 1 && n >= 4 && n / 2 > tail_max && (R.tune[0] == 2 || (n == R.pp[C].n && n >= ((size_t)1 << 16)));
+}
+// what an opening of size n builds lazily on the MAIN runtime, done ahead of openings that run on a lane
+template <int C>
+int pcdl_open_prepare(size_t n) {
+    const Affine<C>* tab = nullptr;
+    if (open_uses_fold_table<C>(n)) return ensure_fold_table<C>(n, &tab);
+    return HALO_OK;
+}
+template int pcdl_open_prepare<0>(size_t);
+template int pcdl_open_prepare<1>(size_t);
 
 // ---------------------------------------------------------------------------------------------------------
 // pcdl::open / open_without_eval (pcdl.rs:326-473)
@@ -808,7 +828,7 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
     // fixed-base table for the first fold (tuning knob 0: 1 = never, 2 = for every size; by default for openings
     // over the whole parameter set of at least 2^16 generators, the size a prover keeps using)
     const Affine<C>* fold_tab = nullptr;
-    if (R.tune[0] != 1 && R.tune[2] != 1 && n >= 4 && n / 2 > tail_max && (R.tune[0] == 2 || (n == R.pp[C].n && n >= ((size_t)1 << 16))))
+    if (open_uses_fold_table<C>(n))
         if (int e = ensure_fold_table<C>(n, &fold_tab)) return e;
     bool pending = false;
     SF pend_xi = fe_zero<S>();

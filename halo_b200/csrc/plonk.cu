@@ -752,18 +752,49 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     const unsigned iw = (unsigned)instance_words(lg_n);
     std::vector<uint64_t> insts(3 * (size_t)iw);
     memcpy(insts.data(), acc_prev, iw * 8);
-    for (int k = 0; k < 2; ++k) {
+    // The two openings are independent (different polynomials, different points, their own transcripts) and each is a
+    // chain of lg n rounds whose last 15 are latency-bound and leave most of the GPU idle: the second one runs on a
+    // helper thread in the library's second execution context (lane_get: own stream, workspaces, pinned buffer) beside
+    // the first.  d_r is complete here (the evaluations above synchronised the stream).  Tuning key 13 = 1: one after
+    // the other.
+    auto open_k = [&](int k) -> int {
+        Runtime& Rk = rt();                                 // the main runtime, or the lane inside the helper thread
         uint64_t* q = insts.data() + (size_t)(1 + k) * iw;
         SF* cs;
         if (int e = ws_get(WS_IPA_C, n * 32, (void**)&cs)) return e;
-        HALO_CUDA(cudaMemcpyAsync(cs, d_r + (size_t)k * n, n * 32, cudaMemcpyDeviceToDevice, st));
-        if (int e = msm_device<C>(R.pp[C].d_gs, cs, n, 1, q, 0)) return e;
+        HALO_CUDA(cudaMemcpyAsync(cs, d_r + (size_t)k * n, n * 32, cudaMemcpyDeviceToDevice, Rk.stream));
+        if (int e = msm_device<C>(Rk.pp[C].d_gs, cs, n, 1, q, 0)) return e;
         q[12] = d;
         const SF& at = k ? xi_omega : xi;
         H::put_scalar(at, q + 13);
         if (int e = pcdl_open<C>(nullptr, n, q, d, (const uint64_t*)&at, nullptr, nullptr, nullptr, nullptr, q + 21, q + 17, true))
             return e;
         memcpy(k ? o_piro : o_pir, q + 21, evalproof_words(lg_n) * 8);
+        return HALO_OK;
+    };
+    {
+        Runtime* lane = nullptr;
+        if (R.tune[13] != 1 && !R.is_lane && pcdl_open_prepare<C>(n) == HALO_OK) lane = lane_get();
+        int rc1 = HALO_OK;
+        std::string err1;
+        Workers helper;
+        if (lane) {
+            helper.spawn(1, [&]() {
+                LaneScope scope(lane);
+                try {
+                    rc1 = cudaSetDevice(lane->device) == cudaSuccess ? open_k(1) : HALO_ECUDA;
+                } catch (...) { rc1 = HALO_ECUDA; last_err() = "plonk: exception in the second opening"; }
+                if (rc1) err1 = last_err();
+                cudaStreamSynchronize(lane->stream);
+            });
+        }
+        const bool concurrent = helper.size() == 1;
+        const int rc0 = open_k(0);
+        helper.join();
+        if (lane) lane_finish(lane);
+        if (rc0) return rc0;
+        if (concurrent) { if (rc1) { last_err() = err1; return rc1; } }
+        else if (int e = open_k(1)) return e;
     }
     lap("round 5 (two openings)");
     if (int e = acc_prover<C>(insts.data(), 3, o_acc)) return e;

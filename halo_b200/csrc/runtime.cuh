@@ -67,9 +67,22 @@ struct Runtime {
     void* ntt_tw[2] = {nullptr, nullptr};   // twiddle table per field: omega_max^k, k < 2^(logmax-1)
     int ntt_logmax[2] = {0, 0};
     std::recursive_mutex mu;
+    bool is_lane = false;           // a second execution context (lane_get): shares the resident tables, never builds them
 };
 
+// The runtime of the calling thread: the process-wide one, or -- inside a LaneScope -- the second execution context.
 Runtime& rt();
+// Second execution context on the same device: its own stream, workspace arena and pinned buffer, with the resident
+// generator sets, fold tables, twiddle tables and tuning knobs of the main runtime copied in (pointers, not data) at
+// every call.  A helper thread that enters it (LaneScope) can run one library pipeline -- an IPA opening -- beside
+// the calling thread's: the two independent Instance::open calls of a PLONK proof (protocol.rs:295-296) are each a
+// chain of latency-bound rounds that leave most of the GPU idle.  Returns nullptr when it cannot be created.
+Runtime* lane_get();
+void lane_finish(Runtime* lane);    // adds the lane's launch count to the main runtime
+struct LaneScope {
+    explicit LaneScope(Runtime* r);
+    ~LaneScope();
+};
 // last error message of the calling thread (halo_last_error)
 inline std::string& last_err() { static thread_local std::string e; return e; }
 

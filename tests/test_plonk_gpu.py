@@ -99,6 +99,13 @@ def test_proof_matches_oracle_and_verifies(hb, oracle, params, curve, lg_n, kind
     finally:
         lib.halo_set_tuning(6, 0)
     same_proof(O, curve, lg_n, dense.w, exp)
+    # the two openings of round 5 run side by side (second execution context); one after the other gives the same proof
+    lib.halo_set_tuning(13, 1)
+    try:
+        serial = hb.plonk.PlonkProof.naive_prover(circuit, pub, wit)
+    finally:
+        lib.halo_set_tuning(13, 0)
+    same_proof(O, curve, lg_n, serial.w, exp)
     # circuit columns resident on the device (halo_plonk_circuit_load): only the witness is uploaded, same proof
     circuit.make_resident(c["polys"])
     try:

@@ -7,6 +7,9 @@ from halo_b200._lib import lib, check
 halo_b200.init()
 if os.environ.get('HALO_TUNE8'):
     lib.halo_set_tuning(8, int(os.environ['HALO_TUNE8']))
+for kv in os.environ.get('HALO_TUNE', '').split(','):          # HALO_TUNE="11=4,8=0": tuning keys
+    if '=' in kv:
+        lib.halo_set_tuning(int(kv.split('=')[0]), int(kv.split('=')[1]))
 lgs = [int(x) for x in sys.argv[1:]] or [12, 16, 18, 20]
 kmax = 1 << max(lgs)
 d_pts = torch.empty((kmax, 8), dtype=torch.int64, device="cuda")
