@@ -256,11 +256,13 @@ template <int C> int pcdl_succinct_check(const uint64_t*, uint64_t*, uint64_t*);
 template <int C> int pcdl_check(const uint64_t*);
 template <int C> int acc_prover(const uint64_t*, size_t, uint64_t*);
 size_t plonk_proof_words(unsigned lg_n);
-template <int C> int plonk_prove(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*);
+template <int C> int plonk_prove(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*, bool);
+int plonk_circuit_shape(int handle, int* curve, unsigned* lg_n);
+static inline size_t instance_words(unsigned lg_n) { return 24 * (size_t)lg_n + 54; }
 int plonk_circuit_load(int curve, unsigned lg_n, const uint64_t* polys, int* handle);
 int plonk_circuit_free(int handle);
 void plonk_circuits_release();
-int plonk_prove_resident(int handle, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*);
+int plonk_prove_resident(int handle, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, bool);
 template <int C> int plonk_verify(unsigned, const uint64_t*, const uint64_t*, size_t, size_t, const uint64_t*, const uint64_t*, int);
 template <int C> int acc_verifier(const uint64_t*, size_t, const uint64_t*, bool sharded = false);
 template <int C> int acc_prover_dist(const uint64_t*, size_t, uint64_t*);
@@ -269,6 +271,7 @@ bool dist_on();
 int dist_rank();
 int dist_world();
 int dist_allgather_dev(const void* d_send, void* d_recv, size_t bytes);
+int dist_bcast_host(void* h_buf, size_t bytes, int root);
 template <int S> int hpoly_coeffs(const uint64_t*, const uint64_t*, size_t, unsigned, uint64_t*);
 template <int C> int hpoly_commit_words(const uint64_t*, unsigned, uint64_t*);
 template <int S> void hpoly_eval_words(const uint64_t*, unsigned, const uint64_t*, uint64_t*);
@@ -867,8 +870,8 @@ int halo_plonk_prove(int curve, unsigned lg_n, const uint64_t* polys, const uint
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
     HALO_CHECK(polys && w_evals && acc_prev && out_proof && (public_inputs || n_public == 0), HALO_EINVAL, "null argument");
-    return curve == 0 ? plonk_prove<0>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof, nullptr)
-                      : plonk_prove<1>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof, nullptr);
+    return curve == 0 ? plonk_prove<0>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof, nullptr, false)
+                      : plonk_prove<1>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof, nullptr, false);
 HALO_API_END
 }
 
@@ -888,7 +891,48 @@ int halo_plonk_prove_circuit(int handle, const uint64_t* w_polys, const uint64_t
                              size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof) { HALO_API_BEGIN
     LOCK(); NEED_INIT();
     HALO_CHECK(w_polys && w_evals && acc_prev && out_proof && (public_inputs || n_public == 0), HALO_EINVAL, "null argument");
-    return plonk_prove_resident(handle, w_polys, w_evals, public_inputs, n_public, acc_prev, out_proof);
+    return plonk_prove_resident(handle, w_polys, w_evals, public_inputs, n_public, acc_prev, out_proof, false);
+HALO_API_END
+}
+
+// ONE proof over the GPUs of the communicator (collective).  The small inputs (public inputs, previous accumulator)
+// are broadcast from rank 0 here, the columns inside plonk_prove.
+static int dist_plonk_small_inputs(unsigned lg_n, const uint64_t* public_inputs, size_t n_public, const uint64_t* acc_prev,
+                                   std::vector<uint64_t>& pub, std::vector<uint64_t>& acc) {
+    HALO_CHECK(lg_n >= 1 && lg_n <= 22, HALO_EINVAL, "plonk: rows must be a power of two in [2, 2^22]");
+    HALO_CHECK(n_public <= ((size_t)1 << lg_n), HALO_EINVAL, "plonk: more public inputs than rows");
+    pub.assign(4 * n_public, 0);
+    acc.assign(instance_words(lg_n), 0);
+    if (dist_rank() == 0) {
+        HALO_CHECK(acc_prev && (public_inputs || n_public == 0), HALO_EINVAL, "null argument on rank 0");
+        if (n_public) memcpy(pub.data(), public_inputs, pub.size() * 8);
+        memcpy(acc.data(), acc_prev, acc.size() * 8);
+    }
+    if (int e = dist_bcast_host(pub.data(), pub.size() * 8, 0)) return e;
+    return dist_bcast_host(acc.data(), acc.size() * 8, 0);
+}
+int halo_dist_plonk_prove(int curve, unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, const uint64_t* public_inputs,
+                          size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof) { HALO_API_BEGIN
+    LOCK(); NEED_INIT();
+    HALO_CHECK(dist_on(), HALO_ENOINIT, "halo_dist_init has not been called");
+    HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
+    HALO_CHECK(out_proof && (dist_rank() != 0 || (polys && w_evals)), HALO_EINVAL, "null argument");
+    std::vector<uint64_t> pub, acc;
+    if (int e = dist_plonk_small_inputs(lg_n, public_inputs, n_public, acc_prev, pub, acc)) return e;
+    return curve == 0 ? plonk_prove<0>(lg_n, polys, w_evals, pub.data(), n_public, acc.data(), out_proof, nullptr, true)
+                      : plonk_prove<1>(lg_n, polys, w_evals, pub.data(), n_public, acc.data(), out_proof, nullptr, true);
+HALO_API_END
+}
+int halo_dist_plonk_prove_circuit(int handle, const uint64_t* w_polys, const uint64_t* w_evals, const uint64_t* public_inputs,
+                                  size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof) { HALO_API_BEGIN
+    LOCK(); NEED_INIT();
+    HALO_CHECK(dist_on(), HALO_ENOINIT, "halo_dist_init has not been called");
+    HALO_CHECK(out_proof && (dist_rank() != 0 || (w_polys && w_evals)), HALO_EINVAL, "null argument");
+    int curve = 0; unsigned lg_n = 0;
+    if (int e = plonk_circuit_shape(handle, &curve, &lg_n)) return e;
+    std::vector<uint64_t> pub, acc;
+    if (int e = dist_plonk_small_inputs(lg_n, public_inputs, n_public, acc_prev, pub, acc)) return e;
+    return plonk_prove_resident(handle, w_polys, w_evals, pub.data(), n_public, acc.data(), out_proof, true);
 HALO_API_END
 }
 

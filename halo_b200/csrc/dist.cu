@@ -28,6 +28,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
 struct DistState {
@@ -51,7 +52,8 @@ int nccl_load() {
     a.CommDestroy = (decltype(a.CommDestroy))dlsym(h, "ncclCommDestroy");
     a.AllGather = (decltype(a.AllGather))dlsym(h, "ncclAllGather");
     a.GetErrorString = (decltype(a.GetErrorString))dlsym(h, "ncclGetErrorString");
-    HALO_CHECK(a.GetUniqueId && a.CommInitRank && a.CommDestroy && a.AllGather && a.GetErrorString, HALO_ECUDA,
+    a.Broadcast = (decltype(a.Broadcast))dlsym(h, "ncclBroadcast");
+    HALO_CHECK(a.GetUniqueId && a.CommInitRank && a.CommDestroy && a.AllGather && a.Broadcast && a.GetErrorString, HALO_ECUDA,
                "dist: libnccl lacks an expected symbol");
     a.handle = h;
     return HALO_OK;
@@ -97,6 +99,29 @@ int dist_allgather_host(const void* h_send, void* h_recv_all, size_t bytes) {
     HALO_CUDA(cudaMemcpyAsync(D.d_send, h_send, bytes, cudaMemcpyHostToDevice, st));
     HALO_NCCL(D.api.AllGather(D.d_send, D.d_recv, bytes, ncclUint8, D.comm, st));
     HALO_CUDA(cudaMemcpyAsync(h_recv_all, D.d_recv, bytes * D.world, cudaMemcpyDeviceToHost, st));
+    HALO_CUDA(cudaStreamSynchronize(st));
+    return HALO_OK;
+}
+
+// broadcast of a device buffer from `root`, in place, on the library stream
+int dist_bcast_dev(void* d_buf, size_t bytes, int root) {
+    DistState& D = ds();
+    HALO_CHECK(D.on, HALO_ENOINIT, "halo_dist_init has not been called");
+    if (bytes == 0) return HALO_OK;
+    HALO_NCCL(D.api.Broadcast(d_buf, d_buf, bytes, ncclUint8, root, D.comm, rt().stream));
+    return HALO_OK;
+}
+// broadcast of host data (small control payloads) from `root`, bounced through device staging; h_buf is read on the
+// root and written on the other ranks
+int dist_bcast_host(void* h_buf, size_t bytes, int root) {
+    DistState& D = ds();
+    HALO_CHECK(D.on, HALO_ENOINIT, "halo_dist_init has not been called");
+    if (bytes == 0) return HALO_OK;
+    cudaStream_t st = rt().stream;
+    if (int e = grow(&D.d_send, &D.send_cap, bytes, false)) return e;
+    if (D.rank == root) HALO_CUDA(cudaMemcpyAsync(D.d_send, h_buf, bytes, cudaMemcpyHostToDevice, st));
+    HALO_NCCL(D.api.Broadcast(D.d_send, D.d_send, bytes, ncclUint8, root, D.comm, st));
+    if (D.rank != root) HALO_CUDA(cudaMemcpyAsync(h_buf, D.d_send, bytes, cudaMemcpyDeviceToHost, st));
     HALO_CUDA(cudaStreamSynchronize(st));
     return HALO_OK;
 }

@@ -438,20 +438,36 @@ static inline size_t instance_words(unsigned lg_n) { return 54 + 24 * (size_t)lg
 
 }  // namespace
 
+// out[j * K + k] = in[k * n + j]: K coset-major blocks of n values -> the interleaved order of the K n-point transform
+template <int F>
+__global__ void __launch_bounds__(256) plonk_interleave_kernel(const Fe<F>* __restrict__ in, size_t n, unsigned K, Fe<F>* __restrict__ out) {
+    const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (t >= n * K) return;
+    const size_t j = t / K; const unsigned k = (unsigned)(t - j * K);
+    p_st<F>(out + t, p_ld<F>(in + (size_t)k * n + j));
+}
+
 size_t plonk_proof_words(unsigned lg_n) { return 78 * 4 + 33 * 12 + 2 * evalproof_words(lg_n) + instance_words(lg_n); }
 
 // proof layout (u64 words): vs = ws[16] rs[15] qs[10] ts[16] ids[8] sigmas[8] z z_omega w_omegas[3] (4 each),
 // Cs = ws[16] ts[16] z (12 each), pi_r, pi_r_omega (EvalProof: Ls Rs U c hiding C_bar w_prime), acc_next (instance)
 // d_circuit == nullptr: polys holds all 57 columns.  Otherwise polys holds the 16 witness columns only and d_circuit
 // the 41 circuit columns (q r id sigma) already on the device (plonk_circuit_load).
+// shard == true (halo_dist_plonk_prove): ONE proof over the GPUs of the library's communicator.  Every rank runs the
+// same control flow and the same transcript; the heavy steps are divided: rank 0 uploads and broadcasts the columns, the
+// commitments are point-range-sharded MSMs, the cosets of the quotient are divided among the ranks and all-gathered, the
+// two openings run on ranks 0 and 1; the serial pieces (grand product, evaluations, accumulation) are replicated.
+// polys / w_evals are read on rank 0 only.
 template <int C>
 int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, const uint64_t* pub, size_t n_pub,
-                const uint64_t* acc_prev, uint64_t* out, const void* d_circuit) {
+                const uint64_t* acc_prev, uint64_t* out, const void* d_circuit, bool shard) {
     typedef Host<C> H;
     typedef typename H::SF SF;
     constexpr int S = H::S;
     Runtime& R = rt();
     cudaStream_t st = R.stream;
+    const bool sharded = shard && dist_on() && dist_world() > 1;
+    const int rank = sharded ? dist_rank() : 0, world = sharded ? dist_world() : 1;
     HALO_CHECK(lg_n >= 1 && lg_n <= 22, HALO_EINVAL, "plonk: rows must be a power of two in [2, 2^22]");
     const size_t n = (size_t)1 << lg_n, d = n - 1;
     HALO_CHECK(R.pp[C].n >= n, HALO_EPARAMS, "plonk: public parameters not loaded for this many rows");
@@ -488,28 +504,34 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
         const SF* dc = (const SF*)d_circuit;
         HALO_CUDA(cudaMemcpyAsync(col(COL_Q), dc, (size_t)NQ * n * 32, cudaMemcpyDeviceToDevice, st));
         HALO_CUDA(cudaMemcpyAsync(col(COL_R), dc + (size_t)NQ * n, (size_t)(NR + 2 * NS) * n * 32, cudaMemcpyDeviceToDevice, st));
-        if (int e = upload_staged(col(COL_W), polys, (size_t)NW * n * 32)) return e;
-    } else {
-        if (int e = upload_staged(cols, polys, (size_t)N_IN * n * 32)) return e;
     }
     // staged evaluation vectors: PI (row i at omega^(i+1), negated), l1, and the three shifted witness columns
     SF* stage = tmp;                                       // [PI | l1 | wom0 wom1 wom2]
-    HALO_CUDA(cudaMemsetAsync(stage, 0, 2 * n * 32, st));
-    std::vector<SF> neg_pub(n_pub);
-    for (size_t i = 0; i < n_pub; ++i) neg_pub[i] = fe_neg<S>(H::scalar(pub + 4 * i));
-    if (n_pub) {
-        size_t head = std::min(n_pub, n - 1);
-        HALO_CUDA(cudaMemcpyAsync(stage + 1, neg_pub.data(), head * 32, cudaMemcpyHostToDevice, st));
-        if (n_pub == n) HALO_CUDA(cudaMemcpyAsync(stage, neg_pub.data() + (n - 1), 32, cudaMemcpyHostToDevice, st));
+    if (rank == 0) {
+        if (d_circuit) { if (int e = upload_staged(col(COL_W), polys, (size_t)NW * n * 32)) return e; }
+        else if (int e = upload_staged(cols, polys, (size_t)N_IN * n * 32)) return e;
+        HALO_CUDA(cudaMemsetAsync(stage, 0, 2 * n * 32, st));
+        std::vector<SF> neg_pub(n_pub);
+        for (size_t i = 0; i < n_pub; ++i) neg_pub[i] = fe_neg<S>(H::scalar(pub + 4 * i));
+        if (n_pub) {
+            size_t head = std::min(n_pub, n - 1);
+            HALO_CUDA(cudaMemcpyAsync(stage + 1, neg_pub.data(), head * 32, cudaMemcpyHostToDevice, st));
+            if (n_pub == n) HALO_CUDA(cudaMemcpyAsync(stage, neg_pub.data() + (n - 1), 32, cudaMemcpyHostToDevice, st));
+        }
+        HALO_CUDA(cudaMemcpyAsync(stage + n + (n > 1 ? 1 : 0), &one, 32, cudaMemcpyHostToDevice, st));
+        for (int i = 0; i < 3; ++i) {                      // shift_left of w_evals[i]
+            const uint64_t* src = w_evals + (size_t)i * n * 4;
+            SF* dst = stage + (size_t)(2 + i) * n;
+            if (int e = upload_staged(dst, src + 4, (n - 1) * 32)) return e;
+            HALO_CUDA(cudaMemcpyAsync(dst + (n - 1), src, 32, cudaMemcpyHostToDevice, st));
+        }
+        HALO_CUDA(cudaStreamSynchronize(st));              // neg_pub / one are host temporaries
     }
-    HALO_CUDA(cudaMemcpyAsync(stage + n + (n > 1 ? 1 : 0), &one, 32, cudaMemcpyHostToDevice, st));
-    for (int i = 0; i < 3; ++i) {                          // shift_left of w_evals[i]
-        const uint64_t* src = w_evals + (size_t)i * n * 4;
-        SF* dst = stage + (size_t)(2 + i) * n;
-        if (int e = upload_staged(dst, src + 4, (n - 1) * 32)) return e;
-        HALO_CUDA(cudaMemcpyAsync(dst + (n - 1), src, 32, cudaMemcpyHostToDevice, st));
+    if (sharded) {                                         // the columns cross the host link once and NVLink world - 1 times
+        if (d_circuit) { if (int e = dist_bcast_dev(col(COL_W), (size_t)NW * n * 32, 0)) return e; }
+        else if (int e = dist_bcast_dev(cols, (size_t)N_IN * n * 32, 0)) return e;
+        if (int e = dist_bcast_dev(stage, (size_t)5 * n * 32, 0)) return e;
     }
-    HALO_CUDA(cudaStreamSynchronize(st));                  // neg_pub / one are host temporaries
     if (int e = ntt_device<S>(stage, col(COL_PI), (int)lg_n, 1, true, nullptr)) return e;
     if (int e = ntt_device<S>(stage + n, col(COL_L1), (int)lg_n, 4, true, nullptr)) return e;   // l1, wom0..2 are adjacent
     // which columns are the zero polynomial: their commitments are the identity, their coset evaluations are zero,
@@ -531,6 +553,19 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     HALO_CUDA(cudaMemsetAsync(d_flags + (N_COLS - 1), 0, sizeof(int), st));
     const bool ids_derived = !ids_not_affine && !dense;
     auto nonzero = [&](int c) { return dense || h_flags[c] != 0; };
+    // nb adjacent columns -> nb commitments as one batched MSM over the resident generators; sharded: every rank takes
+    // its point range of every column (packed into a compact batch) and the window sums are all-gathered (dist.cu)
+    const size_t pr_lo = n * (size_t)rank / (size_t)world, pr_hi = n * (size_t)(rank + 1) / (size_t)world;
+    auto commit_run = [&](const SF* first, size_t nb, uint64_t* o) -> int {
+        if (!sharded) return msm_device<C>(R.pp[C].d_gs, first, n, nb, o, 0);
+        const size_t kl = pr_hi - pr_lo;
+        SF* pack = nullptr;
+        if (kl) {
+            if (int e = ws_get(WS_PLONK_PACK, nb * kl * 32, (void**)&pack)) return e;
+            HALO_CUDA(cudaMemcpy2DAsync(pack, kl * 32, first + pr_lo, n * 32, kl * 32, nb, cudaMemcpyDeviceToDevice, st));
+        }
+        return dist_msm_device<C>((const char*)R.pp[C].d_gs + pr_lo * 64, pack, kl, nb, o);
+    };
     // commitments of `count` adjacent columns: one batched MSM per run of nonzero columns
     auto commit_cols = [&](const SF* first, int count, auto&& live, uint64_t* o) -> int {
         const Jac<C> id = xyzz_to_jac<C>(xyzz_identity<C>());
@@ -538,7 +573,7 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
             if (!live(i)) { memcpy(o + 12 * i, &id, 96); ++i; continue; }
             int j = i + 1;
             while (j < count && live(j)) ++j;
-            if (int e = msm_device<C>(R.pp[C].d_gs, first + (size_t)i * n, n, (size_t)(j - i), o + 12 * i, 0)) return e;
+            if (int e = commit_run(first + (size_t)i * n, (size_t)(j - i), o + 12 * i)) return e;
             i = j;
         }
         return HALO_OK;
@@ -598,7 +633,7 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     plonk_nonzero_kernel<S><<<dim3(32, N_COLS - N_IN), 256, 0, st>>>(col(N_IN), n, d_flags + N_IN);
     R.launches += 1;
     HALO_CUDA(cudaMemcpyAsync(h_flags + N_IN, d_flags + N_IN, (N_COLS - N_IN) * sizeof(int), cudaMemcpyDeviceToHost, st));
-    if (int e = msm_device<C>(R.pp[C].d_gs, col(COL_Z), n, 1, o_Cz, 0)) return e;
+    if (int e = commit_run(col(COL_Z), 1, o_Cz)) return e;
     tr.absorb_point(H::from_words(o_Cz));
     lap("round 3 (z)");
 
@@ -664,17 +699,34 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
         const SF w16 = root_of_unity<S>(4);
         SF zh = w16;                                       // w16^c for c = 1, 3, ...
         const SF w16sq = fe_sqr<S>(w16);
+        const bool split = sharded && 8 % world == 0;      // rank r owns the cosets [8 r / world, 8 (r + 1) / world)
         for (unsigned k = 0; k < 8; ++k) {
             SF inv = fe_inv<S>(fe_sub<S>(zh, one));
-            if (int e = numerator_on_coset(2 * k + 1, f1, k, 8, &inv)) return e;
+            if (!split) { if (int e = numerator_on_coset(2 * k + 1, f1, k, 8, &inv)) return e; }
+            else if ((int)(k * world / 8) == rank) { if (int e = numerator_on_coset(2 * k + 1, f0 + (size_t)k * n, 0, 1, &inv)) return e; }
             zh = fe_mul<S>(zh, w16sq);
+        }
+        if (split) {                                       // coset-major blocks, gathered in place, then interleaved for the 8n transform
+            const size_t blk = (size_t)(8 / world) * n;
+            if (int e = dist_allgather_dev(f0 + (size_t)rank * blk, f0, blk * 32)) return e;
+            plonk_interleave_kernel<S><<<(unsigned)((8 * n + 255) / 256), 256, 0, st>>>(f0, n, 8, f1);
+            R.launches += 1;
         }
         lap("round 4 (quotient on 8 cosets)");
         if (int e = ntt_device<S>(f1, tq, (int)lg_n + 3, 1, true, &w16n)) return e;
         HALO_CUDA(cudaMemsetAsync(tq + 8 * n, 0, 8 * n * 32, st));
     } else {
-        for (unsigned c = 0; c < 16; ++c)
-            if (int e = numerator_on_coset(c, f0, c, 16, nullptr)) return e;
+        const bool split = sharded && 16 % world == 0;
+        for (unsigned c = 0; c < 16; ++c) {
+            if (!split) { if (int e = numerator_on_coset(c, f0, c, 16, nullptr)) return e; }
+            else if ((int)(c * world / 16) == rank) { if (int e = numerator_on_coset(c, f1 + (size_t)c * n, 0, 1, nullptr)) return e; }
+        }
+        if (split) {
+            const size_t blk = (size_t)(16 / world) * n;
+            if (int e = dist_allgather_dev(f1 + (size_t)rank * blk, f1, blk * 32)) return e;
+            plonk_interleave_kernel<S><<<(unsigned)((16 * n + 255) / 256), 256, 0, st>>>(f1, n, 16, f0);
+            R.launches += 1;
+        }
         lap("round 4 (numerator, 16 cosets)");
         if (int e = ntt_device<S>(f0, f1, (int)lg_n + 4, 1, true, nullptr)) return e;
         plonk_quotient_kernel<S><<<(unsigned)((16 * n + 255) / 256), 256, 0, st>>>(f1, 16 * n, n, tq);
@@ -772,7 +824,18 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
         memcpy(k ? o_piro : o_pir, q + 21, evalproof_words(lg_n) * 8);
         return HALO_OK;
     };
-    {
+    if (sharded) {                                         // opening k on rank k; the instances travel as one all-gather
+        std::vector<uint64_t> mine(iw, 0), all((size_t)iw * world);
+        if (rank < 2) {
+            if (int e = open_k(rank)) return e;
+            memcpy(mine.data(), insts.data() + (size_t)(1 + rank) * iw, iw * 8);
+        }
+        if (int e = dist_allgather_host(mine.data(), all.data(), (size_t)iw * 8)) return e;
+        for (int k = 0; k < 2; ++k) {
+            memcpy(insts.data() + (size_t)(1 + k) * iw, all.data() + (size_t)k * iw, iw * 8);
+            memcpy(k ? o_piro : o_pir, insts.data() + (size_t)(1 + k) * iw + 21, evalproof_words(lg_n) * 8);
+        }
+    } else {
         Runtime* lane = nullptr;
         if (R.tune[13] != 1 && !R.is_lane && pcdl_open_prepare<C>(n) == HALO_OK) lane = lane_get();
         int rc1 = HALO_OK;
@@ -802,8 +865,8 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     if (trace) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); }
     return HALO_OK;
 }
-template int plonk_prove<0>(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*);
-template int plonk_prove<1>(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*);
+template int plonk_prove<0>(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*, bool);
+template int plonk_prove<1>(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*, bool);
 
 // ---- circuit columns kept on the device across proofs: the analogue of the reference holding `x: PlonkCircuit` /
 // the Trace's polynomials for every proof of the same circuit (an IVC chain proves one circuit over and over)
@@ -844,13 +907,19 @@ void plonk_circuits_release() {
     circuits().clear();
 }
 
+int plonk_circuit_shape(int handle, int* curve, unsigned* lg_n) {
+    auto& v = circuits();
+    HALO_CHECK(handle >= 1 && (size_t)handle <= v.size() && v[handle - 1].d, HALO_EINVAL, "plonk: unknown circuit handle");
+    *curve = v[handle - 1].curve; *lg_n = v[handle - 1].lg_n;
+    return HALO_OK;
+}
 int plonk_prove_resident(int handle, const uint64_t* w_polys, const uint64_t* w_evals, const uint64_t* pub, size_t n_pub,
-                         const uint64_t* acc_prev, uint64_t* out) {
+                         const uint64_t* acc_prev, uint64_t* out, bool shard) {
     auto& v = circuits();
     HALO_CHECK(handle >= 1 && (size_t)handle <= v.size() && v[handle - 1].d, HALO_EINVAL, "plonk: unknown circuit handle");
     const ResidentCircuit& rc = v[handle - 1];
-    return rc.curve == 0 ? plonk_prove<0>(rc.lg_n, w_polys, w_evals, pub, n_pub, acc_prev, out, rc.d)
-                         : plonk_prove<1>(rc.lg_n, w_polys, w_evals, pub, n_pub, acc_prev, out, rc.d);
+    return rc.curve == 0 ? plonk_prove<0>(rc.lg_n, w_polys, w_evals, pub, n_pub, acc_prev, out, rc.d, shard)
+                         : plonk_prove<1>(rc.lg_n, w_polys, w_evals, pub, n_pub, acc_prev, out, rc.d, shard);
 }
 
 namespace {

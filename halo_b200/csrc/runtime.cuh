@@ -150,7 +150,7 @@ enum WsSlot {
     WS_SCALARS = 0, WS_BASES, WS_COUNTS, WS_OFFSETS, WS_CURSOR, WS_IDX, WS_ORDER, WS_SIZEHIST, WS_BUCKETS,
     WS_SEGSUM, WS_SEGWGT, WS_WINSUM, WS_TMP0, WS_TMP1, WS_TMP2, WS_TMP3, WS_IPA_G, WS_IPA_C, WS_IPA_Z, WS_IPA_T0,
     WS_IPA_T1, WS_IPA_S, WS_IPA_W, WS_NTT0, WS_NTT1, WS_PLONK_COLS, WS_PLONK_TMP, WS_PLONK_EV, WS_PLONK_F0,
-    WS_PLONK_F1, WS_PLONK_MISC, WS_NTT_TAB, WS_FOLD_TMP, WS_FOLD_STATE, WS_BA_W, WS_BA_P, WS_COUNT
+    WS_PLONK_F1, WS_PLONK_MISC, WS_NTT_TAB, WS_FOLD_TMP, WS_FOLD_STATE, WS_BA_W, WS_BA_P, WS_PLONK_PACK, WS_COUNT
 };
 
 }  // namespace halo

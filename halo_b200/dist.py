@@ -5,6 +5,7 @@ Every function here is collective: all ranks call it in the same order and recei
   msm / msm_global   ≙ point_dot_affine (crates/group/src/group.rs:48-50) sharded by point range
   acc_prover / acc_verifier / acc_decider  ≙ crates/accumulation/src/acc.rs:178-217 sharded by instance
   ntt                ≙ batched Evals::from_poly / interpolate (crates/group/src/poly.rs:56-64,133-139) by polynomial
+  plonk_prove        ≙ PlonkProof::naive_prover (crates/plonk/src/plonk/protocol.rs:64-355): ONE proof over all GPUs
 The 128-byte NCCL id travels over whatever channel the launcher has; `init_torch` uses a torch.distributed broadcast
 (any backend), `init_file` a file on a shared path."""
 import ctypes
@@ -120,3 +121,32 @@ def ntt(field, data, inverse=False, coset=None):
     check(lib.halo_dist_ntt(field, ptr(a.reshape(-1, 4)), ctypes.c_uint(n.bit_length() - 1), ctypes.c_size_t(a.shape[0]),
                             ctypes.c_int(1 if inverse else 0), ptr(g)))
     return a.reshape(shape)
+
+
+def plonk_prove(circuit, public_inputs=None, witness=None):
+    """≙ PlonkProof::naive_prover as ONE proof over the GPUs of the communicator.  `circuit` (shape / resident handle)
+    is needed on every rank; `public_inputs` and `witness` are read on rank 0 only (other ranks may pass None, but
+    every rank must know how many public inputs there are: pass the same `public_inputs`, or an int count)."""
+    from . import plonk as _plonk
+    _lib.ensure_init()
+    n = circuit.rows
+    lg_n = n.bit_length() - 1
+    out = np.zeros(_plonk.proof_words(lg_n), dtype=np.uint64)
+    if isinstance(public_inputs, int):
+        n_pub, pub, acc_prev = public_inputs, None, None
+    else:
+        pub = public_inputs.public_inputs
+        n_pub, acc_prev = pub.shape[0], public_inputs.acc_prev.q.w
+    pub_p = ptr(pub.reshape(-1)) if pub is not None and n_pub else None
+    acc_p = ptr(acc_prev) if acc_prev is not None else None
+    if circuit.handle:
+        w_polys = witness.polys[_plonk.Q_POLYS:_plonk.Q_POLYS + _plonk.W_POLYS] if witness is not None else None
+        check(lib.halo_dist_plonk_prove_circuit(ctypes.c_int(circuit.handle), ptr(w_polys.reshape(-1)) if w_polys is not None else None,
+                                                ptr(witness.w_evals.reshape(-1)) if witness is not None else None, pub_p,
+                                                ctypes.c_size_t(n_pub), acc_p, ptr(out)))
+    else:
+        check(lib.halo_dist_plonk_prove(circuit.curve, ctypes.c_uint(lg_n),
+                                        ptr(witness.polys.reshape(-1)) if witness is not None else None,
+                                        ptr(witness.w_evals.reshape(-1)) if witness is not None else None, pub_p,
+                                        ctypes.c_size_t(n_pub), acc_p, ptr(out)))
+    return _plonk.PlonkProof(circuit.curve, lg_n, out)

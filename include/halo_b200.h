@@ -191,6 +191,19 @@ int halo_dist_acc_prover(int curve, const uint64_t* instances, size_t m, uint64_
 int halo_dist_acc_verifier(int curve, const uint64_t* instances, size_t m, const uint64_t* acc);
 int halo_dist_acc_decider(int curve, const uint64_t* acc);
 int halo_dist_ntt(int field, uint64_t* data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null);
+/* ONE PLONK proof over the GPUs of the communicator (SURVEY section 8(e) / BASELINE config 4 at 2, 4, 8 GPUs;
+ * PlonkProof::naive_prover, crates/plonk/src/plonk/protocol.rs:64-355 -- the reference is one process with rayon).
+ * Collective.  polys / w_evals / public_inputs / acc_prev are READ ON RANK 0 ONLY (the other ranks may pass NULL): the
+ * columns cross the host link once and are broadcast over NVLink.  Every rank runs the same transcript; the commitments
+ * (protocol.rs:114,263) are point-range-sharded MSMs, the cosets of the quotient (protocol.rs:170-268) are divided
+ * among the ranks and all-gathered (when the world size divides 8), the two openings (protocol.rs:295-296) run on
+ * ranks 0 and 1, the serial pieces (grand product, evaluations, accumulation) are replicated.  Every rank receives the
+ * proof, identical to halo_plonk_prove's.  lg_n, n_public (and the handle's circuit) must agree on all ranks; the
+ * _circuit variant needs halo_plonk_circuit_load of the same circuit on every rank. */
+int halo_dist_plonk_prove(int curve, unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, const uint64_t* public_inputs,
+                          size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof);
+int halo_dist_plonk_prove_circuit(int handle, const uint64_t* w_polys, const uint64_t* w_evals, const uint64_t* public_inputs,
+                                  size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof);
 
 /* ---- NTT / iNTT  ≙ Evals::from_poly* / Evals::interpolate*  (crates/group/src/poly.rs:56-64,133-139) and the direct
  * evaluate_over_domain_by_ref / interpolate calls at crates/plonk/src/plonk/protocol.rs:82-106,140-141,158-159,195.

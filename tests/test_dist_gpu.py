@@ -2,7 +2,8 @@
 library's own NCCL communicator.  Every sharded result must equal the single-GPU one AND the oracle's, bit for bit:
   MSM by point range (whole problem on every rank; ragged local slices incl. an empty one; ranks whose slices pick
   different window widths), AS_DL by instance (prover / verifier / decider, a tampered instance), NTT batches by
-  polynomial (batch not divisible by the world size).
+  polynomial (batch not divisible by the world size), one PLONK proof over all ranks (inputs on rank 0 only; both
+  quotient paths; resident circuit).
 World size 1 runs everywhere (pack kernel, all-gather and combine with one rank); world size 2 needs two devices."""
 import os
 import tempfile
@@ -89,6 +90,38 @@ def _worker(rank, world, idfile, q):
             ok = (hb.dist.ntt(sf, x) == O.ntt(sf, x)).all() and (hb.dist.ntt(sf, x, inverse=True, coset=g) == O.ntt(sf, x, inverse=True, coset=g)).all()
             ok = ok and (hb.dist.ntt(sf, x[:1]) == O.ntt(sf, x[:1])).all()          # fewer polynomials than ranks
             res[f"ntt_{curve}"] = bool(ok)
+            # ---- ONE PLONK proof over all ranks: inputs on rank 0 only; equal to the oracle's proof and the single-GPU one
+            # (a satisfied circuit: 8-coset quotient; a random one: 16 cosets and the coefficient-form division)
+            import plonk_fixture as F
+            from test_plonk_gpu import same_proof
+            ok = True
+            for lg, kind, npub in ((9, "gates", 0), (8, "random", 3), (3, "mul", 1)):
+                rows = 1 << lg
+                gsr, Sr, Hr = O.pp_generate(curve, rows)
+                hb.pp.reset(curve); hb.pp.set_pp(curve, gsr, Sr, Hr); O.pp_set(curve, gsr, Sr, Hr)
+                c = F.make_circuit(O, curve, lg, kind, seed=70 + lg, n_public=npub)
+                acc0 = hb.acc.Accumulator.zero(curve, rows)
+                circuit = hb.plonk.PlonkCircuit.from_polys(curve, c["polys"], c["n_public"])
+                pub = hb.plonk.PlonkPublicInputs(c["public_inputs"], acc0)
+                wit = hb.plonk.PlonkWitness(c["polys"], c["w_evals"])
+                if rank == 0:
+                    pd = hb.dist.plonk_prove(circuit, pub, wit)
+                else:
+                    pd = hb.dist.plonk_prove(circuit, int(c["public_inputs"].shape[0]), None)
+                exp = O.plonk_prove(curve, lg, c["polys"], c["w_evals"], c["public_inputs"], acc0.q.w)
+                same_proof(O, curve, lg, pd.w, exp)
+                p1 = hb.plonk.PlonkProof.naive_prover(circuit, pub, wit)
+                same_proof(O, curve, lg, pd.w, p1.w)
+                if kind != "random":
+                    pd.verify(circuit, pub)
+                # circuit columns resident on every rank, witness from rank 0
+                circuit.make_resident(c["polys"])
+                try:
+                    pr = hb.dist.plonk_prove(circuit, pub, wit) if rank == 0 else hb.dist.plonk_prove(circuit, int(c["public_inputs"].shape[0]), None)
+                finally:
+                    circuit.release()
+                same_proof(O, curve, lg, pr.w, exp)
+            res[f"plonk_{curve}"] = ok
             hb.pp.reset(curve)
         hb.dist.shutdown()
         q.put((rank, res))
