@@ -544,8 +544,8 @@ def run_halo(args, rank, world, local_rank):
                 "note": "dominated by the protocol's serial Poseidon sponge over all m*(lg n + 1) challenges (host)"}
         halo_b200.pp.reset(PALLAS)
 
-    # whole proofs do not shard (replicas only): at N > 1 every rank proves its own 2^log_n-gate
-    # circuit at the same time; the time is the max over ranks
+    # whole proofs at N > 1, two ways: replicas (every rank proves its own 2^log_n-gate circuit at the same time; the
+    # time is the max over ranks) and ONE proof sharded over all ranks (further down)
     replicas = None
     if world > 1 and not args.no_path:
         lg = min(args.log_n, 20)
@@ -576,6 +576,47 @@ def run_halo(args, rank, world, local_rank):
         replicas = {"ms": best * 1e3, "proofs_per_s": world / best, "ms_circuit_resident": best_res * 1e3,
                     "proofs_per_s_circuit_resident": world / best_res,
                     "note": "one independent proof per GPU, max over ranks"}
+        # ONE proof over all N GPUs (halo_dist_plonk_prove: inputs on rank 0, columns broadcast over NVLink, commitments as
+        # point-range-sharded MSMs, quotient cosets divided among the ranks, the two openings on ranks 0 and 1); the same
+        # circuit on every rank so that the resident variant can be timed too.  Parity unpinned like every PLONK figure.
+        one = {}
+        # the sharded proof needs the SAME generators on every rank (h_pts is this rank's slice of the weak-scaling MSM)
+        gp = torch.empty((rows, 8), dtype=torch.int64, device="cuda")
+        check(lib.halo_gen_points_dev(PALLAS, ctypes.c_uint64(99), ctypes.c_size_t(0), ctypes.c_size_t(rows), ctypes.c_void_p(gp.data_ptr())))
+        halo_b200.pp.reset(PALLAS)
+        halo_b200.pp.set_pp(PALLAS, gp.cpu().numpy().view(np.uint64), sh[0], sh[1])
+        del gp
+        acc0 = halo_b200.acc.Accumulator.zero(PALLAS, rows)            # the genesis accumulator belongs to the generator set
+        pub = halo_b200.plonk.PlonkPublicInputs(np.zeros((0, 4), dtype=np.uint64), acc0)
+        for dense in (False, True):
+            polys, w_evals = halo_b200.plonk.synthetic_circuit(PALLAS, lg, seed=7, dense_gates=dense)
+            circuit = halo_b200.plonk.PlonkCircuit.from_polys(PALLAS, polys, 0)
+            wit = halo_b200.plonk.PlonkWitness(polys, w_evals)
+            def timed_one():
+                best = None
+                for _ in range(3):
+                    dist.barrier(); torch.cuda.synchronize()
+                    t = time.perf_counter()
+                    pi = halo_b200.dist.plonk_prove(circuit, pub, wit) if rank == 0 else halo_b200.dist.plonk_prove(circuit, 0, None)
+                    dt = time.perf_counter() - t
+                    tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+                    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                    best = float(tt.item()) if best is None else min(best, float(tt.item()))
+                return best, pi
+            t_one, pi = timed_one()
+            if not dense:
+                pi.verify(circuit, pub)
+            key = "all_gates" if dense else "mul_circuit"
+            one[key + "_ms"] = t_one * 1e3
+            if not dense:
+                circuit.make_resident(polys)
+                t_res, _ = timed_one()
+                circuit.release()
+                one[key + "_circuit_resident_ms"] = t_res * 1e3
+            del polys, w_evals, wit
+        one["note"] = ("ONE 2^%d-gate proof sharded over %d GPUs behind the C ABI (halo_dist_plonk_prove), host buffers on rank 0, "
+                       "max over ranks; parity unpinned (no reference proof exists)" % (lg, world))
+        replicas["one_proof"] = one
         halo_b200.pp.reset(PALLAS)
 
     if rank != 0:

@@ -48,6 +48,23 @@ def worker(rank, world, idfile, lgs):
                     circuit.release()
                 res[resident] = best
                 assert (pd.w[:78 * 4] == p1.w[:78 * 4]).all(), "evaluations differ from the single-GPU proof"
+                if os.environ.get("HALO_CHECK"):
+                    L = lg
+                    ew = 24 * L + 12 + 4 + 1 + 12 + 4
+                    o = 78 * 4 + 33 * 12
+                    parts = {"Cs": (78 * 4, o), "pi_r": (o, o + ew), "pi_ro": (o + ew, o + 2 * ew), "acc": (o + 2 * ew, len(pd.w))}
+                    for nm, (a, b) in parts.items():
+                        same = bool((pd.w[a:b] == p1.w[a:b]).all())
+                        print(f"rank {rank} lg {lg} dense {dense} resident {resident}: {nm} words equal to single-GPU: {same}", flush=True)
+                    if not dense:
+                        try:
+                            pd.verify(circuit, pub); print(f"rank {rank}: dist proof verifies", flush=True)
+                        except Exception as e:
+                            print(f"rank {rank}: dist proof REJECTED {e}", flush=True)
+                        try:
+                            p1.verify(circuit, pub); print(f"rank {rank}: single proof verifies", flush=True)
+                        except Exception as e:
+                            print(f"rank {rank}: single proof REJECTED {e}", flush=True)
             if rank == 0:
                 print(f"n=2^{lg} {'all gates' if dense else 'mul circuit'}: one proof on {world} GPUs {res[False] * 1e3:.1f} ms "
                       f"({res[True] * 1e3:.1f} ms circuit-resident); single GPU in this process {single * 1e3:.1f} ms", flush=True)
