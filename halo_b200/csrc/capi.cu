@@ -251,10 +251,10 @@ template <int C> int pcdl_commit(const uint64_t*, size_t, size_t, const uint64_t
 template <int C> int pcdl_chunked_commit(const uint64_t*, size_t, size_t, const uint64_t*, size_t, uint64_t*, size_t*);
 template <int C> int fold_table_build(size_t);
 template <int C> int pcdl_open(const uint64_t*, size_t, const uint64_t*, size_t, const uint64_t*, const uint64_t*, const uint64_t*,
-                               const uint64_t*, const uint64_t*, uint64_t*, uint64_t*, bool);
+                               const uint64_t*, const uint64_t*, uint64_t*, uint64_t*, bool, bool);
 template <int C> int pcdl_succinct_check(const uint64_t*, uint64_t*, uint64_t*);
 template <int C> int pcdl_check(const uint64_t*);
-template <int C> int acc_prover(const uint64_t*, size_t, uint64_t*);
+template <int C> int acc_prover(const uint64_t*, size_t, uint64_t*, bool);
 size_t plonk_proof_words(unsigned lg_n);
 template <int C> int plonk_prove(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*, bool);
 int plonk_circuit_shape(int handle, int* curve, unsigned* lg_n);
@@ -521,6 +521,7 @@ int halo_shutdown(void) { HALO_API_BEGIN
     for (int c = 0; c < 2; ++c) {
         if (R.pp[c].d_gs) cudaFree(R.pp[c].d_gs);
         if (R.pp[c].d_fold_tab) cudaFree(R.pp[c].d_fold_tab);
+        if (R.pp[c].d_fold_tab_loc) cudaFree(R.pp[c].d_fold_tab_loc);
         R.pp[c] = ResidentParams();
     }
     if (R.pinned) cudaFreeHost(R.pinned);
@@ -672,6 +673,7 @@ int halo_pp_reset(int curve) { HALO_API_BEGIN
     HALO_CUDA(cudaStreamSynchronize(R.stream));
     if (R.pp[curve].d_gs) cudaFree(R.pp[curve].d_gs);
     if (R.pp[curve].d_fold_tab) cudaFree(R.pp[curve].d_fold_tab);
+    if (R.pp[curve].d_fold_tab_loc) cudaFree(R.pp[curve].d_fold_tab_loc);
     R.pp[curve] = ResidentParams();
     return HALO_OK;
 HALO_API_END
@@ -1107,8 +1109,20 @@ int halo_pcdl_open(int curve, const uint64_t* coeffs, size_t len, const uint64_t
                    uint64_t* out_proof, uint64_t* out_v_or_null) { HALO_API_BEGIN
     LOCK(); NEED_INIT(); NEED_CURVE();
     HALO_CHECK(C_xyz && z && out_proof && (coeffs || len == 0), HALO_EINVAL, "pcdl_open: null pointer");
-    return curve == 0 ? pcdl_open<0>(coeffs, len, C_xyz, d, z, v_or_null, w_or_null, hide_q, hide_wbar, out_proof, out_v_or_null, false)
-                      : pcdl_open<1>(coeffs, len, C_xyz, d, z, v_or_null, w_or_null, hide_q, hide_wbar, out_proof, out_v_or_null, false);
+    return curve == 0 ? pcdl_open<0>(coeffs, len, C_xyz, d, z, v_or_null, w_or_null, hide_q, hide_wbar, out_proof, out_v_or_null, false, false)
+                      : pcdl_open<1>(coeffs, len, C_xyz, d, z, v_or_null, w_or_null, hide_q, hide_wbar, out_proof, out_v_or_null, false, false);
+HALO_API_END
+}
+// pcdl::open over the GPUs of the communicator (collective, the same inputs on every rank, the same proof on every rank):
+// the rounds above the fold-free tail run on interleaved slices of the generators (ipa.cu, pcdl_open with shard = true)
+int halo_dist_pcdl_open(int curve, const uint64_t* coeffs, size_t len, const uint64_t C_xyz[12], size_t d, const uint64_t z[4],
+                        const uint64_t* v_or_null, const uint64_t* w_or_null, const uint64_t* hide_q, const uint64_t* hide_wbar,
+                        uint64_t* out_proof, uint64_t* out_v_or_null) { HALO_API_BEGIN
+    LOCK(); NEED_INIT(); NEED_CURVE();
+    HALO_CHECK(dist_on(), HALO_ENOINIT, "halo_dist_init has not been called");
+    HALO_CHECK(C_xyz && z && out_proof && (coeffs || len == 0), HALO_EINVAL, "pcdl_open: null pointer");
+    return curve == 0 ? pcdl_open<0>(coeffs, len, C_xyz, d, z, v_or_null, w_or_null, hide_q, hide_wbar, out_proof, out_v_or_null, false, true)
+                      : pcdl_open<1>(coeffs, len, C_xyz, d, z, v_or_null, w_or_null, hide_q, hide_wbar, out_proof, out_v_or_null, false, true);
 HALO_API_END
 }
 int halo_pcdl_succinct_check(int curve, const uint64_t* instance, uint64_t* out_xis_or_null, uint64_t* out_U_or_null) { HALO_API_BEGIN
@@ -1127,7 +1141,7 @@ HALO_API_END
 int halo_acc_prover(int curve, const uint64_t* instances, size_t m, uint64_t* out_acc) { HALO_API_BEGIN
     LOCK(); NEED_INIT(); NEED_CURVE();
     HALO_CHECK(out_acc, HALO_EINVAL, "acc_prover: null pointer");
-    return curve == 0 ? acc_prover<0>(instances, m, out_acc) : acc_prover<1>(instances, m, out_acc);
+    return curve == 0 ? acc_prover<0>(instances, m, out_acc, false) : acc_prover<1>(instances, m, out_acc, false);
 HALO_API_END
 }
 int halo_acc_verifier(int curve, const uint64_t* instances, size_t m, const uint64_t* acc) { HALO_API_BEGIN

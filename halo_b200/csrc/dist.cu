@@ -153,8 +153,9 @@ __global__ void dist_pack_kernel(const XYZZ<C>* __restrict__ winsum, u32 c, u32 
     reinterpret_cast<u32*>(out + 128)[(j * DIST_SLOTS + w) * 32 + word] = reinterpret_cast<const u32*>(winsum)[t];
 }
 
+// base_stride != 0: MSM j of the batch reads bases + j * base_stride (the IPA's L / R pair over the two halves)
 template <int C>
-int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, size_t nbatch, uint64_t* out_xyz) {
+int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, size_t nbatch, uint64_t* out_xyz, ptrdiff_t base_stride) {
     DistState& D = ds();
     Runtime& R = rt();
     HALO_CHECK(D.on, HALO_ENOINIT, "halo_dist_init has not been called");
@@ -168,7 +169,7 @@ int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, 
         HALO_CUDA(cudaMemsetAsync(D.d_send, 0, 128, st));                      // nwin = 0: nothing to add
     } else {
         void* d_win = nullptr; int c = 0, nwin = 0;
-        if (int e = msm_windows_device<C>(d_bases, d_scalars, k_local, nbatch, 0, &d_win, &c, &nwin)) return e;
+        if (int e = msm_windows_device<C>(d_bases, d_scalars, k_local, nbatch, base_stride, &d_win, &c, &nwin)) return e;
         HALO_CHECK(nwin <= DIST_SLOTS, HALO_EINVAL, "dist msm: window count above the payload slots");
         const u32 words = (u32)(nbatch * nwin * 32);
         dist_pack_kernel<C><<<(words + 255) / 256, 256, 0, st>>>((const XYZZ<C>*)d_win, (u32)c, (u32)nwin, (u32)nbatch, (unsigned char*)D.d_send);
@@ -204,8 +205,8 @@ int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, 
     }
     return HALO_OK;
 }
-template int dist_msm_device<0>(const void*, const void*, size_t, size_t, uint64_t*);
-template int dist_msm_device<1>(const void*, const void*, size_t, size_t, uint64_t*);
+template int dist_msm_device<0>(const void*, const void*, size_t, size_t, uint64_t*, ptrdiff_t);
+template int dist_msm_device<1>(const void*, const void*, size_t, size_t, uint64_t*, ptrdiff_t);
 
 }  // namespace halo
 

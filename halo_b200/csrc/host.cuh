@@ -52,10 +52,10 @@ template <int C> int msm_device(const void* d_bases, const void* d_scalars, size
 template <int F> int ntt_device(Fe<F>* data, Fe<F>* out, int log_n, size_t batch, bool inverse, const Fe<F>* coset);
 template <int C> int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t d, const uint64_t* z_w,
                                const uint64_t* v_w, const uint64_t* w_w, const uint64_t* hide_q, const uint64_t* hide_wbar,
-                               uint64_t* out_proof, uint64_t* out_v, bool coeffs_resident);
+                               uint64_t* out_proof, uint64_t* out_v, bool coeffs_resident, bool shard = false);
 template <int C> int pcdl_check(const uint64_t* instance);
 template <int C> int pcdl_open_prepare(size_t n);   // builds, on the main runtime, what an opening of size n would build lazily
-template <int C> int acc_prover(const uint64_t* insts, size_t m, uint64_t* out_acc);
+template <int C> int acc_prover(const uint64_t* insts, size_t m, uint64_t* out_acc, bool shard_open = false);
 template <int C> int acc_verifier(const uint64_t* insts, size_t m, const uint64_t* acc, bool sharded = false);
 // dist.cu: the library's NCCL communicator (one process per GPU)
 bool dist_on();
@@ -65,6 +65,7 @@ int dist_allgather_dev(const void* d_send, void* d_recv, size_t bytes);
 int dist_allgather_host(const void* h_send, void* h_recv_all, size_t bytes);
 int dist_bcast_dev(void* d_buf, size_t bytes, int root);
 int dist_bcast_host(void* h_buf, size_t bytes, int root);
-template <int C> int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, size_t nbatch, uint64_t* out_xyz);
+template <int C> int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, size_t nbatch, uint64_t* out_xyz,
+                                     ptrdiff_t base_stride = 0);
 
 }  // namespace halo

@@ -27,14 +27,8 @@ extern "C" int halo_msm_proj(int, const uint64_t*, const uint64_t*, size_t, uint
 
 namespace halo {
 
-// dist.cu: the library's NCCL layer (one process per GPU)
-bool dist_on();
-int dist_rank();
-int dist_world();
-int dist_allgather_dev(const void* d_send, void* d_recv, size_t bytes);
-int dist_allgather_host(const void* h_send, void* h_recv_all, size_t bytes);
+// dist.cu (declared in host.cuh): the library's NCCL layer (one process per GPU)
 void dist_range(size_t total, size_t* lo, size_t* hi);
-template <int C> int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, size_t nbatch, uint64_t* out_xyz);
 
 template <int F> __device__ __forceinline__ Fe<F> g_ld(const Fe<F>* p) {
     Fe<F> r;
@@ -658,22 +652,16 @@ static bool fold_ops_from(const GlvScalar& g, FoldOps* ops) {
 // (halo_pp_reset / halo_shutdown free it).  Rows are produced FOLD_SLICE at a time so that the XYZZ staging buffer
 // stays at a quarter of the table's size; the affine conversion is the batched one the folds use.
 template <int C>
-static int ensure_fold_table(size_t n, const Affine<C>** out) {
+static int build_fold_table(const Affine<C>* hi, size_t m, void** tab_out) {
+    // rows 2^k * hi[j] and 3 * 2^k * hi[j], k < FOLD_ROWS, j < m; *tab_out == nullptr when the device has no room (ladder fold)
     Runtime& R = rt();
     cudaStream_t st = R.stream;
-    ResidentParams& P = R.pp[C];
-    *out = nullptr;
-    if (P.d_fold_tab && P.fold_tab_n == n) { *out = (const Affine<C>*)P.d_fold_tab; return HALO_OK; }
-    if (R.is_lane) return HALO_OK;                         // a lane only borrows the main runtime's table: ladder fold without one
-    HALO_CUDA(cudaStreamSynchronize(st));
-    if (P.d_fold_tab) { cudaFree(P.d_fold_tab); P.d_fold_tab = nullptr; P.fold_tab_n = 0; }
-    const size_t m = n / 2;
+    *tab_out = nullptr;
     void* tab = nullptr;
-    if (cudaMalloc(&tab, (size_t)2 * FOLD_ROWS * m * sizeof(Affine<C>)) != cudaSuccess) { cudaGetLastError(); return HALO_OK; }   // no room: ladder
+    if (cudaMalloc(&tab, (size_t)2 * FOLD_ROWS * m * sizeof(Affine<C>)) != cudaSuccess) { cudaGetLastError(); return HALO_OK; }
     XYZZ<C>*tmp, *state;
     if (int e = ws_get(WS_FOLD_TMP, (size_t)2 * FOLD_SLICE * m * sizeof(XYZZ<C>), (void**)&tmp)) { cudaFree(tab); return e; }
     if (int e = ws_get(WS_FOLD_STATE, m * sizeof(XYZZ<C>), (void**)&state)) { cudaFree(tab); return e; }
-    const Affine<C>* hi = (const Affine<C>*)P.d_gs + m;
     for (int k0 = 0; k0 < FOLD_ROWS; k0 += FOLD_SLICE) {
         const size_t cnt = (size_t)FOLD_SLICE * m;
         ipa_fold_table_rows_kernel<C><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(hi, state, m, k0 == 0, FOLD_SLICE, tmp, tmp + cnt);
@@ -690,7 +678,42 @@ static int ensure_fold_table(size_t n, const Affine<C>** out) {
         last_err() = "fold table: kernel failed";
         return HALO_ECUDA;
     }
+    *tab_out = tab;
+    return HALO_OK;
+}
+template <int C>
+static int ensure_fold_table(size_t n, const Affine<C>** out) {
+    Runtime& R = rt();
+    ResidentParams& P = R.pp[C];
+    *out = nullptr;
+    if (P.d_fold_tab && P.fold_tab_n == n) { *out = (const Affine<C>*)P.d_fold_tab; return HALO_OK; }
+    if (R.is_lane) return HALO_OK;                         // a lane only borrows the main runtime's table: ladder fold without one
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
+    if (P.d_fold_tab) { cudaFree(P.d_fold_tab); P.d_fold_tab = nullptr; P.fold_tab_n = 0; }
+    void* tab = nullptr;
+    if (int e = build_fold_table<C>((const Affine<C>*)P.d_gs + n / 2, n / 2, &tab)) return e;
+    if (!tab) return HALO_OK;
     P.d_fold_tab = tab; P.fold_tab_n = n;
+    *out = (const Affine<C>*)tab;
+    return HALO_OK;
+}
+// the same table over THIS RANK's generators of a sharded opening of size n (gl_hi: the upper half of the rank's
+// interleaved subset of pp.Gs, n / (2 world) points), kept with the parameter set like the global one
+template <int C>
+static int ensure_fold_table_local(size_t n, int world, int rank, const Affine<C>* gl_hi, const Affine<C>** out) {
+    Runtime& R = rt();
+    ResidentParams& P = R.pp[C];
+    *out = nullptr;
+    if (P.d_fold_tab_loc && P.fold_tab_loc_n == n && P.fold_tab_loc_world == world && P.fold_tab_loc_rank == rank) {
+        *out = (const Affine<C>*)P.d_fold_tab_loc; return HALO_OK;
+    }
+    if (R.is_lane) return HALO_OK;
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
+    if (P.d_fold_tab_loc) { cudaFree(P.d_fold_tab_loc); P.d_fold_tab_loc = nullptr; P.fold_tab_loc_n = 0; }
+    void* tab = nullptr;
+    if (int e = build_fold_table<C>(gl_hi, n / 2 / (size_t)world, &tab)) return e;
+    if (!tab) return HALO_OK;
+    P.d_fold_tab_loc = tab; P.fold_tab_loc_n = n; P.fold_tab_loc_world = world; P.fold_tab_loc_rank = rank;
     *out = (const Affine<C>*)tab;
     return HALO_OK;
 }
@@ -709,6 +732,25 @@ int fold_table_build(size_t n) {
 }
 template int fold_table_build<0>(size_t);
 template int fold_table_build<1>(size_t);
+
+// Interleaved ownership of a sharded opening: rank r of W holds the elements i = j * W + r.  E = uint4 words per element
+// (2 for a scalar, 4 for an affine point).  take: out[j] = in[j * W + r];  weave: out[j * W + p] = in[p * cnt + j] (the
+// all-gathered per-rank blocks back into index order).
+__global__ void __launch_bounds__(256) ipa_take_kernel(const uint4* __restrict__ in, size_t cnt, unsigned W, unsigned r, unsigned E,
+                                                       uint4* __restrict__ out) {
+    const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (t >= cnt * E) return;
+    const size_t j = t / E; const unsigned w = (unsigned)(t - j * E);
+    out[t] = in[(j * W + r) * E + w];
+}
+__global__ void __launch_bounds__(256) ipa_weave_kernel(const uint4* __restrict__ in, size_t cnt, unsigned W, unsigned E,
+                                                        uint4* __restrict__ out) {
+    const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (t >= cnt * W * E) return;
+    const size_t e = t / E; const unsigned w = (unsigned)(t - e * E);
+    const size_t p = e / cnt, j = e - p * cnt;
+    out[(j * W + p) * E + w] = in[t];
+}
 
 // fixed-base table for the first fold (tuning knob 0: 1 = never, 2 = for every size; by default for openings over the
 // whole parameter set of at least 2^16 generators, the size a prover keeps using)
@@ -736,8 +778,15 @@ template int pcdl_open_prepare<1>(size_t);
 template <int C>
 int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t d, const uint64_t* z_w,
               const uint64_t* v_w, const uint64_t* w_w, const uint64_t* hide_q, const uint64_t* hide_wbar,
-              uint64_t* out_proof, uint64_t* out_v, bool coeffs_resident) {
+              uint64_t* out_proof, uint64_t* out_v, bool coeffs_resident, bool shard) {
     // coeffs_resident: the n zero-padded coefficients are already in the WS_IPA_C workspace (acc::prover's h(X))
+    // shard (collective; same inputs on every rank of the library's communicator): the rounds above the fold-free tail
+    // run on interleaved slices -- rank r of W owns the indices i = j W + r of the generator, coefficient and power
+    // vectors, so that a fold pairs (i, i + m) INSIDE a rank for every m that is a multiple of W.  Locally that is an
+    // ordinary opening of size n / W (same kernels, same fold variants, a fold table over the rank's own generators),
+    // except that the two dot products are summed over the ranks and L / R are point-range-sharded MSMs
+    // (dist_msm_device).  When the tail starts (<= 2^15 generators, latency-bound) the three vectors are all-gathered
+    // and every rank finishes the opening redundantly.  Same transcript on every rank, same proof as the single-GPU path.
     typedef Host<C> H;
     typedef typename H::SF SF;
     typedef typename H::Pt Pt;
@@ -813,8 +862,32 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
     SF xi = tr.challenge();
     FixedBase<C> Hp(H::mul(H::from_affine_words(R.pp[C].h_xy), xi));
 
-    // gs = pp.Gs[0..n] (pcdl.rs:394)
-    HALO_CUDA(cudaMemcpyAsync(gs, R.pp[C].d_gs, n * 64, cudaMemcpyDeviceToDevice, st));
+    // sharded rounds need a power-of-two world that leaves every rank a whole tail's worth of work above the tail
+    int W = 1, rank = 0;
+    {
+        const int tl = R.tune[3] == 0 ? 15 : R.tune[3];
+        if (shard && dist_on() && dist_world() > 1 && (dist_world() & (dist_world() - 1)) == 0 && tl >= 8 && tl <= 20 &&
+            n >= ((size_t)4 << tl) && (size_t)dist_world() <= ((size_t)1 << (tl - 2)) && !R.is_lane) {
+            W = dist_world(); rank = dist_rank();
+        }
+    }
+    Affine<C>* gs_full = gs; SF *cs_full = cs, *zs_full = zs;       // the replicated tail continues in these
+    if (W == 1) {
+        // gs = pp.Gs[0..n] (pcdl.rs:394)
+        HALO_CUDA(cudaMemcpyAsync(gs, R.pp[C].d_gs, n * 64, cudaMemcpyDeviceToDevice, st));
+    } else {
+        const size_t nl = n / (size_t)W;
+        Affine<C>* gl; SF *cl, *zl;
+        if (int e = ws_get(WS_IPA_GL, nl * 64, (void**)&gl)) return e;
+        if (int e = ws_get(WS_IPA_CL, 2 * nl * 32, (void**)&cl)) return e;
+        zl = cl + nl;
+        ipa_take_kernel<<<(unsigned)((nl * 4 + 255) / 256), 256, 0, st>>>((const uint4*)R.pp[C].d_gs, nl, (unsigned)W, (unsigned)rank, 4, (uint4*)gl);
+        ipa_take_kernel<<<(unsigned)((nl * 2 + 255) / 256), 256, 0, st>>>((const uint4*)cs, nl, (unsigned)W, (unsigned)rank, 2, (uint4*)cl);
+        ipa_take_kernel<<<(unsigned)((nl * 2 + 255) / 256), 256, 0, st>>>((const uint4*)zs, nl, (unsigned)W, (unsigned)rank, 2, (uint4*)zl);
+        R.launches += 3;
+        HALO_CUDA(cudaGetLastError());
+        gs = gl; cs = cl; zs = zl;
+    }
 
     // optional phase trace (tuning knob 7): wall clock with a stream sync at each phase boundary
     const bool trace = R.tune[7] != 0;
@@ -828,26 +901,55 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
     // fixed-base table for the first fold (tuning knob 0: 1 = never, 2 = for every size; by default for openings
     // over the whole parameter set of at least 2^16 generators, the size a prover keeps using)
     const Affine<C>* fold_tab = nullptr;
-    if (open_uses_fold_table<C>(n))
-        if (int e = ensure_fold_table<C>(n, &fold_tab)) return e;
+    if (open_uses_fold_table<C>(n)) {
+        if (W == 1) { if (int e = ensure_fold_table<C>(n, &fold_tab)) return e; }
+        else if (int e = ensure_fold_table_local<C>(n, W, rank, gs + n / 2 / (size_t)W, &fold_tab)) return e;
+    }
     bool pending = false;
     SF pend_xi = fe_zero<S>();
     bool tail = false;
     size_t T = 0, nu = 0;
     int w_cur = 0;
     SF *tail_s = nullptr, *tail_w = nullptr;
-    size_t m = n / 2;
+    size_t m = n / 2 / (size_t)W;                         // LOCAL half-length while the rounds are sharded (W > 1)
     for (unsigned r = 0; r < lg_n; ++r, m /= 2) {
         double t0 = trace ? now() : 0;
+        if (W > 1 && !pending && 2 * m * (size_t)W <= tail_max) {
+            // the tail starts: gather the interleaved slices (2m elements per rank) back into index order; from here on
+            // every rank holds the whole (small) problem and the rounds run as on one GPU
+            const size_t cnt = 2 * m;
+            unsigned char* stage;
+            if (int e = ws_get(WS_IPA_T1, (size_t)W * cnt * 128, (void**)&stage)) return e;
+            unsigned char* sg = stage; unsigned char* sc = stage + (size_t)W * cnt * 64; unsigned char* sz = sc + (size_t)W * cnt * 32;
+            HALO_CUDA(cudaMemcpyAsync(sg + (size_t)rank * cnt * 64, gs, cnt * 64, cudaMemcpyDeviceToDevice, st));
+            HALO_CUDA(cudaMemcpyAsync(sc + (size_t)rank * cnt * 32, cs, cnt * 32, cudaMemcpyDeviceToDevice, st));
+            HALO_CUDA(cudaMemcpyAsync(sz + (size_t)rank * cnt * 32, zs, cnt * 32, cudaMemcpyDeviceToDevice, st));
+            if (int e = dist_allgather_dev(sg + (size_t)rank * cnt * 64, sg, cnt * 64)) return e;
+            if (int e = dist_allgather_dev(sc + (size_t)rank * cnt * 32, sc, cnt * 32)) return e;
+            if (int e = dist_allgather_dev(sz + (size_t)rank * cnt * 32, sz, cnt * 32)) return e;
+            ipa_weave_kernel<<<(unsigned)((cnt * W * 4 + 255) / 256), 256, 0, st>>>((const uint4*)sg, cnt, (unsigned)W, 4, (uint4*)gs_full);
+            ipa_weave_kernel<<<(unsigned)((cnt * W * 2 + 255) / 256), 256, 0, st>>>((const uint4*)sc, cnt, (unsigned)W, 2, (uint4*)cs_full);
+            ipa_weave_kernel<<<(unsigned)((cnt * W * 2 + 255) / 256), 256, 0, st>>>((const uint4*)sz, cnt, (unsigned)W, 2, (uint4*)zs_full);
+            R.launches += 3;
+            HALO_CUDA(cudaGetLastError());
+            gs = gs_full; cs = cs_full; zs = zs_full;
+            m *= (size_t)W; W = 1;
+        }
         const int g = (int)std::min<size_t>(256, (m + 255) / 256);
         ipa_dots_kernel<S><<<g, 256, 0, st>>>(cs, zs, m, part);
         R.launches += 1;
         SF dots[2];
         if (int e = sum_partials<S>(part, g, dots, 2)) return e;
+        if (W > 1) {                                       // the dot products are sums over all ranks' slices
+            std::vector<SF> all((size_t)2 * W);
+            if (int e = dist_allgather_host(dots, all.data(), 64)) return e;
+            dots[0] = fe_zero<S>(); dots[1] = fe_zero<S>();
+            for (int p = 0; p < W; ++p) { dots[0] = fe_add<S>(dots[0], all[2 * p]); dots[1] = fe_add<S>(dots[1], all[2 * p + 1]); }
+        }
         // one pipeline, two MSMs: [0] = R = <l(c), r(G)>, [1] = L = <r(c), l(G)>  (pcdl.rs:412-418)
         uint64_t lr[24];
         double t1 = trace ? now() : 0;
-        if (!tail && !pending && 2 * m <= tail_max) {     // switch: freeze the generators, start the weights at [1]
+        if (!tail && !pending && 2 * m <= tail_max && W == 1) {     // switch: freeze the generators, start the weights at [1]
             tail = true; T = 2 * m; nu = 1;
             if (int e = ws_get(WS_IPA_S, 2 * T * 32, (void**)&tail_s)) return e;
             if (int e = ws_get(WS_IPA_W, 2 * T * 32, (void**)&tail_w)) return e;
@@ -867,9 +969,11 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
             HALO_CUDA(cudaMemcpyAsync(tail_w, wh, 64, cudaMemcpyHostToDevice, st));
             ipa_tail_scalars_kernel<S><<<(unsigned)((Tp + 255) / 256), 256, 0, st>>>(cs, tail_w, m, Tp, tail_s, tail_s + Tp);
             R.launches += 1;
-            if (int e = msm_device<C>(gs, tail_s, Tp, 2, lr, 0)) return e;     // syncs: wh may go out of scope
+            if (W > 1) { if (int e = dist_msm_device<C>(gs, tail_s, Tp, 2, lr, 0)) return e; }
+            else if (int e = msm_device<C>(gs, tail_s, Tp, 2, lr, 0)) return e;     // syncs: wh may go out of scope
         } else {
-            if (int e = msm_device<C>(gs + m, cs, m, 2, lr, -(ptrdiff_t)m)) return e;
+            if (W > 1) { if (int e = dist_msm_device<C>(gs + m, cs, m, 2, lr, -(ptrdiff_t)m)) return e; }
+            else if (int e = msm_device<C>(gs + m, cs, m, 2, lr, -(ptrdiff_t)m)) return e;
         }
         double t2 = trace ? now() : 0;
         Pt Rp = H::add(H::from_words(lr), Hp.mul(dots[1]));
@@ -919,7 +1023,7 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
             if (m >= 8192) xyzz_batch_affine_kernel<C, 8><<<(unsigned)((m / 8 + 128) / 128), 128, 0, st>>>(folded, m, gs);
             else xyzz_batch_affine_kernel<C, 1><<<(unsigned)((m + 127) / 128), 128, 0, st>>>(folded, m, gs);
             R.launches += 3;
-        } else if (radix4 && m > tail_max && m >= 2) {
+        } else if (radix4 && m * (size_t)W > tail_max && m >= 2) {
             // delay this fold: only the scalar vectors are folded now, the generators wait for the next challenge
             ipa_tail_fold_kernel<S><<<(unsigned)((m + 255) / 256), 256, 0, st>>>(cs, zs, m, nullptr, 0, nullptr, xi_next, xi_inv);
             R.launches += 1;
@@ -1353,7 +1457,7 @@ static int acc_common(const uint64_t* insts, size_t m, AccCommon<C>* out, bool s
 
 // acc::prover (acc.rs:178-198): out_acc is a flat instance
 template <int C>
-int acc_prover(const uint64_t* insts, size_t m, uint64_t* out_acc) {
+int acc_prover(const uint64_t* insts, size_t m, uint64_t* out_acc, bool shard_open) {
     typedef Host<C> H;
     typedef typename H::SF SF;
     constexpr int S = H::S;
@@ -1373,7 +1477,7 @@ int acc_prover(const uint64_t* insts, size_t m, uint64_t* out_acc) {
     H::to_words(cs.Cbar, Cw);
     // pcdl::open evaluates h(z) itself (pcdl.rs:471); numerically the same value as v
     return pcdl_open<C>(nullptr, n, Cw, cs.d, (const uint64_t*)&cs.z, nullptr, nullptr, nullptr, nullptr, out_acc + 21,
-                        nullptr, true);
+                        nullptr, true, shard_open);
 }
 
 // sum of `parts` vectors of n elements: out[i] = sum_p in[p * n + i]  (modular addition is not an NCCL operator)
@@ -1387,8 +1491,8 @@ __global__ void __launch_bounds__(256) vec_sum_kernel(const Fe<F>* __restrict__ 
 }
 
 // acc::prover across the GPUs of the communicator: succinct checks by instance (acc_common), h(X) = sum alpha^i h_i(X)
-// as per-rank partial coefficient vectors over an instance range, all-gathered and added on every rank; the opening
-// itself is sequential in its challenges and runs replicated, so every rank returns the same accumulator.
+// as per-rank partial coefficient vectors over an instance range, all-gathered and added on every rank; the opening's
+// rounds above the fold-free tail are sharded too (pcdl_open with shard = true); every rank returns the same accumulator.
 template <int C>
 int acc_prover_dist(const uint64_t* insts, size_t m, uint64_t* out_acc) {
     typedef Host<C> H;
@@ -1421,7 +1525,7 @@ int acc_prover_dist(const uint64_t* insts, size_t m, uint64_t* out_acc) {
     uint64_t Cw[12];
     H::to_words(cs.Cbar, Cw);
     return pcdl_open<C>(nullptr, n, Cw, cs.d, (const uint64_t*)&cs.z, nullptr, nullptr, nullptr, nullptr, out_acc + 21,
-                        nullptr, true);
+                        nullptr, true, true);
 }
 template int acc_prover_dist<0>(const uint64_t*, size_t, uint64_t*);
 template int acc_prover_dist<1>(const uint64_t*, size_t, uint64_t*);
@@ -1474,15 +1578,15 @@ int acc_verifier(const uint64_t* insts, size_t m, const uint64_t* acc, bool shar
 template int pcdl_commit<0>(const uint64_t*, size_t, size_t, const uint64_t*, uint64_t*);
 template int pcdl_commit<1>(const uint64_t*, size_t, size_t, const uint64_t*, uint64_t*);
 template int pcdl_open<0>(const uint64_t*, size_t, const uint64_t*, size_t, const uint64_t*, const uint64_t*, const uint64_t*,
-                          const uint64_t*, const uint64_t*, uint64_t*, uint64_t*, bool);
+                          const uint64_t*, const uint64_t*, uint64_t*, uint64_t*, bool, bool);
 template int pcdl_open<1>(const uint64_t*, size_t, const uint64_t*, size_t, const uint64_t*, const uint64_t*, const uint64_t*,
-                          const uint64_t*, const uint64_t*, uint64_t*, uint64_t*, bool);
+                          const uint64_t*, const uint64_t*, uint64_t*, uint64_t*, bool, bool);
 template int pcdl_succinct_check<0>(const uint64_t*, uint64_t*, uint64_t*);
 template int pcdl_succinct_check<1>(const uint64_t*, uint64_t*, uint64_t*);
 template int pcdl_check<0>(const uint64_t*);
 template int pcdl_check<1>(const uint64_t*);
-template int acc_prover<0>(const uint64_t*, size_t, uint64_t*);
-template int acc_prover<1>(const uint64_t*, size_t, uint64_t*);
+template int acc_prover<0>(const uint64_t*, size_t, uint64_t*, bool);
+template int acc_prover<1>(const uint64_t*, size_t, uint64_t*, bool);
 template int acc_verifier<0>(const uint64_t*, size_t, const uint64_t*, bool);
 template int acc_verifier<1>(const uint64_t*, size_t, const uint64_t*, bool);
 

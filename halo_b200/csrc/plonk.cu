@@ -809,7 +809,7 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     // helper thread in the library's second execution context (lane_get: own stream, workspaces, pinned buffer) beside
     // the first.  d_r is complete here (the evaluations above synchronised the stream).  Tuning key 13 = 1: one after
     // the other.
-    auto open_k = [&](int k) -> int {
+    auto open_k = [&](int k, bool shard_open = false) -> int {
         Runtime& Rk = rt();                                 // the main runtime, or the lane inside the helper thread
         uint64_t* q = insts.data() + (size_t)(1 + k) * iw;
         SF* cs;
@@ -819,12 +819,16 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
         q[12] = d;
         const SF& at = k ? xi_omega : xi;
         H::put_scalar(at, q + 13);
-        if (int e = pcdl_open<C>(nullptr, n, q, d, (const uint64_t*)&at, nullptr, nullptr, nullptr, nullptr, q + 21, q + 17, true))
+        if (int e = pcdl_open<C>(nullptr, n, q, d, (const uint64_t*)&at, nullptr, nullptr, nullptr, nullptr, q + 21, q + 17, true, shard_open))
             return e;
         memcpy(k ? o_piro : o_pir, q + 21, evalproof_words(lg_n) * 8);
         return HALO_OK;
     };
-    if (sharded) {                                         // opening k on rank k; the instances travel as one all-gather
+    if (sharded && world >= 4) {
+        // four or more GPUs: each opening's rounds above its fold-free tail sharded over ALL ranks (pcdl_open, shard = true),
+        // one opening after the other; every rank ends up with both proofs
+        for (int k = 0; k < 2; ++k) if (int e = open_k(k, true)) return e;
+    } else if (sharded) {                                  // two GPUs: opening k on rank k; the instances travel as one all-gather
         std::vector<uint64_t> mine(iw, 0), all((size_t)iw * world);
         if (rank < 2) {
             if (int e = open_k(rank)) return e;
@@ -860,7 +864,7 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
         else if (int e = open_k(1)) return e;
     }
     lap("round 5 (two openings)");
-    if (int e = acc_prover<C>(insts.data(), 3, o_acc)) return e;
+    if (int e = acc_prover<C>(insts.data(), 3, o_acc, sharded)) return e;   // sharded: its opening's upper rounds over all ranks
     lap("round 5 (accumulate)");
     if (trace) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); }
     return HALO_OK;

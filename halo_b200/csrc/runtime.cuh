@@ -25,6 +25,9 @@ struct ResidentParams {
     uint64_t s_xy[8], h_xy[8]; // host copies (affine, Montgomery)
     void* d_fold_tab = nullptr;   // IPA fixed-base fold table: 2^k * Gs[n/2 + j], k-major (ipa.cu), for openings of size fold_tab_n
     size_t fold_tab_n = 0;
+    void* d_fold_tab_loc = nullptr;   // the same table over this rank's generators of a sharded opening (ipa.cu)
+    size_t fold_tab_loc_n = 0;
+    int fold_tab_loc_world = 0, fold_tab_loc_rank = 0;
 };
 
 struct Runtime {
@@ -150,7 +153,7 @@ enum WsSlot {
     WS_SCALARS = 0, WS_BASES, WS_COUNTS, WS_OFFSETS, WS_CURSOR, WS_IDX, WS_ORDER, WS_SIZEHIST, WS_BUCKETS,
     WS_SEGSUM, WS_SEGWGT, WS_WINSUM, WS_TMP0, WS_TMP1, WS_TMP2, WS_TMP3, WS_IPA_G, WS_IPA_C, WS_IPA_Z, WS_IPA_T0,
     WS_IPA_T1, WS_IPA_S, WS_IPA_W, WS_NTT0, WS_NTT1, WS_PLONK_COLS, WS_PLONK_TMP, WS_PLONK_EV, WS_PLONK_F0,
-    WS_PLONK_F1, WS_PLONK_MISC, WS_NTT_TAB, WS_FOLD_TMP, WS_FOLD_STATE, WS_BA_W, WS_BA_P, WS_PLONK_PACK, WS_COUNT
+    WS_PLONK_F1, WS_PLONK_MISC, WS_NTT_TAB, WS_FOLD_TMP, WS_FOLD_STATE, WS_BA_W, WS_BA_P, WS_PLONK_PACK, WS_IPA_GL, WS_IPA_CL, WS_COUNT
 };
 
 }  // namespace halo

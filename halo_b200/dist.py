@@ -5,6 +5,7 @@ Every function here is collective: all ranks call it in the same order and recei
   msm / msm_global   ≙ point_dot_affine (crates/group/src/group.rs:48-50) sharded by point range
   acc_prover / acc_verifier / acc_decider  ≙ crates/accumulation/src/acc.rs:178-217 sharded by instance
   ntt                ≙ batched Evals::from_poly / interpolate (crates/group/src/poly.rs:56-64,133-139) by polynomial
+  pcdl_open          ≙ pcdl::open_without_eval (crates/accumulation/src/pcdl.rs:326-473), upper rounds on interleaved slices
   plonk_prove        ≙ PlonkProof::naive_prover (crates/plonk/src/plonk/protocol.rs:64-355): ONE proof over all GPUs
 The 128-byte NCCL id travels over whatever channel the launcher has; `init_torch` uses a torch.distributed broadcast
 (any backend), `init_file` a file on a shared path."""
@@ -150,3 +151,9 @@ def plonk_prove(circuit, public_inputs=None, witness=None):
                                         ptr(witness.w_evals.reshape(-1)) if witness is not None else None, pub_p,
                                         ctypes.c_size_t(n_pub), acc_p, ptr(out)))
     return _plonk.PlonkProof(circuit.curve, lg_n, out)
+
+
+def pcdl_open(curve, coeffs, C, d, z, v=None, w=None, hide_q=None, hide_wbar=None):
+    """≙ pcdl::open_without_eval over the GPUs of the communicator (the same arguments on every rank); returns
+    (EvalProof, v) like pcdl.open_without_eval."""
+    return pcdl.open_without_eval(curve, coeffs, C, d, z, v, w, hide_q, hide_wbar, _entry=lib.halo_dist_pcdl_open)

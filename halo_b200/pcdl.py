@@ -90,10 +90,11 @@ class EvalProof:
     w_prime = property(lambda s: s.w[24 * s.lg_n + 29: 24 * s.lg_n + 33] if s.hiding else None)
 
 
-def open_without_eval(curve, coeffs, C, d, z, v, w=None, hide_q=None, hide_wbar=None):
+def open_without_eval(curve, coeffs, C, d, z, v, w=None, hide_q=None, hide_wbar=None, _entry=None):
     """≙ pcdl::open_without_eval (pcdl.rs:326-453); v=None gives pcdl::open (pcdl.rs:463-473).
     Returns (EvalProof, v).  Hiding needs the prover's randomness (the reference draws it from `rng`)."""
     _lib.ensure_init()
+    entry = _entry or lib.halo_pcdl_open
     c = as_u64(coeffs, 4)
     n = d + 1
     lg_n = max(_lg(n), 0)
@@ -101,9 +102,9 @@ def open_without_eval(curve, coeffs, C, d, z, v, w=None, hide_q=None, hide_wbar=
     vout = np.empty(4, dtype=np.uint64)
     a4 = lambda x: as_u64(x, 4).reshape(4) if x is not None else None
     q = as_u64(hide_q, 4) if hide_q is not None else None
-    check(lib.halo_pcdl_open(curve, ptr(c) if c.shape[0] else None, ctypes.c_size_t(c.shape[0]),
-                             ptr(as_u64(C, 12).reshape(12)), ctypes.c_size_t(d), ptr(a4(z)), ptr(a4(v)), ptr(a4(w)),
-                             ptr(q), ptr(a4(hide_wbar)), ptr(proof), ptr(vout)))
+    check(entry(curve, ptr(c) if c.shape[0] else None, ctypes.c_size_t(c.shape[0]),
+                ptr(as_u64(C, 12).reshape(12)), ctypes.c_size_t(d), ptr(a4(z)), ptr(a4(v)), ptr(a4(w)),
+                ptr(q), ptr(a4(hide_wbar)), ptr(proof), ptr(vout)))
     return EvalProof(proof, lg_n), vout
 
 

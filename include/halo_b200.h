@@ -191,6 +191,16 @@ int halo_dist_acc_prover(int curve, const uint64_t* instances, size_t m, uint64_
 int halo_dist_acc_verifier(int curve, const uint64_t* instances, size_t m, const uint64_t* acc);
 int halo_dist_acc_decider(int curve, const uint64_t* acc);
 int halo_dist_ntt(int field, uint64_t* data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null);
+/* pcdl::open (crates/accumulation/src/pcdl.rs:326-473) over the GPUs of the communicator.  Collective; every rank passes
+ * the SAME arguments (those of halo_pcdl_open) and receives the same proof, equal to halo_pcdl_open's.  The rounds above
+ * the fold-free tail run on interleaved slices (rank r owns the indices j * world + r of the generator, coefficient and
+ * power vectors, so every fold pairs two elements of the same rank): L / R are point-range-sharded MSMs, the two dot
+ * products are summed over the ranks; at <= 2^15 generators the slices are all-gathered and the latency-bound tail runs
+ * replicated.  Needs a power-of-two world size and n >= 2^17, otherwise it is halo_pcdl_open on every rank.
+ * halo_dist_acc_prover's opening is sharded the same way. */
+int halo_dist_pcdl_open(int curve, const uint64_t* coeffs, size_t len, const uint64_t C_xyz[12], size_t d, const uint64_t z[4],
+                        const uint64_t* v_or_null, const uint64_t* w_or_null, const uint64_t* hide_q, const uint64_t* hide_wbar,
+                        uint64_t* out_proof, uint64_t* out_v_or_null);
 /* ONE PLONK proof over the GPUs of the communicator (SURVEY section 8(e) / BASELINE config 4 at 2, 4, 8 GPUs;
  * PlonkProof::naive_prover, crates/plonk/src/plonk/protocol.rs:64-355 -- the reference is one process with rayon).
  * Collective.  polys / w_evals / public_inputs / acc_prev are READ ON RANK 0 ONLY (the other ranks may pass NULL): the

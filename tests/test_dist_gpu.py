@@ -90,6 +90,37 @@ def _worker(rank, world, idfile, q):
             ok = (hb.dist.ntt(sf, x) == O.ntt(sf, x)).all() and (hb.dist.ntt(sf, x, inverse=True, coset=g) == O.ntt(sf, x, inverse=True, coset=g)).all()
             ok = ok and (hb.dist.ntt(sf, x[:1]) == O.ntt(sf, x[:1])).all()          # fewer polynomials than ranks
             res[f"ntt_{curve}"] = bool(ok)
+            # ---- one opening over all ranks (rounds above the fold-free tail on interleaved slices): equal to the
+            # single-GPU opening and, at the smaller size, to the oracle's; hiding and not; with and without the fold table
+            from halo_b200._lib import lib as _l
+            for lgo, check_oracle in ((17, curve == 0), (18, False)):
+                no = 1 << lgo
+                gso = O.points_arith(curve, no + 2, k0=0x51 + curve)
+                hb.pp.reset(curve); hb.pp.set_pp(curve, gso[:no], gso[no], gso[no + 1])
+                po = O.random_scalars(sf, no, 61 + curve)
+                zo = O.random_scalars(sf, 4, 62 + curve)
+                Co = hb.pcdl.commit(curve, po, no - 1)
+                ok_open = True
+                for hide in (False, True):
+                    kw = dict(w=zo[1], hide_q=O.random_scalars(sf, no - 1, 63), hide_wbar=zo[2]) if hide else {}
+                    Ch = hb.pcdl.commit(curve, po, no - 1, zo[1]) if hide else Co
+                    for t0 in (0, 1):                                        # tuning key 0 = 1: no fold table (ladder folds)
+                        _l.halo_set_tuning(0, t0)
+                        pd_, vd = hb.dist.pcdl_open(curve, po, Ch, no - 1, zo[0], None, **kw)
+                        p1_, v1 = hb.pcdl.open_without_eval(curve, po, Ch, no - 1, zo[0], None, **kw)
+                        _l.halo_set_tuning(0, 0)
+                        qd = hb.pcdl.Instance.new(curve, Ch, no - 1, zo[0], vd, pd_)
+                        q1 = hb.pcdl.Instance.new(curve, Ch, no - 1, zo[0], v1, p1_)
+                        fd, f1 = O.inst_fields(qd.w), O.inst_fields(q1.w)
+                        ok_open = ok_open and all((fd[x] == f1[x]).all() for x in ("z", "v", "c"))
+                        ok_open = ok_open and all((aff(curve, fd[x]) == aff(curve, f1[x])).all() for x in ("C", "U", "Ls", "Rs"))
+                        qd.check()
+                    if check_oracle and not hide:
+                        O.pp_set(curve, gso[:no], gso[no], gso[no + 1])
+                        fe_ = O.inst_fields(O.instance_open(curve, po, no - 1, zo[0]))
+                        ok_open = ok_open and (fd["c"] == fe_["c"]).all() and (aff(curve, fd["Ls"]) == aff(curve, fe_["Ls"])).all() \
+                            and (aff(curve, fd["U"]) == aff(curve, fe_["U"])).all()
+                res[f"open_{curve}_{lgo}"] = bool(ok_open)
             # ---- ONE PLONK proof over all ranks: inputs on rank 0 only; equal to the oracle's proof and the single-GPU one
             # (a satisfied circuit: 8-coset quotient; a random one: 16 cosets and the coefficient-form division)
             import plonk_fixture as F
