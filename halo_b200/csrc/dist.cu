@@ -20,6 +20,7 @@ namespace halo {
 template <int C> int msm_windows_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbatch, ptrdiff_t base_stride,
                                         void** d_winsum, int* c_out, int* nwin_out);
 template <int C> void msm_horner_host(const void* win, int c, int nwin, uint64_t out_xyz[12]);
+template <int C> int msm_host_chunked_windows(const uint64_t* h_bases, const uint64_t* h_scalars, size_t k, void** d_winsum, int* c_out, int* nwin_out);
 
 namespace {
 struct NcclApi {
@@ -154,8 +155,11 @@ __global__ void dist_pack_kernel(const XYZZ<C>* __restrict__ winsum, u32 c, u32 
 }
 
 // base_stride != 0: MSM j of the batch reads bases + j * base_stride (the IPA's L / R pair over the two halves)
+// h_bases != nullptr: this rank's slice comes from HOST buffers (one MSM) and is uploaded pipelined with the
+// accumulation by point range (msm_host_chunked_windows) -- d_bases / d_scalars are then the host pointers
 template <int C>
-int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, size_t nbatch, uint64_t* out_xyz, ptrdiff_t base_stride) {
+int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, size_t nbatch, uint64_t* out_xyz, ptrdiff_t base_stride,
+                    bool from_host) {
     DistState& D = ds();
     Runtime& R = rt();
     HALO_CHECK(D.on, HALO_ENOINIT, "halo_dist_init has not been called");
@@ -169,6 +173,9 @@ int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, 
         HALO_CUDA(cudaMemsetAsync(D.d_send, 0, 128, st));                      // nwin = 0: nothing to add
     } else {
         void* d_win = nullptr; int c = 0, nwin = 0;
+        if (from_host) {
+            if (int e = msm_host_chunked_windows<C>((const uint64_t*)d_bases, (const uint64_t*)d_scalars, k_local, &d_win, &c, &nwin)) return e;
+        } else
         if (int e = msm_windows_device<C>(d_bases, d_scalars, k_local, nbatch, base_stride, &d_win, &c, &nwin)) return e;
         HALO_CHECK(nwin <= DIST_SLOTS, HALO_EINVAL, "dist msm: window count above the payload slots");
         const u32 words = (u32)(nbatch * nwin * 32);
@@ -205,8 +212,8 @@ int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, 
     }
     return HALO_OK;
 }
-template int dist_msm_device<0>(const void*, const void*, size_t, size_t, uint64_t*, ptrdiff_t);
-template int dist_msm_device<1>(const void*, const void*, size_t, size_t, uint64_t*, ptrdiff_t);
+template int dist_msm_device<0>(const void*, const void*, size_t, size_t, uint64_t*, ptrdiff_t, bool);
+template int dist_msm_device<1>(const void*, const void*, size_t, size_t, uint64_t*, ptrdiff_t, bool);
 
 }  // namespace halo
 
@@ -279,7 +286,7 @@ int halo_dist_msm_dev(int curve, const void* d_bases_xy, size_t base_off, const 
         bases = (const char*)R.pp[curve].d_gs;
     }
     bases += base_off * 64;
-    return curve == 0 ? dist_msm_device<0>(bases, d_scalars, k_local, 1, out_xyz) : dist_msm_device<1>(bases, d_scalars, k_local, 1, out_xyz);
+    return curve == 0 ? dist_msm_device<0>(bases, d_scalars, k_local, 1, out_xyz, 0, false) : dist_msm_device<1>(bases, d_scalars, k_local, 1, out_xyz, 0, false);
 HALO_API_END
 }
 
@@ -287,6 +294,10 @@ int halo_dist_msm(int curve, const uint64_t* bases_xy, size_t base_off, const ui
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "bad curve");
     HALO_CHECK(out_xyz && (scalars || k_local == 0), HALO_EINVAL, "dist msm: null pointer");
+    // a large slice over caller-supplied bases: upload pipelined with the accumulation by point range, as halo_msm does
+    if (bases_xy && k_local >= ((size_t)1 << 19) && k_local < ((size_t)1 << 27) && rt().tune[9] != 1 && rt().tune[8] == 0)
+        return curve == 0 ? dist_msm_device<0>(bases_xy + 8 * base_off, scalars, k_local, 1, out_xyz, 0, true)
+                          : dist_msm_device<1>(bases_xy + 8 * base_off, scalars, k_local, 1, out_xyz, 0, true);
     void *d_s = nullptr, *d_b = nullptr;
     if (int e = msm_upload_inputs(bases_xy, base_off, scalars, k_local, &d_s, &d_b)) { msm_upload_finish(); return e; }
     if (d_b) base_off = 0;
@@ -318,7 +329,7 @@ int halo_dist_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, 
         bases = (const char*)R.pp[curve].d_gs;
     }
     bases += base_off * 64;
-    return curve == 0 ? dist_msm_device<0>(bases, d_scalars, k_local, b, out_xyz) : dist_msm_device<1>(bases, d_scalars, k_local, b, out_xyz);
+    return curve == 0 ? dist_msm_device<0>(bases, d_scalars, k_local, b, out_xyz, 0, false) : dist_msm_device<1>(bases, d_scalars, k_local, b, out_xyz, 0, false);
 HALO_API_END
 }
 

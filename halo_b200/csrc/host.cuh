@@ -66,6 +66,6 @@ int dist_allgather_host(const void* h_send, void* h_recv_all, size_t bytes);
 int dist_bcast_dev(void* d_buf, size_t bytes, int root);
 int dist_bcast_host(void* h_buf, size_t bytes, int root);
 template <int C> int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, size_t nbatch, uint64_t* out_xyz,
-                                     ptrdiff_t base_stride = 0);
+                                     ptrdiff_t base_stride = 0, bool from_host = false);
 
 }  // namespace halo

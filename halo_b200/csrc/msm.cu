@@ -1007,8 +1007,11 @@ static int msm_small(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR>*
 // Pinned or registered buffers: every copy asynchronous.  Pageable buffers (a Rust Vec): staged through pinned chunks
 // by a helper thread (upload_staged) while this thread enqueues the kernels.  Four ranges in both cases.
 // ---------------------------------------------------------------------------------------------------------
+// The device half: leaves the window sums of the whole MSM in device memory (*d_winsum; *c_out / *nwin_out say how to
+// combine them) with everything queued on the runtime stream -- the multi-GPU exchange (dist.cu) all-gathers them from
+// there; msm_host_chunked below copies them back and combines them.
 template <int C>
-int msm_host_chunked(const uint64_t* h_bases, const uint64_t* h_scalars, size_t k, uint64_t* out_xyz) {
+int msm_host_chunked_windows(const uint64_t* h_bases, const uint64_t* h_scalars, size_t k, void** d_winsum, int* c_out, int* nwin_out) {
     Runtime& R = rt();
     cudaStream_t st = R.stream;
     const bool pageable = host_ptr_is_pageable(h_bases) || host_ptr_is_pageable(h_scalars);
@@ -1082,10 +1085,23 @@ int msm_host_chunked(const uint64_t* h_bases, const uint64_t* h_scalars, size_t 
     if (rc) up_rc.store(rc);                                              // lets the upload thread's waiters stop
     up.join();
     if (rc) { cudaStreamSynchronize(R.copy_stream); cudaStreamSynchronize(st); return rc; }
+    *d_winsum = d_win; *c_out = P0.c; *nwin_out = P0.nwin;
+    return HALO_OK;
+}
+template int msm_host_chunked_windows<0>(const uint64_t*, const uint64_t*, size_t, void**, int*, int*);
+template int msm_host_chunked_windows<1>(const uint64_t*, const uint64_t*, size_t, void**, int*, int*);
+
+template <int C>
+int msm_host_chunked(const uint64_t* h_bases, const uint64_t* h_scalars, size_t k, uint64_t* out_xyz) {
+    Runtime& R = rt();
+    void* d_win = nullptr;
+    MsmPlan P0;
+    if (int e = msm_host_chunked_windows<C>(h_bases, h_scalars, k, &d_win, &P0.c, &P0.nwin)) return e;
+    const size_t nwt = (size_t)P0.nwin;
     void* h = nullptr;
-    if (int e = pinned_get(P0.nwt * sizeof(XYZZ<C>), &h)) return e;
-    HALO_CUDA(cudaMemcpyAsync(h, d_win, P0.nwt * sizeof(XYZZ<C>), cudaMemcpyDeviceToHost, st));
-    HALO_CUDA(cudaStreamSynchronize(st));
+    if (int e = pinned_get(nwt * sizeof(XYZZ<C>), &h)) return e;
+    HALO_CUDA(cudaMemcpyAsync(h, d_win, nwt * sizeof(XYZZ<C>), cudaMemcpyDeviceToHost, R.stream));
+    HALO_CUDA(cudaStreamSynchronize(R.stream));
     msm_combine_host<C>((const XYZZ<C>*)h, P0, out_xyz);
     return HALO_OK;
 }

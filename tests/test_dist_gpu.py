@@ -45,6 +45,13 @@ def _worker(rank, world, idfile, q):
             lo, hi = (0, cut) if rank == 0 else (cut, k) if rank == world - 1 else (k, k)
             got = hb.dist.msm(curve, sc[lo:hi], pts[lo:hi])
             res[f"msm_ragged_{curve}"] = bool((aff(curve, got) == aff(curve, exp)).all())
+            # ---- a slice large enough for the point-range-pipelined host upload (>= 2^19 points per rank)
+            if curve == 0:
+                kb = world * (1 << 19) + 3
+                ptsb = O.points_arith(curve, kb, k0=0x99)
+                scb = O.random_scalars(sf, kb, 77)
+                got = hb.dist.msm_global(curve, scb, ptsb)
+                res["msm_big_host_slices"] = bool((aff(curve, got) == aff(curve, O.msm(curve, ptsb, scb))).all())
             # ---- resident generators, sliced by the library
             n = 1 << 12
             gs, S, H = O.pp_generate(curve, n)
