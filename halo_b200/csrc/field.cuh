@@ -18,6 +18,8 @@
 // a 64-bit-limb implementation of the same functions.
 #pragma once
 #include <stdint.h>
+#include <string.h>
+#include <stdio.h>
 
 #if defined(__CUDACC__)
 #define HD __host__ __device__ __forceinline__
@@ -311,8 +313,10 @@ template <int FID> HD void modulus64(u64 p[4]) {
     p[1] = ((u64)FieldConst<FID>::P3 << 32) | FieldConst<FID>::P2;
     p[2] = 0; p[3] = 0x4000000000000000ULL;
 }
-HD void load(u64 w[4], const u32* l) { for (int i = 0; i < 4; ++i) w[i] = (u64)l[2 * i] | ((u64)l[2 * i + 1] << 32); }
-HD void store(u32* l, const u64 w[4]) { for (int i = 0; i < 4; ++i) { l[2 * i] = (u32)w[i]; l[2 * i + 1] = (u32)(w[i] >> 32); } }
+// 64-bit accesses on both sides (little-endian host): a value stored as eight 32-bit words and reloaded as four 64-bit
+// ones defeats store-to-load forwarding, which cost more than the multiplication itself in the serial sponge chain
+HD void load(u64 w[4], const u32* l) { memcpy(w, l, 32); }
+HD void store(u32* l, const u64 w[4]) { memcpy(l, w, 32); }
 HD bool geq(const u64 a[4], const u64 b[4]) { for (int i = 3; i >= 0; --i) if (a[i] != b[i]) return a[i] > b[i]; return true; }
 HD u64 add(u64 o[4], const u64 a[4], const u64 b[4]) { u128 c = 0; for (int i = 0; i < 4; ++i) { c += (u128)a[i] + b[i]; o[i] = (u64)c; c >>= 64; } return (u64)c; }
 HD u64 sub(u64 o[4], const u64 a[4], const u64 b[4]) { u64 br = 0; for (int i = 0; i < 4; ++i) { u128 d = (u128)a[i] - b[i] - br; o[i] = (u64)d; br = (u64)(d >> 64) & 1; } return br; }
@@ -371,9 +375,93 @@ template <int FID> HD void redc_wide(u64 out[4], const u64 w[8]) {
 }
 }  // namespace hostimpl
 
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__CUDA_ARCH__) && !defined(HALO_NO_HOST_ADX)
+#define HALO_HOST_ADX 1
+namespace hostimpl {
+// BMI2 + ADX path of the host multiplication (the serial Fiat-Shamir sponge is ~5 k dependent multiplications per
+// challenge and bounds AS_DL over many instances): the interleaved (CIOS) Montgomery product, one row per asm block.
+// A row adds x * y_i to the 5-word accumulator and divides by 2^64 after adding m p (m = -t0 / p mod 2^64); mulx leaves
+// the flags alone, adcx / adox run the low-word and high-word carry chains side by side.  Every output is early-clobber:
+// the accumulator words are written before the last x_j is read, and an input with the same VALUE (x_j = 0 and a zero
+// accumulator word, x_0 = y_i in a squaring) would otherwise be given the same register.  K = {p0, p1, p3, -p^-1 mod
+// 2^64} (p2 = 0).  Bounds: t < 2p before a row, t + x y_i + m p < 2^64 * 2p < 2^320, so five words never overflow.
+inline bool host_has_adx() {
+    static const bool ok = __builtin_cpu_supports("bmi2") && __builtin_cpu_supports("adx");
+    return ok;
+}
+#define HALO_MONT_ROW(T0, T1, T2, T3, T4, YI)                                                                         \
+    {                                                                                                                 \
+        unsigned long long d_ = (YI), lo_, hi_, z_;                                                                   \
+        asm("xorl %k[z], %k[z]\n\t"                                                                                   \
+            "mulx %[x0], %[lo], %[hi]\n\t adox %[lo], %[t0]\n\t adcx %[hi], %[t1]\n\t"                                \
+            "mulx %[x1], %[lo], %[hi]\n\t adox %[lo], %[t1]\n\t adcx %[hi], %[t2]\n\t"                                \
+            "mulx %[x2], %[lo], %[hi]\n\t adox %[lo], %[t2]\n\t adcx %[hi], %[t3]\n\t"                                \
+            "mulx %[x3], %[lo], %[hi]\n\t adox %[lo], %[t3]\n\t adcx %[hi], %[t4]\n\t"                                \
+            "adox %[z], %[t4]\n\t"                                                                                    \
+            "mov %[t0], %%rdx\n\t imulq 24(%[k]), %%rdx\n\t"                                                          \
+            "xorl %k[z], %k[z]\n\t"                                                                                   \
+            "mulx 0(%[k]), %[lo], %[hi]\n\t adox %[lo], %[t0]\n\t adcx %[hi], %[t1]\n\t"                              \
+            "mulx 8(%[k]), %[lo], %[hi]\n\t adox %[lo], %[t1]\n\t adcx %[hi], %[t2]\n\t"                              \
+            "adox %[z], %[t2]\n\t"                                                                                    \
+            "mulx 16(%[k]), %[lo], %[hi]\n\t adox %[lo], %[t3]\n\t adcx %[z], %[t3]\n\t"                              \
+            "adox %[hi], %[t4]\n\t adcx %[z], %[t4]\n\t"                                                              \
+            : [t0] "+&r"(T0), [t1] "+&r"(T1), [t2] "+&r"(T2), [t3] "+&r"(T3), [t4] "+&r"(T4), "+&d"(d_), [lo] "=&r"(lo_), \
+              [hi] "=&r"(hi_), [z] "=&r"(z_)                                                                          \
+            : [x0] "rm"(x0), [x1] "rm"(x1), [x2] "rm"(x2), [x3] "rm"(x3), [k] "r"(K)                                   \
+            : "cc");                                                                                                  \
+    }
+template <int FID> inline void mont_mul_adx(u64 r[4], const u64 x[4], const u64 y[4]) {
+    typedef unsigned long long ull;
+    static const ull K[4] = {((ull)FieldConst<FID>::P1 << 32) | 1u, ((ull)FieldConst<FID>::P3 << 32) | FieldConst<FID>::P2,
+                             0x4000000000000000ULL, (((ull)FieldConst<FID>::P1 - 1) << 32) | 0xffffffffULL};
+    const ull x0 = x[0], x1 = x[1], x2 = x[2], x3 = x[3];
+    ull t0 = 0, t1 = 0, t2 = 0, t3 = 0, t4 = 0;
+    HALO_MONT_ROW(t0, t1, t2, t3, t4, y[0]); t0 = 0;      // the low word is zero after a row: it becomes the next top word
+    HALO_MONT_ROW(t1, t2, t3, t4, t0, y[1]); t1 = 0;
+    HALO_MONT_ROW(t2, t3, t4, t0, t1, y[2]); t2 = 0;
+    HALO_MONT_ROW(t3, t4, t0, t1, t2, y[3]);
+    // (t4, t0, t1, t2) < 2p: one conditional subtraction
+    ull s0, s1, s2, s3;
+    unsigned char bw;
+    bw = __builtin_ia32_sbb_u64(0, t4, K[0], &s0);
+    bw = __builtin_ia32_sbb_u64(bw, t0, K[1], &s1);
+    bw = __builtin_ia32_sbb_u64(bw, t1, 0, &s2);
+    bw = __builtin_ia32_sbb_u64(bw, t2, K[2], &s3);
+    r[0] = bw ? t4 : s0; r[1] = bw ? t0 : s1; r[2] = bw ? t1 : s2; r[3] = bw ? t2 : s3;
+}
+#undef HALO_MONT_ROW
+}  // namespace hostimpl
+#endif
+
 template <int FID> HD Fe<FID> fe_mul(const Fe<FID>& a, const Fe<FID>& b) {
     using namespace hostimpl;
     u64 x[4], y[4], p[4]; load(x, a.l); load(y, b.l); modulus64<FID>(p);
+#if defined(HALO_HOST_ADX)
+    // the five-word bound of the ADX rows needs both operands below 2^254 (< p); callers that reduce a raw 256-bit integer
+    // by multiplying it with R^2 (fe_from_canonical on a value of the other field) take the generic path with its sixth word
+    if (((x[3] | y[3]) >> 62) == 0 && host_has_adx()) {
+        u64 r[4];
+        mont_mul_adx<FID>(r, x, y);
+#ifdef HALO_ADX_SELFCHECK
+        {
+            u64 t[6] = {0, 0, 0, 0, 0, 0};
+            for (int i = 0; i < 4; ++i) {
+                u128 c = 0;
+                for (int j = 0; j < 4; ++j) { c += (u128)x[j] * y[i] + t[j]; t[j] = (u64)c; c >>= 64; }
+                c += t[4]; t[4] = (u64)c; t[5] = (u64)(c >> 64);
+                redc_step<FID>(t);
+            }
+            if (t[4] || geq(t, p)) sub(t, t, p);
+            if (t[0] != r[0] || t[1] != r[1] || t[2] != r[2] || t[3] != r[3])
+                fprintf(stderr, "ADX MISMATCH F%d x=%016llx %016llx %016llx %016llx y=%016llx %016llx %016llx %016llx adx=%016llx.. gen=%016llx..\n", FID,
+                        (unsigned long long)x[3], (unsigned long long)x[2], (unsigned long long)x[1], (unsigned long long)x[0],
+                        (unsigned long long)y[3], (unsigned long long)y[2], (unsigned long long)y[1], (unsigned long long)y[0],
+                        (unsigned long long)r[3], (unsigned long long)t[3]);
+        }
+#endif
+        Fe<FID> o; store(o.l, r); return o;
+    }
+#endif
     u64 t[6] = {0, 0, 0, 0, 0, 0};
     for (int i = 0; i < 4; ++i) {
         u128 c = 0;

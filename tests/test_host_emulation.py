@@ -22,9 +22,11 @@ def _build(tag, flags):
     return ctypes.CDLL(so)
 
 
-@pytest.fixture(scope="module", params=["ptx", "plain"])
+# "plain" takes the BMI2 + ADX multiplication of the host path when the CPU has it, "plain_noadx" the generic one
+@pytest.fixture(scope="module", params=["ptx", "plain", "plain_noadx"])
 def emu(request):
-    return _build(request.param, ["-DEMU_PLAIN_HOST"] if request.param == "plain" else [])
+    flags = {"ptx": [], "plain": ["-DEMU_PLAIN_HOST"], "plain_noadx": ["-DEMU_PLAIN_HOST", "-DHALO_NO_HOST_ADX"]}
+    return _build(request.param, flags[request.param])
 
 
 def _p(a):
