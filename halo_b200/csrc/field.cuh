@@ -430,6 +430,64 @@ template <int FID> inline void mont_mul_adx(u64 r[4], const u64 x[4], const u64 
     r[0] = bw ? t4 : s0; r[1] = bw ? t0 : s1; r[2] = bw ? t1 : s2; r[3] = bw ? t2 : s3;
 }
 #undef HALO_MONT_ROW
+// The three-term dot product of the sponge's MDS rows with ONE reduction: per word i of the second operands three
+// multiply-accumulate rows into a six-word accumulator, then one reduction row.  The result (T + M p) / 2^256 with
+// T < 3 p^2 is below 2p, as in redc_wide.
+#define HALO_MAC_ROW(T0, T1, T2, T3, T4, T5, X, YI)                                                                   \
+    {                                                                                                                 \
+        unsigned long long d_ = (YI), lo_, hi_, z_;                                                                   \
+        asm("xorl %k[z], %k[z]\n\t"                                                                                   \
+            "mulx %[x0], %[lo], %[hi]\n\t adox %[lo], %[t0]\n\t adcx %[hi], %[t1]\n\t"                                \
+            "mulx %[x1], %[lo], %[hi]\n\t adox %[lo], %[t1]\n\t adcx %[hi], %[t2]\n\t"                                \
+            "mulx %[x2], %[lo], %[hi]\n\t adox %[lo], %[t2]\n\t adcx %[hi], %[t3]\n\t"                                \
+            "mulx %[x3], %[lo], %[hi]\n\t adox %[lo], %[t3]\n\t adcx %[hi], %[t4]\n\t"                                \
+            "adox %[z], %[t4]\n\t adcx %[z], %[t5]\n\t adox %[z], %[t5]\n\t"                                          \
+            : [t0] "+&r"(T0), [t1] "+&r"(T1), [t2] "+&r"(T2), [t3] "+&r"(T3), [t4] "+&r"(T4), [t5] "+&r"(T5),         \
+              [lo] "=&r"(lo_), [hi] "=&r"(hi_), [z] "=&r"(z_)                                                         \
+            : "d"(d_), [x0] "rm"(X[0]), [x1] "rm"(X[1]), [x2] "rm"(X[2]), [x3] "rm"(X[3])                             \
+            : "cc");                                                                                                  \
+    }
+#define HALO_REDC_ROW(T0, T1, T2, T3, T4, T5)                                                                         \
+    {                                                                                                                 \
+        unsigned long long d_, lo_, hi_, z_;                                                                          \
+        asm("mov %[t0], %%rdx\n\t imulq 24(%[k]), %%rdx\n\t"                                                          \
+            "xorl %k[z], %k[z]\n\t"                                                                                   \
+            "mulx 0(%[k]), %[lo], %[hi]\n\t adox %[lo], %[t0]\n\t adcx %[hi], %[t1]\n\t"                              \
+            "mulx 8(%[k]), %[lo], %[hi]\n\t adox %[lo], %[t1]\n\t adcx %[hi], %[t2]\n\t"                              \
+            "adox %[z], %[t2]\n\t"                                                                                    \
+            "mulx 16(%[k]), %[lo], %[hi]\n\t adox %[lo], %[t3]\n\t adcx %[z], %[t3]\n\t"                              \
+            "adox %[hi], %[t4]\n\t adcx %[z], %[t4]\n\t"                                                              \
+            "adox %[z], %[t5]\n\t adcx %[z], %[t5]\n\t"                                                               \
+            : [t0] "+&r"(T0), [t1] "+&r"(T1), [t2] "+&r"(T2), [t3] "+&r"(T3), [t4] "+&r"(T4), [t5] "+&r"(T5),         \
+              "=&d"(d_), [lo] "=&r"(lo_), [hi] "=&r"(hi_), [z] "=&r"(z_)                                              \
+            : [k] "r"(K)                                                                                              \
+            : "cc");                                                                                                  \
+    }
+template <int FID> inline void mont_dot3_adx(u64 r[4], const u64 a0[4], const u64 b0[4], const u64 a1[4], const u64 b1[4],
+                                             const u64 a2[4], const u64 b2[4]) {
+    typedef unsigned long long ull;
+    static const ull K[4] = {((ull)FieldConst<FID>::P1 << 32) | 1u, ((ull)FieldConst<FID>::P3 << 32) | FieldConst<FID>::P2,
+                             0x4000000000000000ULL, (((ull)FieldConst<FID>::P1 - 1) << 32) | 0xffffffffULL};
+    ull t0 = 0, t1 = 0, t2 = 0, t3 = 0, t4 = 0, t5 = 0;
+#define HALO_DOT_STEP(T0, T1, T2, T3, T4, T5, I)                                                                      \
+    HALO_MAC_ROW(T0, T1, T2, T3, T4, T5, a0, b0[I]) HALO_MAC_ROW(T0, T1, T2, T3, T4, T5, a1, b1[I])                   \
+    HALO_MAC_ROW(T0, T1, T2, T3, T4, T5, a2, b2[I]) HALO_REDC_ROW(T0, T1, T2, T3, T4, T5)
+    HALO_DOT_STEP(t0, t1, t2, t3, t4, t5, 0) t0 = 0;      // the low word is zero after the reduction row: the next top word
+    HALO_DOT_STEP(t1, t2, t3, t4, t5, t0, 1) t1 = 0;
+    HALO_DOT_STEP(t2, t3, t4, t5, t0, t1, 2) t2 = 0;
+    HALO_DOT_STEP(t3, t4, t5, t0, t1, t2, 3)
+#undef HALO_DOT_STEP
+    // (t4, t5, t0, t1) with top words t2 = 0: below 2p, one conditional subtraction
+    ull s0, s1, s2, s3;
+    unsigned char bw;
+    bw = __builtin_ia32_sbb_u64(0, t4, K[0], &s0);
+    bw = __builtin_ia32_sbb_u64(bw, t5, K[1], &s1);
+    bw = __builtin_ia32_sbb_u64(bw, t0, 0, &s2);
+    bw = __builtin_ia32_sbb_u64(bw, t1, K[2], &s3);
+    r[0] = bw ? t4 : s0; r[1] = bw ? t5 : s1; r[2] = bw ? t0 : s2; r[3] = bw ? t1 : s3;
+}
+#undef HALO_MAC_ROW
+#undef HALO_REDC_ROW
 }  // namespace hostimpl
 #endif
 
@@ -476,6 +534,17 @@ template <int FID> HD Fe<FID> fe_mul(const Fe<FID>& a, const Fe<FID>& b) {
 template <int FID> HD Fe<FID> fe_dot3(const Fe<FID>& a0, const Fe<FID>& b0, const Fe<FID>& a1, const Fe<FID>& b1,
                                       const Fe<FID>& a2, const Fe<FID>& b2) {
     using namespace hostimpl;
+#if defined(HALO_HOST_ADX)
+    {
+        u64 xa[4], ya[4], xb[4], yb[4], xc[4], yc[4];
+        load(xa, a0.l); load(ya, b0.l); load(xb, a1.l); load(yb, b1.l); load(xc, a2.l); load(yc, b2.l);
+        if (((xa[3] | ya[3] | xb[3] | yb[3] | xc[3] | yc[3]) >> 62) == 0 && host_has_adx()) {      // all below 2^254 < p
+            u64 r[4];
+            mont_dot3_adx<FID>(r, xa, ya, xb, yb, xc, yc);
+            Fe<FID> o; store(o.l, r); return o;
+        }
+    }
+#endif
     u64 x[4], y[4], w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     load(x, a0.l); load(y, b0.l); mac_wide(w, x, y);
     load(x, a1.l); load(y, b1.l); mac_wide(w, x, y);
