@@ -605,8 +605,13 @@ template <int FID> HD Fe<FID> fe_pow(const Fe<FID>& a, const u32* e, int nbits =
     }
     return acc;
 }
-// Fermat inverse; 0 -> 0
+template <int FID> HD Fe<FID> fe_inv_safegcd(const Fe<FID>& a);
+// Inverse; 0 -> 0.  Device: Fermat ladder.  Plain host path (transcript, verifier arithmetic: an inversion per challenge
+// and per point brought to affine form): the divstep inversion further down, a third of the ladder's time on a host core.
 template <int FID> HD Fe<FID> fe_inv(const Fe<FID>& a) {
+#if !defined(HALO_PTX_PATH)
+    return fe_inv_safegcd<FID>(a);
+#endif
     u32 e[8];
     for (int i = 0; i < 8; ++i) e[i] = modulus_limb<FID>(i);
     e[0] = 0xffffffffu; e[1] -= 1;            // p - 2  (p0 = 1 -> borrow from limb 1)
