@@ -102,6 +102,8 @@ bool host_ptr_is_pageable(const void* p) {
     return a.type == cudaMemoryTypeUnregistered;
 }
 
+bool dist_on();
+int dist_world();
 int upload_staged(void* d_dst, const void* h_src, size_t bytes, cudaStream_t order_stream) {
     Runtime& R = rt();
     if (!order_stream) order_stream = R.stream;
@@ -109,10 +111,14 @@ int upload_staged(void* d_dst, const void* h_src, size_t bytes, cudaStream_t ord
         HALO_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, order_stream));
         return HALO_OK;
     }
-    constexpr int T = Runtime::UP_THREADS, SL = Runtime::UP_SLOTS;
+    constexpr int TMAX = Runtime::UP_THREADS, SL = Runtime::UP_SLOTS;
     constexpr size_t CH = Runtime::UP_CHUNK;
+    // up to 16 staging threads (2^20-gate columns: 36 -> 30 ms with 16 instead of 8); the ranks of one box share the
+    // host's cores, so a process that has joined a communicator takes its share of them
+    const int hw = (int)std::max(2u, std::thread::hardware_concurrency());
+    const int T = std::max(2, std::min(TMAX, dist_on() ? hw / std::max(1, dist_world()) : hw));
     if (!R.up_stream[0]) {
-        for (int t = 0; t < T; ++t) {
+        for (int t = 0; t < TMAX; ++t) {
             HALO_CUDA(cudaStreamCreateWithFlags(&R.up_stream[t], cudaStreamNonBlocking));
             for (int k = 0; k < SL; ++k) {
                 HALO_CUDA(cudaMallocHost(&R.up_buf[t][k], CH));
@@ -127,8 +133,8 @@ int upload_staged(void* d_dst, const void* h_src, size_t bytes, cudaStream_t ord
     int dev = 0;
     HALO_CUDA(cudaGetDevice(&dev));
     const size_t nchunks = (bytes + CH - 1) / CH;
-    int status[T];
-    for (int t = 0; t < T; ++t) status[t] = 0;
+    int status[TMAX];
+    for (int t = 0; t < TMAX; ++t) status[t] = 0;
     Workers wk;
     wk.spawn_indexed(0, (unsigned)T, [&](unsigned t) {
         {

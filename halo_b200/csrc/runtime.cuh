@@ -53,7 +53,7 @@ struct Runtime {
     void* pinned = nullptr;         // pinned host staging
     size_t pinned_cap = 0;
     // staged upload of large pageable buffers: UP_THREADS workers, two pinned chunks and one stream each
-    static constexpr int UP_THREADS = 8, UP_SLOTS = 2;
+    static constexpr int UP_THREADS = 16, UP_SLOTS = 2;
     static constexpr size_t UP_CHUNK = (size_t)2 << 20;
     void* up_buf[UP_THREADS][UP_SLOTS] = {};
     cudaEvent_t up_ev[UP_THREADS][UP_SLOTS] = {};
