@@ -528,6 +528,7 @@ int halo_shutdown(void) { HALO_API_BEGIN
         if (R.pp[c].d_gs) cudaFree(R.pp[c].d_gs);
         if (R.pp[c].d_fold_tab) cudaFree(R.pp[c].d_fold_tab);
         if (R.pp[c].d_fold_tab_loc) cudaFree(R.pp[c].d_fold_tab_loc);
+        if (R.pp[c].d_fixed_tab) cudaFree(R.pp[c].d_fixed_tab);
         R.pp[c] = ResidentParams();
     }
     if (R.pinned) cudaFreeHost(R.pinned);
@@ -680,6 +681,7 @@ int halo_pp_reset(int curve) { HALO_API_BEGIN
     if (R.pp[curve].d_gs) cudaFree(R.pp[curve].d_gs);
     if (R.pp[curve].d_fold_tab) cudaFree(R.pp[curve].d_fold_tab);
     if (R.pp[curve].d_fold_tab_loc) cudaFree(R.pp[curve].d_fold_tab_loc);
+    if (R.pp[curve].d_fixed_tab) cudaFree(R.pp[curve].d_fixed_tab);
     R.pp[curve] = ResidentParams();
     return HALO_OK;
 HALO_API_END

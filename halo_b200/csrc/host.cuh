@@ -54,6 +54,7 @@ template <int C> int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_
                                const uint64_t* v_w, const uint64_t* w_w, const uint64_t* hide_q, const uint64_t* hide_wbar,
                                uint64_t* out_proof, uint64_t* out_v, bool coeffs_resident, bool shard = false);
 template <int C> int pcdl_check(const uint64_t* instance);
+template <int C> int ensure_fixed_table(const void** tab, int* c, int* ncols, size_t* row_stride);   // commit-path table of pp.Gs (ipa.cu)
 template <int C> int pcdl_open_prepare(size_t n);   // builds, on the main runtime, what an opening of size n would build lazily
 template <int C> int acc_prover(const uint64_t* insts, size_t m, uint64_t* out_acc, bool shard_open = false);
 template <int C> int acc_verifier(const uint64_t* insts, size_t m, const uint64_t* acc, bool sharded = false);

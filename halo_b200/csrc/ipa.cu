@@ -718,6 +718,62 @@ static int ensure_fold_table_local(size_t n, int world, int rank, const Affine<C
     return HALO_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Fixed-base table of the resident generators for the COMMIT path (msm.cu, msm_fixed): row w holds 2^(c w) * Gs[i],
+// i < pp.n, affine.  With it the digit columns of a commitment all land in ONE window of 2^(c-1) buckets (the bucket
+// reduction and the Horner combine all but disappear) and c can be 18-20 instead of 15-16: 13 additions per point
+// instead of 16 at n = 2^20.  Built once per parameter set on first use (13 x 64 MB at 2^20, ~40 ms), freed with it.
+// ---------------------------------------------------------------------------------------------------------
+template <int C>
+__global__ void __launch_bounds__(128) fixed_table_step_kernel(const Affine<C>* __restrict__ gs, XYZZ<C>* __restrict__ state, size_t n,
+                                                               int first, int doublings) {
+    size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    XYZZ<C> P;
+    if (first) { Affine<C> a; a.x = g_ld(&gs[j].x); a.y = g_ld(&gs[j].y); P = xyzz_from_affine<C>(a); }
+    else { P.X = g_ld(&state[j].X); P.Y = g_ld(&state[j].Y); P.ZZ = g_ld(&state[j].ZZ); P.ZZZ = g_ld(&state[j].ZZZ); }
+    for (int k = 0; k < doublings; ++k) P = xyzz_dbl<C>(P);
+    g_st(&state[j].X, P.X); g_st(&state[j].Y, P.Y); g_st(&state[j].ZZ, P.ZZ); g_st(&state[j].ZZZ, P.ZZZ);
+}
+template <int C>
+int ensure_fixed_table(const void** tab_out, int* c_out, int* ncols_out, size_t* row_stride_out) {
+    Runtime& R = rt();
+    cudaStream_t st = R.stream;
+    ResidentParams& P = R.pp[C];
+    *tab_out = nullptr;
+    const size_t n = P.n;
+    if (n < ((size_t)1 << 18) || n > ((size_t)1 << 24)) return HALO_OK;
+    if (P.d_fixed_tab && P.fixed_tab_n == n) {
+        *tab_out = P.d_fixed_tab; *c_out = P.fixed_tab_c; *ncols_out = 255 / P.fixed_tab_c + 1; *row_stride_out = n;
+        return HALO_OK;
+    }
+    if (R.is_lane) return HALO_OK;
+    HALO_CUDA(cudaStreamSynchronize(st));
+    if (P.d_fixed_tab) { cudaFree(P.d_fixed_tab); P.d_fixed_tab = nullptr; P.fixed_tab_n = 0; }
+    const int c = std::min(20, std::max(18, (int)ilog2(n)));
+    const int ncols = 255 / c + 1;
+    void* tab = nullptr;
+    if (cudaMalloc(&tab, (size_t)ncols * n * sizeof(Affine<C>)) != cudaSuccess) { cudaGetLastError(); return HALO_OK; }   // no room: ordinary MSM
+    XYZZ<C>* state;
+    if (int e = ws_get(WS_FOLD_STATE, n * sizeof(XYZZ<C>), (void**)&state)) { cudaFree(tab); return e; }
+    HALO_CUDA(cudaMemcpyAsync(tab, P.d_gs, n * sizeof(Affine<C>), cudaMemcpyDeviceToDevice, st));     // row 0 is Gs itself
+    for (int w = 1; w < ncols; ++w) {
+        fixed_table_step_kernel<C><<<(unsigned)((n + 127) / 128), 128, 0, st>>>((const Affine<C>*)P.d_gs, state, n, w == 1, c);
+        xyzz_batch_affine_kernel<C, 8><<<(unsigned)((n / 8 + 128) / 128), 128, 0, st>>>(state, n, (Affine<C>*)tab + (size_t)w * n);
+        R.launches += 2;
+    }
+    if (cudaGetLastError() != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
+        cudaFree(tab);
+        last_err() = "fixed-base table: kernel failed";
+        return HALO_ECUDA;
+    }
+    P.d_fixed_tab = tab; P.fixed_tab_n = n; P.fixed_tab_c = c;
+    *tab_out = tab; *c_out = c; *ncols_out = ncols; *row_stride_out = n;
+    return HALO_OK;
+}
+template int ensure_fixed_table<0>(const void**, int*, int*, size_t*);
+template int ensure_fixed_table<1>(const void**, int*, int*, size_t*);
+
 // explicit set-up step (halo_ipa_fold_table_build): build the table for openings of size n now instead of inside the
 // first opening
 template <int C>
@@ -973,6 +1029,10 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
             else if (int e = msm_device<C>(gs, tail_s, Tp, 2, lr, 0)) return e;     // syncs: wh may go out of scope
         } else {
             if (W > 1) { if (int e = dist_msm_device<C>(gs + m, cs, m, 2, lr, -(ptrdiff_t)m)) return e; }
+            else if (r == 0 && n == R.pp[C].n && !R.is_lane) {
+                // the generators are still pp.Gs: addressed in place, msm_device takes the commit-path table for the pair
+                if (int e = msm_device<C>((const Affine<C>*)R.pp[C].d_gs + m, cs, m, 2, lr, -(ptrdiff_t)m)) return e;
+            }
             else if (int e = msm_device<C>(gs + m, cs, m, 2, lr, -(ptrdiff_t)m)) return e;
         }
         double t2 = trace ? now() : 0;

@@ -31,6 +31,9 @@
 
 namespace halo {
 
+// ipa.cu: the commit-path table of the resident generators (rows 2^(c w) * Gs[i]); *tab == nullptr when there is none
+template <int C> int ensure_fixed_table(const void** tab, int* c, int* ncols, size_t* row_stride);
+
 // ---------------------------------------------------------------------------------------------------------
 // helpers
 // ---------------------------------------------------------------------------------------------------------
@@ -79,16 +82,17 @@ __device__ __forceinline__ int window_digit(const u32 (&s)[8], int w, int c, int
 // ---------------------------------------------------------------------------------------------------------
 template <int SF>
 __global__ void __launch_bounds__(256) msm_count(const Fe<SF>* __restrict__ scalars, size_t k, size_t total, int c,
-                                                 int nwin, u32* __restrict__ counts) {
+                                                 int nwin, int fixed, u32* __restrict__ counts) {
+    // fixed != 0 (fixed-base table path): the nwin digit columns of an MSM share ONE bucket window
     const u32 B = 1u << (c - 1);
     for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
         const size_t j = t / k;                                   // which MSM of the batch
         Fe<SF> s = fe_to_canonical<SF>(load_fe(scalars + t));
-        u32* cw = counts + j * (size_t)nwin * B;
+        u32* cw = counts + j * (size_t)(fixed ? 1 : nwin) * B;
         int carry = 0;
         for (int w = 0; w < nwin; ++w) {
             int d = window_digit(s.l, w, c, carry);
-            if (d != 0) atomicAdd(&cw[(size_t)w * B + (u32)(abs(d) - 1)], 1u);
+            if (d != 0) atomicAdd(&cw[(size_t)(fixed ? 0 : w) * B + (u32)(abs(d) - 1)], 1u);
         }
     }
 }
@@ -151,19 +155,21 @@ __global__ void __launch_bounds__(256) scan_apply(const u32* __restrict__ in, si
 // ---------------------------------------------------------------------------------------------------------
 template <int SF>
 __global__ void __launch_bounds__(256) msm_scatter(const Fe<SF>* __restrict__ scalars, size_t k, size_t total, int c,
-                                                   int nwin, u32* __restrict__ cursor, u32* __restrict__ idx) {
+                                                   int nwin, int fixed, u32 row_stride, u32* __restrict__ cursor, u32* __restrict__ idx) {
+    // fixed != 0: one bucket window per MSM; the entry of digit column w is the table index w * row_stride + i
+    // (row w of the table holds 2^(c w) * G_i)
     const u32 B = 1u << (c - 1);
     for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
         const size_t j = t / k;
         const u32 i = (u32)(t - j * k);
         Fe<SF> s = fe_to_canonical<SF>(load_fe(scalars + t));
-        u32* cw = cursor + j * (size_t)nwin * B;
+        u32* cw = cursor + j * (size_t)(fixed ? 1 : nwin) * B;
         int carry = 0;
         for (int w = 0; w < nwin; ++w) {
             int d = window_digit(s.l, w, c, carry);
             if (d != 0) {
-                u32 pos = atomicAdd(&cw[(size_t)w * B + (u32)(abs(d) - 1)], 1u);
-                idx[pos] = i | (d < 0 ? 0x80000000u : 0u);
+                u32 pos = atomicAdd(&cw[(size_t)(fixed ? 0 : w) * B + (u32)(abs(d) - 1)], 1u);
+                idx[pos] = (fixed ? (u32)w * row_stride + i : i) | (d < 0 ? 0x80000000u : 0u);
             }
         }
     }
@@ -660,6 +666,10 @@ struct MsmPlan {
     u32 L;                // max points per task
     size_t max_tasks, max_partial;
     u32 ba_G;             // > 0: batched-affine accumulation with this many positions per thread (5b)
+    // fixed-base table path (msm_fixed_device): ncols digit columns per MSM share one bucket window (nwin == 1), the
+    // bases are rows of 2^(c w) * G_i of row_stride points each
+    int ncols = 0;        // 0: the ordinary pipeline (digit columns == windows)
+    u32 row_stride = 0;
 };
 static MsmPlan make_plan(size_t k, size_t nbatch) {
     MsmPlan p;
@@ -683,6 +693,27 @@ static MsmPlan make_plan(size_t k, size_t nbatch) {
     // instructions per addition on this 255-bit field, and latency-bound where the task path is pipe-bound).
     const int t8 = rt().tune[8];
     p.ba_G = (t8 == 64 || t8 == 128 || t8 == 256) ? (u32)t8 : 0u;
+    return p;
+}
+
+// plan of the fixed-base table path: ncols digit columns of width c per MSM into ONE window of 2^(c-1) buckets
+static MsmPlan make_plan_fixed(size_t k, size_t nbatch, int c, int ncols, size_t row_stride) {
+    MsmPlan p;
+    p.c = c;
+    p.nwin = 1;
+    p.nbatch = nbatch;
+    p.nwt = nbatch;
+    p.B = (size_t)1 << (c - 1);
+    p.nb = p.B * p.nwt;
+    const size_t work = k * (size_t)ncols * nbatch;
+    p.L = 128;
+    const size_t mean4 = 4 * (k * (size_t)ncols / p.B);
+    if (mean4 > p.L) p.L = (u32)std::min<size_t>(mean4, MSM_MAX_L);
+    p.max_tasks = p.nb + work / p.L + 1;
+    p.max_partial = 2 * (work / p.L) + 2;
+    p.ba_G = 0;
+    p.ncols = ncols;
+    p.row_stride = (u32)row_stride;
     return p;
 }
 
@@ -718,7 +749,8 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     if (int e = ws_get(WS_OFFSETS, (2 * P.nb + nblk + 1) * 4, (void**)&offsets)) return e;
     cursor = offsets + P.nb;
     bsum = cursor + P.nb;
-    if (int e = ws_get(WS_IDX, P.nwt * k * 4, (void**)&idx)) return e;
+    const int dcols = P.ncols ? P.ncols : P.nwin;          // digit columns per MSM
+    if (int e = ws_get(WS_IDX, P.nbatch * (size_t)dcols * k * 4, (void**)&idx)) return e;
     if (int e = ws_get(WS_ORDER, P.max_tasks * sizeof(uint2), (void**)&tasks)) return e;
     // pslot | cbase | big (nb words each) | chunk list (max_partial entries)
     if (int e = ws_get(WS_SIZEHIST, 3 * P.nb * 4 + P.max_partial * sizeof(uint2), (void**)&pslot)) return e;
@@ -743,11 +775,11 @@ static int msm_enqueue(const Affine<C>* d_bases, const Fe<CurveTraits<C>::SCALAR
     HALO_CUDA(cudaMemsetAsync(counts, 0, zero_words * 4, st));
     const int grid_pts = (int)std::min<size_t>((total + 255) / 256, (size_t)R.sm_count * 8);
     const int grid_b = (int)std::min<size_t>((P.nb + 255) / 256, (size_t)R.sm_count * 8);
-    msm_count<SF><<<grid_pts, 256, 0, st>>>(d_scalars, k, total, P.c, P.nwin, counts);
+    msm_count<SF><<<grid_pts, 256, 0, st>>>(d_scalars, k, total, P.c, dcols, P.ncols ? 1 : 0, counts);
     prof_mark("count");
     scan_u32(counts, P.nb, offsets, cursor, bsum, nullptr, st);
     prof_mark("scan");
-    msm_scatter<SF><<<grid_pts, 256, 0, st>>>(d_scalars, k, total, P.c, P.nwin, cursor, idx);
+    msm_scatter<SF><<<grid_pts, 256, 0, st>>>(d_scalars, k, total, P.c, dcols, P.ncols ? 1 : 0, P.row_stride, cursor, idx);
     prof_mark("scatter");
     if (P.ba_G) {
         // batched-affine accumulation (5b): persistent grid, scratch per resident warp
@@ -1127,6 +1159,22 @@ int msm_device(const void* d_bases, const void* d_scalars, size_t k, size_t nbat
     }
     MsmPlan P = make_plan(k, nbatch);
     if (base_stride) P.ba_G = 0;                          // per-MSM base sets (the IPA's L/R pair): task path
+    // Commitments over the resident generators (pedersen::commit, pedersen.rs:7-27: the bases are pp.Gs[0..k)): the
+    // fixed-base table of the parameter set turns the digit columns into ONE bucket window per MSM with c = 18-20
+    // (tuning key 14 = 1: off).  Large prefixes only -- below half the set the ordinary pipeline is as good.
+    // The L / R pair of an opening's FIRST round has the same property (its generators are still pp.Gs): two MSMs over
+    // the two halves, addressed like the ordinary pair (bases + k with a stride of -k) inside every row of the table.
+    const bool commit_shape = d_bases == R.pp[C].d_gs && base_stride == 0 && 2 * k >= R.pp[C].n && k <= R.pp[C].n;
+    const bool lr_shape = nbatch == 2 && 2 * k == R.pp[C].n && base_stride == -(ptrdiff_t)k &&
+                          d_bases == (const void*)((const Affine<C>*)R.pp[C].d_gs + k);
+    if ((commit_shape || lr_shape) && R.tune[14] != 1 && R.tune[8] == 0 && R.pp[C].n >= ((size_t)1 << 18) && nbatch <= 64) {
+        const void* tab = nullptr; int fc = 0, fcols = 0; size_t stride = 0;
+        if (int e = ensure_fixed_table<C>(&tab, &fc, &fcols, &stride)) return e;
+        if (tab && nbatch * (size_t)fcols * k < ((size_t)1 << 32) && (size_t)fcols * stride < ((size_t)1 << 31)) {
+            P = make_plan_fixed(k, nbatch, fc, fcols, stride);
+            d_bases = lr_shape ? (const void*)((const Affine<C>*)tab + k) : tab;
+        }
+    }
     HALO_CHECK(P.nwt * k < ((size_t)1 << 32), HALO_EINVAL, "msm: batch too large (nbatch*nwin*k must be < 2^32)");
     XYZZ<C>* d_win = nullptr;
     if (int e = msm_enqueue<C>((const Affine<C>*)d_bases, (const Fe<CurveTraits<C>::SCALAR>*)d_scalars, k, P, base_stride, &d_win)) return e;

@@ -25,6 +25,9 @@ struct ResidentParams {
     uint64_t s_xy[8], h_xy[8]; // host copies (affine, Montgomery)
     void* d_fold_tab = nullptr;   // IPA fixed-base fold table: 2^k * Gs[n/2 + j], k-major (ipa.cu), for openings of size fold_tab_n
     size_t fold_tab_n = 0;
+    void* d_fixed_tab = nullptr;      // commit path: rows 2^(c w) * Gs[i] (ipa.cu ensure_fixed_table, msm.cu msm_fixed)
+    size_t fixed_tab_n = 0;
+    int fixed_tab_c = 0;
     void* d_fold_tab_loc = nullptr;   // the same table over this rank's generators of a sharded opening (ipa.cu)
     size_t fold_tab_loc_n = 0;
     int fold_tab_loc_world = 0, fold_tab_loc_rank = 0;

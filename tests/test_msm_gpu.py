@@ -347,3 +347,52 @@ def test_msm_host_buffers_pipelined_by_point_range(hb, oracle, curve):
         assert (_aff(O, curve, hb.group.point_dot_affine(curve, sc, pts)) == exp).all()
     finally:
         lib.halo_set_tuning(9, 0)
+
+
+@pytest.mark.parametrize("curve", [0, 1])
+def test_commit_over_resident_generators_fixed_base_table(hb, oracle, curve):
+    """Commitments over a large resident parameter set take the fixed-base table (rows 2^(c w) * Gs[i], one bucket window
+    per MSM): equal to the ordinary pipeline (tuning key 14 = 1) and to the oracle, for the full length, a ragged prefix
+    above half the set, a short prefix (ordinary pipeline), a batch, and scalar vectors that stress the digit columns
+    (all p - 1: every digit at its signed extreme with carries into the top column; 0 / 1; a duplicate-heavy generator
+    set with identities as in the reference's)."""
+    O = oracle
+    lib = hb._lib.lib
+    sf = O.SCALAR_FIELD[curve]
+    p = O.MODULUS[sf]
+    n = 1 << 18
+    gs = O.points_arith(curve, n + 2, k0=0x1234 + curve)
+    gs[5] = gs[4]; gs[7] = 0; gs[n - 1] = gs[0]                      # duplicates and an identity among the generators
+    hb.pp.reset(curve)
+    hb.pp.set_pp(curve, gs[:n], gs[n], gs[n + 1])
+    aff = lambda q: O.point_to_affine(curve, np.asarray(q, dtype=np.uint64).reshape(-1, 12))
+    try:
+        cases = {"random": O.random_scalars(sf, n, 5), "pm1": np.tile(O.ints_to_mont(sf, [p - 1]), (n, 1)),
+                 "zero_one": O.ints_to_mont(sf, [0, 1] * (n // 2))}
+        cases["random"][3] = 0
+        for name, sc in cases.items():
+            for k in (n, n // 2 + 7, n // 4):
+                got = hb.pcdl.commit(curve, sc[:k], n - 1)
+                lib.halo_set_tuning(14, 1)
+                try:
+                    plain = hb.pcdl.commit(curve, sc[:k], n - 1)
+                finally:
+                    lib.halo_set_tuning(14, 0)
+                assert (aff(got) == aff(plain)).all(), (name, k)
+                if name == "random" or k == n:
+                    assert (aff(got) == aff(O.msm(curve, gs[:k], sc[:k]))).all(), (name, k)
+        # a batch over the resident set (the 16 commits of a prover round use this shape)
+        b = 3
+        cols = O.random_scalars(sf, b * n, 9).reshape(b, n, 4)
+        cols[1, :100] = 0
+        got = hb.group.msm_batch_resident(curve, cols) if hasattr(hb.group, "msm_batch_resident") else None
+        if got is None:
+            import ctypes
+            out = np.zeros((b, 12), dtype=np.uint64)
+            hb._lib.check(lib.halo_msm_batch(curve, ctypes.c_size_t(0), hb._lib.ptr(cols.reshape(-1)), ctypes.c_size_t(n), ctypes.c_size_t(b),
+                                             hb._lib.ptr(out.reshape(-1))))
+            got = out
+        for j in range(b):
+            assert (aff(got[j]) == aff(O.msm(curve, gs[:n], cols[j]))).all(), j
+    finally:
+        hb.pp.reset(curve)
