@@ -1029,7 +1029,7 @@ int pcdl_open(const uint64_t* coeffs, size_t len, const uint64_t* C_xyz, size_t 
             else if (int e = msm_device<C>(gs, tail_s, Tp, 2, lr, 0)) return e;     // syncs: wh may go out of scope
         } else {
             if (W > 1) { if (int e = dist_msm_device<C>(gs + m, cs, m, 2, lr, -(ptrdiff_t)m)) return e; }
-            else if (r == 0 && n == R.pp[C].n && !R.is_lane) {
+            else if (r == 0 && n == R.pp[C].n) {
                 // the generators are still pp.Gs: addressed in place, msm_device takes the commit-path table for the pair
                 if (int e = msm_device<C>((const Affine<C>*)R.pp[C].d_gs + m, cs, m, 2, lr, -(ptrdiff_t)m)) return e;
             }
