@@ -507,9 +507,82 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     }
     // staged evaluation vectors: PI (row i at omega^(i+1), negated), l1, and the three shifted witness columns
     SF* stage = tmp;                                       // [PI | l1 | wom0 wom1 wom2]
+    // Round 1 needs the witness columns only, so they are uploaded FIRST and (one GPU) their commitments start at once
+    // on a helper thread in the library's second execution context, beside the upload of the other 41 columns, the staged
+    // evaluation vectors and the small inverse transforms -- the GPU is otherwise idle while the host stages 1.4 GB.
+    // Tuning key 15 = 1: commitments after round 0 as before.
+    const bool dense = R.tune[6] == 1;
+    int h_flags[N_COLS];
+    for (int i = 0; i < N_COLS; ++i) h_flags[i] = 0;
+    auto nonzero = [&](int c) { return dense || h_flags[c] != 0; };
+    // nb adjacent columns -> nb commitments as one batched MSM over the resident generators; sharded: every rank takes
+    // its point range of every column (packed into a compact batch) and the window sums are all-gathered (dist.cu)
+    const size_t pr_lo = n * (size_t)rank / (size_t)world, pr_hi = n * (size_t)(rank + 1) / (size_t)world;
+    auto commit_run = [&](const SF* first, size_t nb, uint64_t* o) -> int {
+        Runtime& Rk = rt();                                 // the main runtime, or the lane inside a helper thread
+        if (!sharded) return msm_device<C>(Rk.pp[C].d_gs, first, n, nb, o, 0);
+        const size_t kl = pr_hi - pr_lo;
+        SF* pack = nullptr;
+        if (kl) {
+            if (int e = ws_get(WS_PLONK_PACK, nb * kl * 32, (void**)&pack)) return e;
+            HALO_CUDA(cudaMemcpy2DAsync(pack, kl * 32, first + pr_lo, n * 32, kl * 32, nb, cudaMemcpyDeviceToDevice, st));
+        }
+        return dist_msm_device<C>((const char*)Rk.pp[C].d_gs + pr_lo * 64, pack, kl, nb, o);
+    };
+    // commitments of `count` adjacent columns: one batched MSM per run of nonzero columns
+    auto commit_cols = [&](const SF* first, int count, auto&& live, uint64_t* o) -> int {
+        const Jac<C> id = xyzz_to_jac<C>(xyzz_identity<C>());
+        for (int i = 0; i < count;) {
+            if (!live(i)) { memcpy(o + 12 * i, &id, 96); ++i; continue; }
+            int j = i + 1;
+            while (j < count && live(j)) ++j;
+            if (int e = commit_run(first + (size_t)i * n, (size_t)(j - i), o + 12 * i)) return e;
+            i = j;
+        }
+        return HALO_OK;
+    };
+    uint64_t* o_vs = out;
+    uint64_t* o_Cws = out + 78 * 4;
+    uint64_t* o_Cts = o_Cws + NW * 12;
+    uint64_t* o_Cz = o_Cts + NT * 12;
+    uint64_t* o_pir = o_Cz + 12;
+    uint64_t* o_piro = o_pir + evalproof_words(lg_n);
+    uint64_t* o_acc = o_piro + evalproof_words(lg_n);
+    Runtime* lane1 = nullptr;
+    int rc_w = HALO_OK;
+    std::string err_w;
+    Workers helper1;
     if (rank == 0) {
-        if (d_circuit) { if (int e = upload_staged(col(COL_W), polys, (size_t)NW * n * 32)) return e; }
-        else if (int e = upload_staged(cols, polys, (size_t)N_IN * n * 32)) return e;
+        const uint64_t* w_src = d_circuit ? polys : polys + (size_t)COL_W * n * 4;
+        if (int e = upload_staged(col(COL_W), w_src, (size_t)NW * n * 32)) return e;
+        if (!sharded && !R.is_lane && R.tune[15] != 1 && n >= 4096) {
+            HALO_CUDA(cudaMemsetAsync(d_flags + COL_W, 0, NW * sizeof(int), st));
+            plonk_nonzero_kernel<S><<<dim3(32, NW), 256, 0, st>>>(col(COL_W), n, d_flags + COL_W);
+            R.launches += 1;
+            HALO_CUDA(cudaMemcpyAsync(h_flags + COL_W, d_flags + COL_W, NW * sizeof(int), cudaMemcpyDeviceToHost, st));
+            HALO_CUDA(cudaStreamSynchronize(st));          // the witness columns are in place, their flags on the host
+            if (R.tune[14] != 1 && 2 * n >= R.pp[C].n) {    // the commit-path table is built by the main runtime only
+                const void* t_ = nullptr; int c_ = 0, k_ = 0; size_t s_ = 0;
+                if (int e = ensure_fixed_table<C>(&t_, &c_, &k_, &s_)) return e;
+            }
+            lane1 = lane_get();
+            if (lane1) {
+                helper1.spawn(1, [&]() {
+                    LaneScope scope(lane1);
+                    try {
+                        rc_w = cudaSetDevice(lane1->device) == cudaSuccess
+                                   ? commit_cols(col(COL_W), NW, [&](int i) { return nonzero(COL_W + i); }, o_Cws) : HALO_ECUDA;
+                    } catch (...) { rc_w = HALO_ECUDA; last_err() = "plonk: exception in the witness commitments"; }
+                    if (rc_w) err_w = last_err();
+                    cudaStreamSynchronize(lane1->stream);
+                });
+                if (helper1.size() == 0) lane1 = nullptr;
+            }
+        }
+        if (!d_circuit) {                                  // the other columns: [0, COL_W) and [COL_W + NW, N_IN)
+            if (int e = upload_staged(cols, polys, (size_t)COL_W * n * 32)) return e;
+            if (int e = upload_staged(col(COL_W + NW), polys + (size_t)(COL_W + NW) * n * 4, (size_t)(N_IN - COL_W - NW) * n * 32)) return e;
+        }
         HALO_CUDA(cudaMemsetAsync(stage, 0, 2 * n * 32, st));
         std::vector<SF> neg_pub(n_pub);
         for (size_t i = 0; i < n_pub; ++i) neg_pub[i] = fe_neg<S>(H::scalar(pub + 4 * i));
@@ -536,7 +609,6 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     if (int e = ntt_device<S>(stage + n, col(COL_L1), (int)lg_n, 4, true, nullptr)) return e;   // l1, wom0..2 are adjacent
     // which columns are the zero polynomial: their commitments are the identity, their coset evaluations are zero,
     // and the custom gates of an all-zero selector are switched off (tuning key 6 = 1 treats every column as dense)
-    const bool dense = R.tune[6] == 1;
     HALO_CUDA(cudaMemsetAsync(d_flags, 0, N_COLS * sizeof(int), st));
     plonk_nonzero_kernel<S><<<dim3(32, N_IN), 256, 0, st>>>(cols, n, d_flags);
     R.launches += 1;
@@ -545,52 +617,28 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     const SF id_step = fe_from_u64<S>((u64)n);
     plonk_id_affine_kernel<S><<<dim3(32, NS - 1), 256, 0, st>>>(col(COL_ID), n, id_step, d_flags + (N_COLS - 1));
     R.launches += 1;
-    int h_flags[N_COLS];
     int ids_not_affine = 1;
-    HALO_CUDA(cudaMemcpyAsync(h_flags, d_flags, N_IN * sizeof(int), cudaMemcpyDeviceToHost, st));
-    HALO_CUDA(cudaMemcpyAsync(&ids_not_affine, d_flags + (N_COLS - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
-    HALO_CUDA(cudaStreamSynchronize(st));
+    {
+        // (a helper thread may be reading the witness entries of h_flags: they are rewritten with the same values only
+        // when no helper runs)
+        int f_all[N_IN];
+        HALO_CUDA(cudaMemcpyAsync(f_all, d_flags, N_IN * sizeof(int), cudaMemcpyDeviceToHost, st));
+        HALO_CUDA(cudaMemcpyAsync(&ids_not_affine, d_flags + (N_COLS - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+        HALO_CUDA(cudaStreamSynchronize(st));
+        for (int i = 0; i < N_IN; ++i) if (!lane1 || i < COL_W || i >= COL_W + NW) h_flags[i] = f_all[i];
+    }
     HALO_CUDA(cudaMemsetAsync(d_flags + (N_COLS - 1), 0, sizeof(int), st));
     const bool ids_derived = !ids_not_affine && !dense;
-    auto nonzero = [&](int c) { return dense || h_flags[c] != 0; };
-    // nb adjacent columns -> nb commitments as one batched MSM over the resident generators; sharded: every rank takes
-    // its point range of every column (packed into a compact batch) and the window sums are all-gathered (dist.cu)
-    const size_t pr_lo = n * (size_t)rank / (size_t)world, pr_hi = n * (size_t)(rank + 1) / (size_t)world;
-    auto commit_run = [&](const SF* first, size_t nb, uint64_t* o) -> int {
-        if (!sharded) return msm_device<C>(R.pp[C].d_gs, first, n, nb, o, 0);
-        const size_t kl = pr_hi - pr_lo;
-        SF* pack = nullptr;
-        if (kl) {
-            if (int e = ws_get(WS_PLONK_PACK, nb * kl * 32, (void**)&pack)) return e;
-            HALO_CUDA(cudaMemcpy2DAsync(pack, kl * 32, first + pr_lo, n * 32, kl * 32, nb, cudaMemcpyDeviceToDevice, st));
-        }
-        return dist_msm_device<C>((const char*)R.pp[C].d_gs + pr_lo * 64, pack, kl, nb, o);
-    };
-    // commitments of `count` adjacent columns: one batched MSM per run of nonzero columns
-    auto commit_cols = [&](const SF* first, int count, auto&& live, uint64_t* o) -> int {
-        const Jac<C> id = xyzz_to_jac<C>(xyzz_identity<C>());
-        for (int i = 0; i < count;) {
-            if (!live(i)) { memcpy(o + 12 * i, &id, 96); ++i; continue; }
-            int j = i + 1;
-            while (j < count && live(j)) ++j;
-            if (int e = commit_run(first + (size_t)i * n, (size_t)(j - i), o + 12 * i)) return e;
-            i = j;
-        }
-        return HALO_OK;
-    };
     lap("round 0 (upload, iNTTs)");
 
     Transcript<C> tr(LABEL_PLONK);
-    uint64_t* o_vs = out;
-    uint64_t* o_Cws = out + 78 * 4;
-    uint64_t* o_Cts = o_Cws + NW * 12;
-    uint64_t* o_Cz = o_Cts + NT * 12;
-    uint64_t* o_pir = o_Cz + 12;
-    uint64_t* o_piro = o_pir + evalproof_words(lg_n);
-    uint64_t* o_acc = o_piro + evalproof_words(lg_n);
 
     // ---- round 1 (:114-115): the 16 witness commitments as one batched MSM over the resident generators
-    if (int e = commit_cols(col(COL_W), NW, [&](int i) { return nonzero(COL_W + i); }, o_Cws)) return e;
+    if (lane1) {                                           // started beside round 0
+        helper1.join();
+        lane_finish(lane1);
+        if (rc_w) { last_err() = err_w; return rc_w; }
+    } else if (int e = commit_cols(col(COL_W), NW, [&](int i) { return nonzero(COL_W + i); }, o_Cws)) return e;
     for (int i = 0; i < NW; ++i) tr.absorb_point(H::from_words(o_Cws + 12 * i));
     lap("round 1 (16 commits)");
 

@@ -70,6 +70,15 @@ def test_plonk_2p16_proof_equals_oracle(hb, oracle, params16, curve, kind, n_pub
     finally:
         circuit.release()
     same_proof(O, curve, LG, res.w, exp)
+    # the witness commitments run beside the rest of round 0 and the two openings side by side (second execution
+    # context); strictly one after the other (tuning keys 15 and 13) gives the identical proof
+    from halo_b200._lib import lib
+    lib.halo_set_tuning(15, 1); lib.halo_set_tuning(13, 1)
+    try:
+        seq = hb.plonk.PlonkProof.naive_prover(circuit, pub, wit)
+    finally:
+        lib.halo_set_tuning(15, 0); lib.halo_set_tuning(13, 0)
+    same_proof(O, curve, LG, seq.w, exp)
     ok = O.plonk_verify(curve, LG, circuit.C_qs, c["public_inputs"], c["n_public"], acc0.q.w, pi.w)
     if kind == "random":
         assert not ok

@@ -106,6 +106,7 @@ def test_proof_matches_oracle_and_verifies(hb, oracle, params, curve, lg_n, kind
     finally:
         lib.halo_set_tuning(13, 0)
     same_proof(O, curve, lg_n, serial.w, exp)
+    # (tuning key 15 = 1: the witness commitments after round 0 instead of beside it; they overlap only from 2^12 rows)
     # circuit columns resident on the device (halo_plonk_circuit_load): only the witness is uploaded, same proof
     circuit.make_resident(c["polys"])
     try:
