@@ -50,6 +50,9 @@ private:
         return fe_mul<F>(x3, x4);
     }
     void permute() {
+#if defined(HALO_HOST_ADX)
+        if (hostimpl::host_has_adx()) { permute_adx(); return; }
+#endif
         for (int r = 0; r < 55; ++r) {
             Fe<F> t[3] = {pow7(s_[0]), pow7(s_[1]), pow7(s_[2])};
             for (int i = 0; i < 3; ++i) {
@@ -59,6 +62,35 @@ private:
             }
         }
     }
+#if defined(HALO_HOST_ADX)
+    // The same 55 rounds on 64-bit limbs throughout (BMI2 + ADX rows of field.cuh): the state, the s-box intermediates and
+    // the MDS rows never pass through the 32-bit-limb element type.  Every value stays below p (products and sums are
+    // fully reduced), which is what the five-word rows need.
+    void permute_adx() {
+        using namespace hostimpl;
+        u64 st[3][4], t[3][4], p[4];
+        modulus64<F>(p);
+        for (int i = 0; i < 3; ++i) load(st[i], s_[i].l);
+        for (int r = 0; r < 55; ++r) {
+            for (int i = 0; i < 3; ++i) {
+                u64 x2[4], x3[4], x4[4];
+                mont_mul_adx<F>(x2, st[i], st[i]);
+                mont_mul_adx<F>(x4, x2, x2);
+                mont_mul_adx<F>(x3, x2, st[i]);
+                mont_mul_adx<F>(t[i], x4, x3);
+            }
+            for (int i = 0; i < 3; ++i) {
+                const unsigned long long (*M)[4] = poseidon_data::POSEIDON_MDS[F] + 3 * i;
+                u64 d[4];
+                mont_dot3_adx<F>(d, t[0], (const u64*)M[0], t[1], (const u64*)M[1], t[2], (const u64*)M[2]);
+                add(d, d, (const u64*)poseidon_data::POSEIDON_RC[F][3 * r + i]);      // both below p < 2^255: no carry out
+                if (geq(d, p)) sub(d, d, p);
+                for (int k = 0; k < 4; ++k) st[i][k] = d[k];
+            }
+        }
+        for (int i = 0; i < 3; ++i) store(s_[i].l, st[i]);
+    }
+#endif
     Fe<F> s_[3];
     bool absorbing_;
     int filled_;
