@@ -90,7 +90,10 @@ int halo_msm_batch_dev(int curve, const void* d_bases_xy, size_t base_off, const
  * key 9 = 1 disables the point-range pipelining of halo_msm over host buffers (upload overlapped with accumulation),
  * key 10 = number of point ranges of that pipeline (2..16; default 4),
  * key 8 = 64 / 128 / 256: bucket accumulation of the general MSM pipeline by batched affine additions with that many
- *        positions per thread (opt-in: measured slower than the default XYZZ task path on these 255-bit fields) */
+ *        positions per thread (opt-in: measured slower than the default XYZZ task path on these 255-bit fields),
+ * key 13 = 1 runs the two openings of a PLONK proof one after the other instead of side by side,
+ * key 14 = 1 disables the fixed-base table of the resident generators (commit path, first L / R pair of an opening),
+ * key 15 = 1 computes the witness commitments of a PLONK proof after round 0 instead of beside it */
 int halo_set_tuning(int key, int value);
 /* window width override for experiments (0 = automatic) */
 int halo_msm_set_window(int c);
