@@ -116,7 +116,11 @@ int upload_staged(void* d_dst, const void* h_src, size_t bytes, cudaStream_t ord
     // up to 16 staging threads (2^20-gate columns: 36 -> 30 ms with 16 instead of 8); the ranks of one box share the
     // host's cores, so a process that has joined a communicator takes its share of them
     const int hw = (int)std::max(2u, std::thread::hardware_concurrency());
-    const int T = std::max(2, std::min(TMAX, dist_on() ? hw / std::max(1, dist_world()) : hw));
+    const size_t nchunks_all = (bytes + CH - 1) / CH;
+    // ... and no more threads than half the chunks: an 8 MB slice of a pipelined MSM upload is four chunks, and starting
+    // sixteen threads for it costs more than the copy
+    const int T = (int)std::max<size_t>(1, std::min<size_t>((size_t)std::max(2, std::min(TMAX, dist_on() ? hw / std::max(1, dist_world()) : hw)),
+                                                            nchunks_all / 2));
     if (!R.up_stream[0]) {
         for (int t = 0; t < TMAX; ++t) {
             HALO_CUDA(cudaStreamCreateWithFlags(&R.up_stream[t], cudaStreamNonBlocking));
