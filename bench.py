@@ -256,16 +256,21 @@ def measure_path(lib, check, halo_b200, torch, stream, d_pts, h_sc, log_n):
         rows = 1 << lg
         acc0 = halo_b200.acc.Accumulator.zero(PALLAS, rows)
         pub = halo_b200.plonk.PlonkPublicInputs(np.zeros((0, 4), dtype=np.uint64), acc0)
-        for dense in (False, True):
-            polys, w_evals = halo_b200.plonk.synthetic_circuit(PALLAS, lg, seed=7, dense_gates=dense)
+        # three circuits: the config-4 multiplication circuit; every selector / witness / round-constant column random with
+        # the constant selector solved so that the circuit IS satisfied (what an honest prover proves: 8-coset quotient);
+        # the same with an unsatisfied witness (the 16-coset fallback the reference's divide_by_vanishing_poly implies)
+        for dense, sat in ((False, False), (True, True), (True, False)):
+            polys, w_evals = halo_b200.plonk.synthetic_circuit(PALLAS, lg, seed=7, dense_gates=dense, satisfied=sat)
             circuit = halo_b200.plonk.PlonkCircuit.from_polys(PALLAS, polys, 0)
             wit = halo_b200.plonk.PlonkWitness(polys, w_evals)
             best = None
             for _ in range(2):
                 t = time.perf_counter(); pi = halo_b200.plonk.PlonkProof.naive_prover(circuit, pub, wit); dt = time.perf_counter() - t
                 best = dt if best is None else min(best, dt)
-            key = f"plonk_prove_2^{lg}" + ("_all_gates" if dense else "")
+            key = f"plonk_prove_2^{lg}" + (("_all_gates" if sat else "_all_gates_unsatisfied_witness") if dense else "")
             out[key] = {"ms": best * 1e3, "h2d_bytes": int(polys.nbytes + w_evals.nbytes)}
+            if dense and sat:
+                t = time.perf_counter(); pi.verify(circuit, pub); out[key]["verify_ms"] = (time.perf_counter() - t) * 1e3
             if not dense:
                 t = time.perf_counter(); pi.verify(circuit, pub); out[f"plonk_verify_2^{lg}"] = {"ms": (time.perf_counter() - t) * 1e3}
                 # the circuit's own 41 columns resident in HBM (halo_plonk_circuit_load): a proof uploads its witness only
@@ -589,7 +594,7 @@ def run_halo(args, rank, world, local_rank):
         acc0 = halo_b200.acc.Accumulator.zero(PALLAS, rows)            # the genesis accumulator belongs to the generator set
         pub = halo_b200.plonk.PlonkPublicInputs(np.zeros((0, 4), dtype=np.uint64), acc0)
         for dense in (False, True):
-            polys, w_evals = halo_b200.plonk.synthetic_circuit(PALLAS, lg, seed=7, dense_gates=dense)
+            polys, w_evals = halo_b200.plonk.synthetic_circuit(PALLAS, lg, seed=7, dense_gates=dense, satisfied=dense)
             circuit = halo_b200.plonk.PlonkCircuit.from_polys(PALLAS, polys, 0)
             wit = halo_b200.plonk.PlonkWitness(polys, w_evals)
             def timed_one():
@@ -604,8 +609,7 @@ def run_halo(args, rank, world, local_rank):
                     best = float(tt.item()) if best is None else min(best, float(tt.item()))
                 return best, pi
             t_one, pi = timed_one()
-            if not dense:
-                pi.verify(circuit, pub)
+            pi.verify(circuit, pub)                       # both circuits are satisfied: the proofs must be accepted
             key = "all_gates" if dense else "mul_circuit"
             one[key + "_ms"] = t_one * 1e3
             if not dense:

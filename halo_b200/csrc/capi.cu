@@ -266,7 +266,7 @@ template <int C> int pcdl_succinct_check(const uint64_t*, uint64_t*, uint64_t*);
 template <int C> int pcdl_check(const uint64_t*);
 template <int C> int acc_prover(const uint64_t*, size_t, uint64_t*, bool);
 size_t plonk_proof_words(unsigned lg_n);
-template <int C> int plonk_prove(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*, bool);
+template <int C> int plonk_prove(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*, bool, uint64_t*);
 int plonk_circuit_shape(int handle, int* curve, unsigned* lg_n);
 static inline size_t instance_words(unsigned lg_n) { return 24 * (size_t)lg_n + 54; }
 int plonk_circuit_load(int curve, unsigned lg_n, const uint64_t* polys, int* handle);
@@ -884,8 +884,28 @@ int halo_plonk_prove(int curve, unsigned lg_n, const uint64_t* polys, const uint
     LOCK(); NEED_INIT();
     HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
     HALO_CHECK(polys && w_evals && acc_prev && out_proof && (public_inputs || n_public == 0), HALO_EINVAL, "null argument");
-    return curve == 0 ? plonk_prove<0>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof, nullptr, false)
-                      : plonk_prove<1>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof, nullptr, false);
+    return curve == 0 ? plonk_prove<0>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof, nullptr, false, nullptr)
+                      : plonk_prove<1>(lg_n, polys, w_evals, public_inputs, n_public, acc_prev, out_proof, nullptr, false, nullptr);
+HALO_API_END
+}
+
+// f_GC on H (the gate constraints of protocol.rs:170-241 without the permutation terms): out[j] = f_GC(omega^j), n x 4
+// words.  All zero exactly when the witness satisfies every gate row.
+int halo_plonk_gate_residual(int curve, unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, const uint64_t* public_inputs,
+                             size_t n_public, uint64_t* out_evals) { HALO_API_BEGIN
+    LOCK(); NEED_INIT();
+    HALO_CHECK(curve == 0 || curve == 1, HALO_EINVAL, "curve must be 0 (Pallas) or 1 (Vesta)");
+    HALO_CHECK(polys && w_evals && out_evals && (public_inputs || n_public == 0), HALO_EINVAL, "null argument");
+    HALO_CHECK(lg_n >= 1 && lg_n <= 22, HALO_EINVAL, "plonk: rows must be a power of two in [2, 2^22]");
+    std::vector<uint64_t> acc(instance_words(lg_n), 0), proof(plonk_proof_words(lg_n), 0);
+    acc[12] = ((uint64_t)1 << lg_n) - 1;
+    Runtime& R = rt();
+    const int t15 = R.tune[15];
+    R.tune[15] = 1;                                        // no helper thread: the run stops before round 1's result is used
+    const int rc = curve == 0 ? plonk_prove<0>(lg_n, polys, w_evals, public_inputs, n_public, acc.data(), proof.data(), nullptr, false, out_evals)
+                              : plonk_prove<1>(lg_n, polys, w_evals, public_inputs, n_public, acc.data(), proof.data(), nullptr, false, out_evals);
+    R.tune[15] = t15;
+    return rc;
 HALO_API_END
 }
 
@@ -933,8 +953,8 @@ int halo_dist_plonk_prove(int curve, unsigned lg_n, const uint64_t* polys, const
     HALO_CHECK(out_proof && (dist_rank() != 0 || (polys && w_evals)), HALO_EINVAL, "null argument");
     std::vector<uint64_t> pub, acc;
     if (int e = dist_plonk_small_inputs(lg_n, public_inputs, n_public, acc_prev, pub, acc)) return e;
-    return curve == 0 ? plonk_prove<0>(lg_n, polys, w_evals, pub.data(), n_public, acc.data(), out_proof, nullptr, true)
-                      : plonk_prove<1>(lg_n, polys, w_evals, pub.data(), n_public, acc.data(), out_proof, nullptr, true);
+    return curve == 0 ? plonk_prove<0>(lg_n, polys, w_evals, pub.data(), n_public, acc.data(), out_proof, nullptr, true, nullptr)
+                      : plonk_prove<1>(lg_n, polys, w_evals, pub.data(), n_public, acc.data(), out_proof, nullptr, true, nullptr);
 HALO_API_END
 }
 int halo_dist_plonk_prove_circuit(int handle, const uint64_t* w_polys, const uint64_t* w_evals, const uint64_t* public_inputs,

@@ -460,7 +460,8 @@ size_t plonk_proof_words(unsigned lg_n) { return 78 * 4 + 33 * 12 + 2 * evalproo
 // polys / w_evals are read on rank 0 only.
 template <int C>
 int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, const uint64_t* pub, size_t n_pub,
-                const uint64_t* acc_prev, uint64_t* out, const void* d_circuit, bool shard) {
+                const uint64_t* acc_prev, uint64_t* out, const void* d_circuit, bool shard, uint64_t* residual_out) {
+    // residual_out != nullptr (halo_plonk_gate_residual): stop at round 4 and return f_GC on H instead of a proof
     typedef Host<C> H;
     typedef typename H::SF SF;
     constexpr int S = H::S;
@@ -735,6 +736,15 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     // degree < 8n and is interpolated from the 8 odd cosets, which form the coset w16n * (8n domain) and on which
     // Z_H is the constant w16^c - 1.  Otherwise the reference still returns the polynomial quotient (protocol.rs:256
     // drops the remainder), which takes f on all 16 cosets and the coefficient-form division.
+    if (residual_out) {
+        // the gate constraints alone (alpha = 0 removes the permutation terms): n values f_GC(omega^j), j = 0 .. n-1
+        ch.alpha = fe_zero<S>(); ch.alpha2 = fe_zero<S>();
+        if (int e = numerator_on_coset(0, f1, 0, 1, nullptr)) return e;
+        HALO_CUDA(cudaMemcpyAsync(residual_out, f1, n * 32, cudaMemcpyDeviceToHost, st));
+        HALO_CUDA(cudaStreamSynchronize(st));
+        if (trace) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); }
+        return HALO_OK;
+    }
     if (int e = numerator_on_coset(0, f1, 0, 1, nullptr)) return e;
     HALO_CUDA(cudaMemsetAsync(d_flags, 0, sizeof(int), st));
     plonk_nonzero_kernel<S><<<dim3(64, 1), 256, 0, st>>>(f1, n, d_flags);
@@ -916,8 +926,8 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
     if (trace) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); }
     return HALO_OK;
 }
-template int plonk_prove<0>(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*, bool);
-template int plonk_prove<1>(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*, bool);
+template int plonk_prove<0>(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*, bool, uint64_t*);
+template int plonk_prove<1>(unsigned, const uint64_t*, const uint64_t*, const uint64_t*, size_t, const uint64_t*, uint64_t*, const void*, bool, uint64_t*);
 
 // ---- circuit columns kept on the device across proofs: the analogue of the reference holding `x: PlonkCircuit` /
 // the Trace's polynomials for every proof of the same circuit (an IVC chain proves one circuit over and over)
@@ -969,8 +979,8 @@ int plonk_prove_resident(int handle, const uint64_t* w_polys, const uint64_t* w_
     auto& v = circuits();
     HALO_CHECK(handle >= 1 && (size_t)handle <= v.size() && v[handle - 1].d, HALO_EINVAL, "plonk: unknown circuit handle");
     const ResidentCircuit& rc = v[handle - 1];
-    return rc.curve == 0 ? plonk_prove<0>(rc.lg_n, w_polys, w_evals, pub, n_pub, acc_prev, out, rc.d, shard)
-                         : plonk_prove<1>(rc.lg_n, w_polys, w_evals, pub, n_pub, acc_prev, out, rc.d, shard);
+    return rc.curve == 0 ? plonk_prove<0>(rc.lg_n, w_polys, w_evals, pub, n_pub, acc_prev, out, rc.d, shard, nullptr)
+                         : plonk_prove<1>(rc.lg_n, w_polys, w_evals, pub, n_pub, acc_prev, out, rc.d, shard, nullptr);
 }
 
 namespace {

@@ -140,11 +140,27 @@ class PlonkProof:
         self._verify(circuit, public_inputs, False)
 
 
-def synthetic_circuit(curve, lg_n, seed=1, dense_gates=False):
+def gate_residual(curve, polys, w_evals, public_inputs=None):
+    """f_GC on H (protocol.rs:170-241 without the permutation terms): (n, 4) values f_GC(omega^j); all zero exactly when
+    every gate row is satisfied."""
+    _lib.ensure_init()
+    n = polys.shape[1]
+    lg_n = n.bit_length() - 1
+    pub = public_inputs if public_inputs is not None else np.zeros((0, 4), dtype=np.uint64)
+    out = np.zeros((n, 4), dtype=np.uint64)
+    check(lib.halo_plonk_gate_residual(curve, ctypes.c_uint(lg_n), ptr(np.ascontiguousarray(polys).reshape(-1)),
+                                       ptr(np.ascontiguousarray(w_evals).reshape(-1)), ptr(pub.reshape(-1)) if pub.shape[0] else None,
+                                       ctypes.c_size_t(pub.shape[0]), ptr(out.reshape(-1))))
+    return out
+
+
+def synthetic_circuit(curve, lg_n, seed=1, dense_gates=False, satisfied=False):
     """The synthetic workload of SURVEY §8(d) config 4, built with GPU arithmetic: rows w0 = a, w1 = b, w2 = a*b with
     q_m = 1, q_o = -1, identity permutation, no public inputs.  dense_gates=True additionally fills the five custom
     selectors, the round-constant columns and the remaining witnesses with random values (every gate expression
-    is then evaluated; the circuit is no longer satisfied).  Returns (polys (57, n, 4), w_evals (3, n, 4))."""
+    is then evaluated; the circuit is no longer satisfied).  satisfied=True (with dense_gates) then solves the constant
+    selector row by row, q_c := -(everything else of f_GC), so that the all-gates circuit IS satisfied -- what an honest
+    prover's circuit is -- and the quotient takes the 8-coset path.  Returns (polys (57, n, 4), w_evals (3, n, 4))."""
     from . import consts, group, poly
     field = curve
     n = 1 << lg_n
@@ -175,6 +191,10 @@ def synthetic_circuit(curve, lg_n, seed=1, dense_gates=False):
     polys = np.empty_like(cols)
     for lo in range(0, N_COLUMNS, 19):
         polys[lo:lo + 19] = poly.ntt(field, evals[lo:lo + 19], inverse=True)
+    if dense_gates and satisfied:
+        res = gate_residual(curve, polys, evals[10:13].copy())
+        qc = group.field_op(field, "sub", evals[4], res)                  # f_GC is linear in q_c with coefficient one
+        polys[4] = poly.ntt(field, qc.reshape(1, n, 4), inverse=True)[0]
     return polys, evals[10:13].copy()
 
 

@@ -267,6 +267,12 @@ int halo_scalar_dot_noalloc_dev(int field, const void* d_xs, const void* d_ys, s
 size_t halo_plonk_proof_words(unsigned lg_n);
 int halo_plonk_prove(int curve, unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, const uint64_t* public_inputs,
                      size_t n_public, const uint64_t* acc_prev, uint64_t* out_proof);
+/* The gate constraints on H: out_evals[j] = f_GC(omega^j), j < n (n x 4 words), i.e. the F_GC of
+ * crates/plonk/src/plonk/protocol.rs:170-241 evaluated on the rows, without the permutation terms.  All zero exactly when
+ * the witness satisfies every gate row (the quotient then takes the 8-coset path).  Same inputs as halo_plonk_prove; a
+ * set-up / diagnostic call (the synthetic all-gates circuit of the benchmark solves its constant selector with it). */
+int halo_plonk_gate_residual(int curve, unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, const uint64_t* public_inputs,
+                             size_t n_public, uint64_t* out_evals);
 /* The circuit's own columns kept on the device across proofs of the same circuit -- the analogue of the reference
  * holding `x: PlonkCircuit` and the Trace's polynomials for every step of an IVC chain (crates/plonk/src/frontend/ivc/
  * mod.rs:640-660 proves one circuit per curve over and over).  halo_plonk_circuit_load takes the same 57-column

@@ -242,3 +242,30 @@ def test_large_proof_verifies_and_matches_commit_path(hb, oracle):
             hb.plonk.PlonkProof(curve, lg_n, bad).verify_succinct(circuit, pub)
     finally:
         hb.pp.reset(curve)
+
+
+@pytest.mark.parametrize("curve", [0, 1])
+def test_all_gates_synthetic_circuit_satisfied(hb, oracle, params, curve):
+    """The benchmark's all-gates circuit (every selector, witness and round-constant column random) with its constant
+    selector solved row by row from halo_plonk_gate_residual: f_GC vanishes on H, the proof equals the oracle's field by
+    field, and BOTH verifiers accept it -- every custom gate expression is live in an accepted proof.  The unsolved
+    circuit has a non-zero residual and is rejected."""
+    O = oracle
+    lg_n = 8
+    n = 1 << lg_n
+    none = np.zeros((0, 4), dtype=np.uint64)
+    polys, w_evals = hb.plonk.synthetic_circuit(curve, lg_n, seed=21 + curve, dense_gates=True, satisfied=True)
+    assert not hb.plonk.gate_residual(curve, polys, w_evals).any()
+    acc0 = genesis(hb, curve, n)
+    circuit = hb.plonk.PlonkCircuit.from_polys(curve, polys, 0)
+    pub = hb.plonk.PlonkPublicInputs(none, acc0)
+    pi = hb.plonk.PlonkProof.naive_prover(circuit, pub, hb.plonk.PlonkWitness(polys, w_evals))
+    same_proof(O, curve, lg_n, pi.w, O.plonk_prove(curve, lg_n, polys, w_evals, none, acc0.q.w))
+    pi.verify(circuit, pub)
+    assert O.plonk_verify(curve, lg_n, circuit.C_qs, none, 0, acc0.q.w, pi.w)
+    bad_polys, bad_evals = hb.plonk.synthetic_circuit(curve, lg_n, seed=21 + curve, dense_gates=True)
+    assert hb.plonk.gate_residual(curve, bad_polys, bad_evals).any()
+    bad_circuit = hb.plonk.PlonkCircuit.from_polys(curve, bad_polys, 0)
+    bad = hb.plonk.PlonkProof.naive_prover(bad_circuit, pub, hb.plonk.PlonkWitness(bad_polys, bad_evals))
+    with pytest.raises(hb.Rejected):
+        bad.verify_succinct(bad_circuit, pub)

@@ -26,10 +26,10 @@ def set_pp(n):
     hb.pp.set_pp(CURVE, gs.cpu().numpy().view(np.uint64), sh[0], sh[1])
 
 
-def run(lg_n, dense=False, reps=2):
+def run(lg_n, dense=False, reps=2, satisfied=False):
     n = 1 << lg_n
     set_pp(n)
-    t = time.perf_counter(); polys, w_evals = hb.plonk.synthetic_circuit(CURVE, lg_n, dense_gates=dense); t_build = time.perf_counter() - t
+    t = time.perf_counter(); polys, w_evals = hb.plonk.synthetic_circuit(CURVE, lg_n, dense_gates=dense, satisfied=satisfied); t_build = time.perf_counter() - t
     acc0 = hb.acc.Accumulator.zero(CURVE, n)
     t = time.perf_counter(); circuit = hb.plonk.PlonkCircuit.from_polys(CURVE, polys, 0); t_setup = time.perf_counter() - t
     pub = hb.plonk.PlonkPublicInputs(np.zeros((0, 4), dtype=np.uint64), acc0)
@@ -52,7 +52,7 @@ def run(lg_n, dense=False, reps=2):
     for r in range(reps):
         t = time.perf_counter(); pi = hb.plonk.PlonkProof.naive_prover(circuit, pub, wit); best_res = min(best_res, time.perf_counter() - t)
     circuit.release()
-    print(f"n=2^{lg_n} {'all gates' if dense else 'mul circuit'}: prove {best * 1e3:.1f} ms ({best_res * 1e3:.1f} ms with the circuit resident)  verify {t_verify * 1e3:.1f} ms "
+    print(f"n=2^{lg_n} {('all gates' + ('' if satisfied else ', unsatisfied witness')) if dense else 'mul circuit'}: prove {best * 1e3:.1f} ms ({best_res * 1e3:.1f} ms with the circuit resident)  verify {t_verify * 1e3:.1f} ms "
           f"(accepted={ok})  [circuit build {t_build:.1f} s, selector commits {t_setup * 1e3:.0f} ms]", flush=True)
     return best, t_verify
 
@@ -61,4 +61,5 @@ if __name__ == "__main__":
     lgs = [int(x) for x in sys.argv[1:]] or [12, 16]
     for lg in lgs:
         run(lg)
+        run(lg, dense=True, satisfied=True)
         run(lg, dense=True, reps=1)
