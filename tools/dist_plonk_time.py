@@ -24,7 +24,7 @@ def worker(rank, world, idfile, lgs):
         hb.pp.set_pp(curve, gs.cpu().numpy().view(np.uint64), sh[0], sh[1])
         del gs
         for dense in (False, True):
-            polys, w_evals = hb.plonk.synthetic_circuit(curve, lg, dense_gates=dense)
+            polys, w_evals = hb.plonk.synthetic_circuit(curve, lg, dense_gates=dense, satisfied=dense)
             acc0 = hb.acc.Accumulator.zero(curve, n)
             circuit = hb.plonk.PlonkCircuit.from_polys(curve, polys, 0)
             pub = hb.plonk.PlonkPublicInputs(np.zeros((0, 4), dtype=np.uint64), acc0)
