@@ -705,7 +705,7 @@ def run_halo(args, rank, world, local_rank):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(k * 96), "d2h_bytes_per_step": int(nw * 128),
                 "ms_per_step": e2e_ms / args.steps, "host_buffers": "pinned",
                 "pageable": {"value": n_pts * args.steps / (e2e_pg_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_pg_ms / args.steps,
-                             "note": "plain malloc'd buffers (a Rust Vec): staged through pinned chunks by 8 host threads"}},
+                             "note": "plain malloc'd buffers (a Rust Vec): staged through pinned chunks (non-temporal copies) by the library's host threads"}},
         "gpu_launches": int(launches), "self_check": self_check, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu, "path": path,
     }))
     if dist is not None:
