@@ -245,7 +245,7 @@ def test_large_proof_verifies_and_matches_commit_path(hb, oracle):
 
 
 @pytest.mark.parametrize("curve", [0, 1])
-def test_all_gates_synthetic_circuit_satisfied(hb, oracle, params, curve):
+def test_all_gates_synthetic_circuit_satisfied(hb, oracle, curve):
     """The benchmark's all-gates circuit (every selector, witness and round-constant column random) with its constant
     selector solved row by row from halo_plonk_gate_residual: f_GC vanishes on H, the proof equals the oracle's field by
     field, and BOTH verifiers accept it -- every custom gate expression is live in an accepted proof.  The unsolved
@@ -254,6 +254,8 @@ def test_all_gates_synthetic_circuit_satisfied(hb, oracle, params, curve):
     lg_n = 8
     n = 1 << lg_n
     none = np.zeros((0, 4), dtype=np.uint64)
+    gs, S, H = O.pp_generate(curve, N_PP)                 # (an earlier test of this module resets the parameters)
+    hb.pp.reset(curve); hb.pp.set_pp(curve, gs, S, H); O.pp_set(curve, gs, S, H)
     polys, w_evals = hb.plonk.synthetic_circuit(curve, lg_n, seed=21 + curve, dense_gates=True, satisfied=True)
     assert not hb.plonk.gate_residual(curve, polys, w_evals).any()
     acc0 = genesis(hb, curve, n)
@@ -269,3 +271,4 @@ def test_all_gates_synthetic_circuit_satisfied(hb, oracle, params, curve):
     bad = hb.plonk.PlonkProof.naive_prover(bad_circuit, pub, hb.plonk.PlonkWitness(bad_polys, bad_evals))
     with pytest.raises(hb.Rejected):
         bad.verify_succinct(bad_circuit, pub)
+    hb.pp.reset(curve)

@@ -9,6 +9,9 @@ from halo_b200._lib import lib, check
 from halo_b200 import consts
 
 hb.init()
+for kv in os.environ.get('HALO_TUNE', '').split(','):          # HALO_TUNE="15=1,13=1": tuning keys
+    if '=' in kv:
+        lib.halo_set_tuning(int(kv.split('=')[0]), int(kv.split('=')[1]))
 s = torch.cuda.Stream()
 torch.cuda.set_stream(s)
 check(lib.halo_set_stream(ctypes.c_void_p(s.cuda_stream)))
