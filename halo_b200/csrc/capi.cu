@@ -556,7 +556,7 @@ int halo_shutdown(void) { HALO_API_BEGIN
     for (int c = 0; c < 2; ++c) {
         if (R.pp[c].d_gs) cudaFree(R.pp[c].d_gs);
         if (R.pp[c].d_fold_tab) cudaFree(R.pp[c].d_fold_tab);
-        if (R.pp[c].d_fold_tab_loc) cudaFree(R.pp[c].d_fold_tab_loc);
+        for (void* t : R.pp[c].d_fold_tab_loc) if (t) cudaFree(t);
         if (R.pp[c].d_fixed_tab) cudaFree(R.pp[c].d_fixed_tab);
         R.pp[c] = ResidentParams();
     }
@@ -709,7 +709,7 @@ int halo_pp_reset(int curve) { HALO_API_BEGIN
     HALO_CUDA(cudaStreamSynchronize(R.stream));
     if (R.pp[curve].d_gs) cudaFree(R.pp[curve].d_gs);
     if (R.pp[curve].d_fold_tab) cudaFree(R.pp[curve].d_fold_tab);
-    if (R.pp[curve].d_fold_tab_loc) cudaFree(R.pp[curve].d_fold_tab_loc);
+    for (void* t : R.pp[curve].d_fold_tab_loc) if (t) cudaFree(t);
     if (R.pp[curve].d_fixed_tab) cudaFree(R.pp[curve].d_fixed_tab);
     R.pp[curve] = ResidentParams();
     return HALO_OK;

@@ -30,6 +30,7 @@ struct NcclApi {
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*CommSplit)(ncclComm_t, int, int, ncclComm_t*, void*) = nullptr;      // optional (NCCL >= 2.18)
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
 struct DistState {
@@ -39,6 +40,11 @@ struct DistState {
     NcclApi api;
     void* d_send = nullptr; void* d_recv = nullptr; size_t send_cap = 0, recv_cap = 0;
     void* h_recv = nullptr; size_t h_cap = 0;
+    // the two HALVES of the communicator (ranks [0, world/2) and [world/2, world)), created on first use: inside a
+    // half scope (dist_half_enter / _leave) rank, world and every collective of this file refer to the caller's half
+    ncclComm_t full_comm = nullptr, half_comm = nullptr;
+    int full_rank = 0, full_world = 1;
+    bool in_half = false;
 };
 DistState& ds() { static DistState s; return s; }
 
@@ -54,6 +60,7 @@ int nccl_load() {
     a.AllGather = (decltype(a.AllGather))dlsym(h, "ncclAllGather");
     a.GetErrorString = (decltype(a.GetErrorString))dlsym(h, "ncclGetErrorString");
     a.Broadcast = (decltype(a.Broadcast))dlsym(h, "ncclBroadcast");
+    a.CommSplit = (decltype(a.CommSplit))dlsym(h, "ncclCommSplit");
     HALO_CHECK(a.GetUniqueId && a.CommInitRank && a.CommDestroy && a.AllGather && a.Broadcast && a.GetErrorString, HALO_ECUDA,
                "dist: libnccl lacks an expected symbol");
     a.handle = h;
@@ -82,6 +89,31 @@ int grow(void** p, size_t* cap, size_t bytes, bool host) {
 bool dist_on() { return ds().on; }
 int dist_rank() { return ds().rank; }
 int dist_world() { return ds().world; }
+
+// Half scope: two independent collectives (the two openings of one proof) run side by side on the two halves of the box.
+bool dist_half_available() {
+    const DistState& D = ds();
+    return D.on && !D.in_half && D.world >= 4 && D.world % 2 == 0 && D.api.CommSplit != nullptr;
+}
+int dist_half_enter() {                                    // collective over the FULL communicator on first use
+    DistState& D = ds();
+    HALO_CHECK(dist_half_available(), HALO_EINVAL, "dist: no half communicator (needs an even world >= 4 and ncclCommSplit)");
+    if (!D.half_comm) {
+        HALO_CUDA(cudaStreamSynchronize(rt().stream));
+        HALO_NCCL(D.api.CommSplit(D.comm, D.rank / (D.world / 2), D.rank, &D.half_comm, nullptr));
+    }
+    D.full_comm = D.comm; D.full_rank = D.rank; D.full_world = D.world;
+    D.comm = D.half_comm; D.world = D.full_world / 2; D.rank = D.full_rank % D.world;
+    D.in_half = true;
+    return HALO_OK;
+}
+void dist_half_leave() {
+    DistState& D = ds();
+    if (!D.in_half) return;
+    D.comm = D.full_comm; D.rank = D.full_rank; D.world = D.full_world;
+    D.in_half = false;
+}
+bool dist_in_half() { return ds().in_half; }
 
 // all-gather of `bytes` per rank between device buffers, on the library stream
 int dist_allgather_dev(const void* d_send, void* d_recv, size_t bytes) {
@@ -259,6 +291,8 @@ int halo_dist_shutdown(void) { HALO_API_BEGIN
     DistState& D = ds();
     if (!D.on) return HALO_OK;
     if (rt().inited) cudaStreamSynchronize(rt().stream);
+    dist_half_leave();
+    if (D.half_comm) { D.api.CommDestroy(D.half_comm); D.half_comm = nullptr; }
     D.api.CommDestroy(D.comm);
     if (D.d_send) cudaFree(D.d_send);
     if (D.d_recv) cudaFree(D.d_recv);

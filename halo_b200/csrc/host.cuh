@@ -66,6 +66,10 @@ int dist_allgather_dev(const void* d_send, void* d_recv, size_t bytes);
 int dist_allgather_host(const void* h_send, void* h_recv_all, size_t bytes);
 int dist_bcast_dev(void* d_buf, size_t bytes, int root);
 int dist_bcast_host(void* h_buf, size_t bytes, int root);
+bool dist_half_available();      // the communicator can be split into two halves (even world >= 4)
+int dist_half_enter();           // from here on rank / world / collectives refer to the caller's half
+void dist_half_leave();
+bool dist_in_half();
 template <int C> int dist_msm_device(const void* d_bases, const void* d_scalars, size_t k_local, size_t nbatch, uint64_t* out_xyz,
                                      ptrdiff_t base_stride = 0, bool from_host = false);
 

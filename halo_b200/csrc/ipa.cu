@@ -703,17 +703,18 @@ template <int C>
 static int ensure_fold_table_local(size_t n, int world, int rank, const Affine<C>* gl_hi, const Affine<C>** out) {
     Runtime& R = rt();
     ResidentParams& P = R.pp[C];
+    const int s = dist_in_half() ? 1 : 0;
     *out = nullptr;
-    if (P.d_fold_tab_loc && P.fold_tab_loc_n == n && P.fold_tab_loc_world == world && P.fold_tab_loc_rank == rank) {
-        *out = (const Affine<C>*)P.d_fold_tab_loc; return HALO_OK;
+    if (P.d_fold_tab_loc[s] && P.fold_tab_loc_n[s] == n && P.fold_tab_loc_world[s] == world && P.fold_tab_loc_rank[s] == rank) {
+        *out = (const Affine<C>*)P.d_fold_tab_loc[s]; return HALO_OK;
     }
     if (R.is_lane) return HALO_OK;
     HALO_CUDA(cudaStreamSynchronize(R.stream));
-    if (P.d_fold_tab_loc) { cudaFree(P.d_fold_tab_loc); P.d_fold_tab_loc = nullptr; P.fold_tab_loc_n = 0; }
+    if (P.d_fold_tab_loc[s]) { cudaFree(P.d_fold_tab_loc[s]); P.d_fold_tab_loc[s] = nullptr; P.fold_tab_loc_n[s] = 0; }
     void* tab = nullptr;
     if (int e = build_fold_table<C>(gl_hi, n / 2 / (size_t)world, &tab)) return e;
     if (!tab) return HALO_OK;
-    P.d_fold_tab_loc = tab; P.fold_tab_loc_n = n; P.fold_tab_loc_world = world; P.fold_tab_loc_rank = rank;
+    P.d_fold_tab_loc[s] = tab; P.fold_tab_loc_n[s] = n; P.fold_tab_loc_world[s] = world; P.fold_tab_loc_rank[s] = rank;
     *out = (const Affine<C>*)tab;
     return HALO_OK;
 }

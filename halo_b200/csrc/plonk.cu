@@ -882,7 +882,22 @@ int plonk_prove(unsigned lg_n, const uint64_t* polys, const uint64_t* w_evals, c
         memcpy(k ? o_piro : o_pir, q + 21, evalproof_words(lg_n) * 8);
         return HALO_OK;
     };
-    if (sharded) {
+    if (sharded && dist_half_available()) {
+        // four or more GPUs: opening 0 sharded over the first HALF of the ranks, opening 1 over the second half, side by
+        // side (halves of the communicator, ncclCommSplit); the two instances then travel over the full communicator
+        const int hw = world / 2, h = rank / hw;
+        if (int e = dist_half_enter()) return e;
+        const int rc_h = open_k(h, true);
+        dist_half_leave();
+        if (rc_h) return rc_h;
+        std::vector<uint64_t> mine(iw), all((size_t)iw * world);
+        memcpy(mine.data(), insts.data() + (size_t)(1 + h) * iw, iw * 8);
+        if (int e = dist_allgather_host(mine.data(), all.data(), (size_t)iw * 8)) return e;
+        for (int k = 0; k < 2; ++k) {
+            memcpy(insts.data() + (size_t)(1 + k) * iw, all.data() + (size_t)(k * hw) * iw, iw * 8);
+            memcpy(k ? o_piro : o_pir, insts.data() + (size_t)(1 + k) * iw + 21, evalproof_words(lg_n) * 8);
+        }
+    } else if (sharded) {
         // opening k on rank k, the instances travel as one all-gather.  (Measured on 8 GPUs: an opening sharded over all
         // ranks takes 29.7 ms against 46 ms on one GPU -- its 15 tail rounds do not shard -- so two sharded openings one
         // after the other, 59 ms, lose against two unsharded ones side by side.)

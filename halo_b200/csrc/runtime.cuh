@@ -28,9 +28,11 @@ struct ResidentParams {
     void* d_fixed_tab = nullptr;      // commit path: rows 2^(c w) * Gs[i] (ipa.cu ensure_fixed_table, msm.cu msm_fixed)
     size_t fixed_tab_n = 0;
     int fixed_tab_c = 0;
-    void* d_fold_tab_loc = nullptr;   // the same table over this rank's generators of a sharded opening (ipa.cu)
-    size_t fold_tab_loc_n = 0;
-    int fold_tab_loc_world = 0, fold_tab_loc_rank = 0;
+    // the same table over this rank's generators of a sharded opening (ipa.cu): slot 0 for the whole communicator, slot 1
+    // for its half (the one-proof prover uses both in every proof)
+    void* d_fold_tab_loc[2] = {nullptr, nullptr};
+    size_t fold_tab_loc_n[2] = {0, 0};
+    int fold_tab_loc_world[2] = {0, 0}, fold_tab_loc_rank[2] = {0, 0};
 };
 
 struct Runtime {

@@ -197,3 +197,10 @@ def test_dist_paths_world_size_1():
 @pytest.mark.timeout(600)
 def test_dist_paths_world_size_2():
     _run(2)
+
+
+@pytest.mark.timeout(900)
+def test_dist_paths_world_size_4():
+    """Four ranks: the sharded opening over four interleaved slices, and in the one-proof prover the two openings on the
+    two HALVES of the communicator (ncclCommSplit)."""
+    _run(4)
