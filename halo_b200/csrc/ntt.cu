@@ -99,6 +99,21 @@ __global__ void __launch_bounds__(NTT_THREADS) ntt_pass_kernel(Fe<F>* __restrict
         const int t = P.t0 + st;
         const int u = P.s - 1 - st;                       // bit of the row index paired by this stage
         const u32 umask = (1u << u) - 1u;
+        if (t == P.n - 1) {
+            // the last stage of the transform: j = 0 for every butterfly, the twiddle is omega^0 = 1 in both directions,
+            // and a product with one returns its (already reduced) operand -- a twentieth of a 2^20 transform's
+            // multiplications that need not be done
+            for (u32 b = threadIdx.x; b < (tile >> 1); b += NTT_THREADS) {
+                const u32 l = b & qmask, r = b >> P.q;
+                const u32 m0 = ((r >> u) << (u + 1)) | (r & umask);
+                const u32 e0 = (m0 << P.q) | l, e1 = e0 + (1u << (u + P.q));
+                Fe<F> a = sm_get<F>(lo, hi, e0), c = sm_get<F>(lo, hi, e1);
+                sm_put<F>(lo, hi, e0, fe_add<F>(a, c));
+                sm_put<F>(lo, hi, e1, fe_sub<F>(a, c));
+            }
+            __syncthreads();
+            continue;
+        }
         for (u32 b = threadIdx.x; b < (tile >> 1); b += NTT_THREADS) {
             const u32 l = b & qmask, r = b >> P.q;
             const u32 m0 = ((r >> u) << (u + 1)) | (r & umask);
