@@ -6,10 +6,10 @@ over the C ABI of libhalo_b200.so.  Elements are numpy uint64 arrays holding the
 """
 from . import _lib
 from ._lib import HaloError, ParamsError, PreconditionError, Rejected, init
-from . import consts, group, pp, pedersen, poly, pcdl, acc, plonk, dist, serialize
+from . import consts, group, pp, pedersen, poly, pcdl, acc, plonk, dist, serialize, poseidon
 
 PALLAS, VESTA = 0, 1
 FP, FQ = 0, 1
 
-__all__ = ["init", "group", "pp", "pedersen", "poly", "pcdl", "acc", "plonk", "dist", "serialize", "consts", "HaloError", "ParamsError", "PreconditionError", "Rejected",
+__all__ = ["init", "group", "pp", "pedersen", "poly", "pcdl", "acc", "plonk", "dist", "serialize", "poseidon", "consts", "HaloError", "ParamsError", "PreconditionError", "Rejected",
            "PALLAS", "VESTA", "FP", "FQ"]

@@ -194,6 +194,15 @@ int halo_dist_acc_prover(int curve, const uint64_t* instances, size_t m, uint64_
 int halo_dist_acc_verifier(int curve, const uint64_t* instances, size_t m, const uint64_t* acc);
 int halo_dist_acc_decider(int curve, const uint64_t* acc);
 int halo_dist_ntt(int field, uint64_t* data, unsigned log_n, size_t b, int inverse, const uint64_t* coset_offset_or_null);
+/* Poseidon on the device: `count` INDEPENDENT sponges, one GPU thread each.  Sponge k absorbs
+ * inputs[k * len .. (k + 1) * len) (Montgomery elements of `field`, 4 words each) and squeezes one element into out[k] --
+ * InnerSponge::new / absorb / squeeze of crates/poseidon/src/inner_sponge.rs:11-115 (Kimchi parameters: x^7, 55 full
+ * rounds, width 3, rate 2; constants of crates/group/src/poseidon_consts.rs).  A single Fiat-Shamir transcript is a
+ * serial chain and stays on the host inside the library; this entry is for batches (hash-to-field over a column, Merkle
+ * layers, many transcripts at once).  len = 0 squeezes the empty sponge.  The _dev variant takes device pointers and
+ * only enqueues on the library stream. */
+int halo_poseidon_hash_batch(int field, const uint64_t* inputs, size_t len, size_t count, uint64_t* out);
+int halo_poseidon_hash_batch_dev(int field, const void* d_inputs, size_t len, size_t count, void* d_out);
 /* pcdl::open (crates/accumulation/src/pcdl.rs:326-473) over the GPUs of the communicator.  Collective; every rank passes
  * the SAME arguments (those of halo_pcdl_open) and receives the same proof, equal to halo_pcdl_open's.  The rounds above
  * the fold-free tail run on interleaved slices (rank r owns the indices j * world + r of the generator, coefficient and
